@@ -1,0 +1,114 @@
+/* b200approx.h -- C ABI of libb200approx.so: the B200 (sm_100a) implementation of
+ * util.approximate's distance-based predict/fit hot path.
+ *
+ * The reference crosses Python -> ctypes -> Fortran once PER QUERY POINT
+ * (fmodpy-generated `c_<routine>` BIND(C) symbols, every argument by pointer:
+ * util/approximate/shepard/weight/weight_bind_c.f90:7-28, weight_from_py.py:54-85).
+ * That per-point loop is what this library replaces, so each entry point below
+ * takes the whole batch of query points.  Conventions:
+ *   - plain C, no exceptions; every function returns 0 on success, non-zero on
+ *     error (text via b200_last_error()).
+ *   - the caller owns every host buffer; the library owns device memory behind
+ *     the model handle; one handle = one fitted data set on one GPU; calls on a
+ *     handle are serialised by the caller.
+ *   - matrices are row-major fp64 (numpy C order: points x dimensions); indices
+ *     are 0-based int64 (numpy's default), status arrays int32.
+ *   - there is no CPU fallback: without a CUDA device every call fails.
+ */
+#ifndef B200APPROX_H
+#define B200APPROX_H
+#include <stdint.h>
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+typedef struct b200_model b200_model;
+
+/* sub-model weighting used by NearestNeighbor(method=...) */
+enum { B200_AVERAGE = 0, B200_SHEPARD = 1, B200_VORONOI = 2 };
+/* knn path selection for b200_set_option("knn_path") */
+enum { B200_PATH_AUTO = 0, B200_PATH_EXACT = 1, B200_PATH_TENSOR = 2 };
+
+int b200_version(void);
+const char* b200_last_error(void);
+int b200_device_count(void);
+
+/* Upload the fitted points x (n,d) to `device`.  Replaces the state the reference
+ * models keep after _fit: NearestNeighbor.points + BallTree
+ * (nearest_neighbor/__init__.py:29-35), ShepMod.x (modified_shepard/__init__.py:30),
+ * LSHEP.x (linear_shepard/__init__.py:38), Voronoi.points (voronoi/__init__.py:33). */
+int b200_create(const double* x, int64_t n, int32_t d, int32_t device, b200_model** out);
+int b200_destroy(b200_model* m);
+
+/* Tunables ("knn_path", "margin", "rows_per_call") and counters ("uncertified",
+ * "ms_stage1", "ms_rerank", "ms_weights", "ms_exact", "launches", ...). */
+int b200_set_option(b200_model* m, const char* key, double value);
+int b200_get_stat(b200_model* m, const char* key, double* value);
+
+/* k nearest fitted points of each query, ascending by (squared distance, index):
+ * the batched form of `self.tree.query(pt[None,:], k=..., return_distance=False)`
+ * (nearest_neighbor/__init__.py:75-76).  idx (q,k); d2 (q,k) squared distances
+ * (may be NULL).  self_offset >= 0 excludes data row self_offset+p for query p
+ * (the "other nodes" scans of SHEPMOD / LSHEP: modified_shepard.f95:45-53). */
+int b200_knn(b200_model* m, const double* z, int64_t q, int32_t k, int64_t self_offset,
+             int64_t* idx, double* d2);
+
+/* NearestNeighbor._predict + WeightedApproximator.predict
+ * (nearest_neighbor/__init__.py:60-89, base.py:146-173): kNN, sub-model weights
+ * on the k neighbours (Average :7-14, Shepard = WEIGHT shepard/weight.f90:1-34,
+ * Voronoi = PREDICT voronoi/voronoi.f90:57-155), and, when y != NULL, the
+ * weighted sums.  ids/wts (q,k) padded rows with cnt (q) valid entries (any may
+ * be NULL); err (q) sub-model error codes (Voronoi ERROR 0/1/2); y (n,r),
+ * out (q,r). */
+int b200_nn_predict(b200_model* m, const double* z, int64_t q, int32_t k, int32_t method,
+                    const double* y, int32_t r, int64_t* ids, double* wts, int32_t* cnt,
+                    int32_t* err, double* out);
+
+/* SHEPMOD (modified_shepard.f95:10-60): radius of influence rw (n); *ier 0/1. */
+int b200_shepmod_fit(b200_model* m, double* rw, int32_t* ier);
+/* SHEPMODVAL over a batch + ShepMod._predict's `wts > 0` filter
+ * (modified_shepard.f95:83-176, modified_shepard/__init__.py:39-58).
+ * ids/wts (q,cap) ascending index, cnt (q) true counts (rows with cnt > cap are
+ * truncated: call again with a larger cap), ier (q) 0/1; optional y (n,r) ->
+ * out (q,r). */
+int b200_shepmod_predict(b200_model* m, const double* z, int64_t q, int32_t cap, int64_t* ids,
+                         double* wts, int32_t* cnt, int32_t* ier, const double* y, int32_t r,
+                         double* out);
+
+/* LSHEP non-robust fit (linear_shepard.f95:23-134,177; DGELSS replaced by a
+ * batched Householder QR, rank-deficient nodes flagged IER=2): f (n,r) response
+ * columns; a (r,n,d) gradients, rw (n) radii BEFORE the wrapper's `radius`
+ * multiplier (linear_shepard/__init__.py:55); *ier 0/1/2. */
+int b200_lshep_fit(b200_model* m, const double* f, int32_t r, double* a, double* rw,
+                   int32_t* ier);
+/* LSHEPVAL over a batch (linear_shepard.f95:365-472) with the radii scaled by
+ * `radius`: out (q,r), ier (q,r) 0/1/2. */
+int b200_lshep_predict(b200_model* m, double radius, const double* z, int64_t q, double* out,
+                       int32_t* ier);
+
+/* ---- device-pointer forms (inputs/outputs already in HBM on the model's GPU;
+ * `stream` is a cudaStream_t, NULL = default).  No counterpart in the reference
+ * (it has no device memory); used for the HBM-resident throughput figure and
+ * the multi-GPU path.  idx is int32 here. */
+int b200_knn_dev(b200_model* m, const double* z_dev, int64_t q, int32_t k, int64_t self_offset,
+                 int32_t* idx_dev, double* d2_dev, void* stream);
+int b200_nn_weights_dev(b200_model* m, const double* z_dev, int64_t q, int32_t k, int32_t method,
+                        const int32_t* idx_dev, const double* y_dev, int32_t r, double* wts_dev,
+                        int32_t* cnt_dev, int32_t* err_dev, double* out_dev, void* stream);
+/* Data-sharded kNN merge: `parts` lists of (q,k) sorted (d2, global idx) -> the k
+ * best per query by (d2, idx).  d2_parts/idx_parts are (parts,q,k) contiguous. */
+int b200_merge_topk_dev(int32_t device, const double* d2_parts, const int32_t* idx_parts,
+                        int32_t parts, int64_t q, int32_t k, double* d2_out, int32_t* idx_out,
+                        void* stream);
+
+/* Test hook, no counterpart in the reference: run the tensor path on q <= 4096
+ * queries and return the raw stage-1 scores (q, cols) with cols = 128*ceil(n/128),
+ * score = s^2 * (||y_j - mu||^2 - 2 (z - mu).(y_j - mu)), s = stat "tc_scale". */
+int b200_tc_debug_scores(b200_model* m, const double* z, int64_t q, int32_t k, float* scores,
+                         int64_t cols);
+
+#ifdef __cplusplus
+}
+#endif
+#endif

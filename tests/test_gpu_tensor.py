@@ -1,0 +1,117 @@
+"""GPU tests of the tensor-core kNN path (tcgen05 fused distance + selection,
+fp64 re-rank, certificate, exact fallback): the result must be the exact
+(d2, index)-ordered neighbours, bit for bit, whatever the filter does."""
+import numpy as np
+import pytest
+
+from conftest import fun, synth
+
+pytestmark = pytest.mark.gpu
+
+
+@pytest.fixture(scope="module")
+def L():
+    from util_b200 import _lib
+    assert _lib.lib().b200_device_count() >= 1
+    return _lib
+
+
+def test_stage1_scores_match_fp64_within_bound(L):
+    """score/s^2 + ||z-mu||^2 must equal the exact d^2 up to the fp16 operand rounding;
+    checks the UMMA descriptors, the K-major tile images and the norm triple."""
+    for (n, q, d) in [(1000, 300, 8), (700, 256, 64), (513, 100, 29)]:
+        x, z = synth(n, q, d)
+        m = L.Model(x)
+        s = m.tc_debug_scores(z, k=1)
+        sc = m.stat("tc_scale")
+        K = int(m.stat("tc_K"))
+        assert K % 16 == 0 and K >= d + 3
+        D = ((z[:, None, :] - x[None, :, :]) ** 2).sum(-1)
+        est = s[:, :n].astype(np.float64) / sc ** 2
+        # per query the offset ||z - mu||^2 is constant: compare centred differences
+        off = np.median(D - est, axis=1, keepdims=True)
+        err = np.abs(D - est - off)
+        ymax = m.stat("tc_ymax")
+        bound = 4 * 2.0 ** -11 * (2 * np.sqrt(d) * 1.0) * ymax / sc ** 2 + 1e-4
+        assert err.max() < bound, (n, q, d, err.max(), bound)
+        assert np.all(s[:, n:] > 5e4)  # padding columns carry the sentinel norm
+        mu = x.mean(0)
+        assert np.allclose(off[:, 0], ((z - mu) ** 2).sum(1), rtol=1e-3, atol=1e-3)
+
+
+@pytest.mark.parametrize("n,q,d,k", [(20000, 1000, 64, 16), (30000, 700, 16, 17), (9000, 513, 8, 1),
+                                     (12000, 300, 32, 33), (5000, 260, 10, 15), (40000, 300, 3, 8)])
+def test_tensor_knn_bit_exact(L, oracle, n, q, d, k):
+    x, z = synth(n, q, d)
+    m = L.Model(x)
+    m.set_option("knn_path", L.PATH_TENSOR)
+    idx, d2 = m.knn(z, k)
+    oi, od = oracle.knn(x, z, k)
+    assert np.array_equal(idx, oi)
+    assert np.array_equal(d2, od)
+    assert m.stat("tc_queries") == q
+    # the filter should certify nearly everything on uniform data
+    assert m.stat("uncertified") <= 0.2 * q
+
+
+def test_tensor_knn_self_excluding(L, oracle):
+    x, _ = synth(15000, 1, 16)
+    m = L.Model(x)
+    m.set_option("knn_path", L.PATH_TENSOR)
+    idx, d2 = m.knn(x[:2000], 17, self_offset=0)
+    oi, od = oracle.knn(x, x[:2000], 18)
+    assert np.array_equal(idx, oi[:, 1:]) and np.array_equal(d2, od[:, 1:])
+
+
+def test_tensor_knn_hard_inputs(L, oracle):
+    """Clustered / duplicated / far-offset data: the certificate must send what the
+    fp16 filter cannot separate to the exact path, never return a wrong index."""
+    rng = np.random.default_rng(5)
+    # tight clusters far from the origin
+    centres = rng.random((20, 12)) * 100 + 1000
+    x = np.repeat(centres, 500, axis=0) + rng.normal(scale=1e-3, size=(10000, 12))
+    z = np.repeat(centres, 10, axis=0) + rng.normal(scale=1e-3, size=(200, 12))
+    m = L.Model(x)
+    m.set_option("knn_path", L.PATH_TENSOR)
+    idx, d2 = m.knn(z, 8)
+    oi, od = oracle.knn(x, z, 8)
+    assert np.array_equal(idx, oi) and np.array_equal(d2, od)
+    # exact duplicates and lattice ties -> lowest index wins
+    g = np.array([[a, b, c] for a in range(16) for b in range(16) for c in range(16)], dtype=float)
+    x = np.vstack([g, g])
+    z = g[::9] + 0.5
+    m = L.Model(x)
+    m.set_option("knn_path", L.PATH_TENSOR)
+    idx, d2 = m.knn(z, 10)
+    oi, od = oracle.knn(x, z, 10)
+    assert np.array_equal(idx, oi) and np.array_equal(d2, od)
+    # queries far outside the data (fp16 overflow guard) and n not a multiple of 128
+    x, z = synth(4999, 130, 5)
+    z[:5] *= 1e6
+    m = L.Model(x)
+    m.set_option("knn_path", L.PATH_TENSOR)
+    idx, d2 = m.knn(z, 4)
+    oi, od = oracle.knn(x, z, 4)
+    assert np.array_equal(idx, oi) and np.array_equal(d2, od)
+
+
+def test_tensor_knn_round_trip_at_size(L):
+    """Size-independent properties at a larger size (no oracle): every fitted row is its own
+    nearest neighbour at distance 0, distances ascend, indices are in range and distinct."""
+    n, d, k = 200000, 64, 16
+    x = np.random.default_rng(0).random((n, d))
+    m = L.Model(x)
+    m.set_option("knn_path", L.PATH_TENSOR)
+    sel = np.random.default_rng(2).choice(n, 4096, replace=False)
+    idx, d2 = m.knn(x[sel], k)
+    assert np.array_equal(idx[:, 0], sel) and np.all(d2[:, 0] == 0)
+    assert np.all(np.diff(d2, axis=1) >= 0)
+    assert idx.min() >= 0 and idx.max() < n
+    assert all(len(set(r)) == k for r in idx[:200])
+    # and d2 is exactly the reference arithmetic on the returned rows
+    j = idx[:50]
+    ref = np.zeros((50, k))
+    for c in range(d):
+        t = x[sel[:50], None, c] - x[j, c]
+        ref += t * t
+    assert np.array_equal(ref, d2[:50])

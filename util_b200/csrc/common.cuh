@@ -1,0 +1,147 @@
+// common.cuh -- shared declarations of libb200approx (sm_100a only).
+#pragma once
+#include <cuda_runtime.h>
+#include <cuda_fp16.h>
+#include <math_constants.h>
+#include <stdint.h>
+#include <stdio.h>
+#include <string.h>
+#include <string>
+#include <vector>
+#include <algorithm>
+#include <cmath>
+
+#include "../../include/b200approx.h"
+
+namespace b200 {
+
+void set_error(const char* fmt, ...);
+
+#define B200_CUDA(call)                                                              \
+  do {                                                                               \
+    cudaError_t e_ = (call);                                                         \
+    if (e_ != cudaSuccess) {                                                         \
+      b200::set_error("%s:%d %s -> %s", __FILE__, __LINE__, #call, cudaGetErrorString(e_)); \
+      return 2;                                                                      \
+    }                                                                                \
+  } while (0)
+
+#define B200_TRY(call)        \
+  do {                        \
+    int rc_ = (call);         \
+    if (rc_) return rc_;      \
+  } while (0)
+
+// Grow-only device buffer (library-owned scratch reused across calls).
+struct DevBuf {
+  void* p = nullptr;
+  size_t cap = 0;
+  int reserve(size_t bytes) {
+    if (bytes <= cap) return 0;
+    if (p) cudaFree(p);
+    p = nullptr;
+    cap = 0;
+    size_t want = bytes + bytes / 4 + 256;
+    cudaError_t e = cudaMalloc(&p, want);
+    if (e != cudaSuccess) {
+      set_error("cudaMalloc(%zu) -> %s", want, cudaGetErrorString(e));
+      return 2;
+    }
+    cap = want;
+    return 0;
+  }
+  void release() {
+    if (p) cudaFree(p);
+    p = nullptr;
+    cap = 0;
+  }
+  template <class T> T* as() const { return reinterpret_cast<T*>(p); }
+};
+
+// Tensor-path operand images of the fitted points (knn_tc.cu).
+struct TcData {
+  bool ready = false;
+  int K = 0;            // padded contraction length (multiple of 16)
+  int64_t tiles = 0;    // 128-point tiles
+  double scale = 1.0;   // power of two applied after centring
+  double ymax = 0.0;    // max over points of max(||yc||, ||fp16(yc)||) (scaled units)
+  double cmax = 0.0;    // max |coordinate| of the raw data
+  DevBuf mu;            // d doubles: per-dimension centre
+  DevBuf img;           // tiles * 128 * K halfs, UMMA K-major no-swizzle tile images
+};
+
+struct Stats {
+  double uncertified = 0, ms_stage1 = 0, ms_rerank = 0, ms_weights = 0, ms_exact = 0,
+         launches = 0, tc_queries = 0, exact_queries = 0, last_cap = 0;
+};
+
+}  // namespace b200
+
+struct b200_model {
+  int device = 0;
+  int64_t n = 0;
+  int d = 0;
+  int sm_count = 148;
+  double* x = nullptr;  // (n,d) row-major fp64 on the device
+  b200::TcData tc;
+  // ShepMod / LSHEP fitted state
+  b200::DevBuf rw, lf, la;  // rw (n); lshep f (r,n), a (r,n,d)
+  int lshep_r = 0;
+  bool shepmod_ready = false, lshep_ready = false;
+  // cached response values for fused weighted sums
+  b200::DevBuf y;
+  // scratch
+  b200::DevBuf zq, idx32, d2, wts, cnt, err, out, part_d2, part_idx, cand, cand_meta, zimg,
+      flags, misc, ids64;
+  // options
+  int knn_path = 0;
+  int margin = -1;  // extra candidates kept by the tensor filter (-1: = k)
+  int64_t rows_per_call = 1 << 20;
+  b200::Stats st;
+  cudaEvent_t ev0 = nullptr, ev1 = nullptr, ev2 = nullptr;
+  float* dbg_scores = nullptr;  // tests only: raw tensor-path scores are dumped here
+};
+
+namespace b200 {
+
+// api.cu: picks the tensor or the exact kNN path
+int knn_dispatch(b200_model* m, const double* z_dev, int64_t q, int k, int64_t self_offset,
+                 int32_t* idx_dev, double* d2_dev, cudaStream_t st);
+// knn_exact.cu
+int knn_exact(b200_model* m, const double* z_dev, int64_t q, int k, int64_t self_offset,
+              int32_t* idx_dev, double* d2_dev, const int32_t* qsel, int64_t nsel,
+              cudaStream_t st);
+int merge_topk(const double* d2_parts, const int32_t* idx_parts, int parts, int64_t q, int k,
+               double* d2_out, int32_t* idx_out, cudaStream_t st);
+// knn_tc.cu
+bool tc_supported(const b200_model* m, int k);
+int knn_tc(b200_model* m, const double* z_dev, int64_t q, int k, int64_t self_offset,
+           int32_t* idx_dev, double* d2_dev, cudaStream_t st);
+// weights.cu
+int nn_weights(b200_model* m, const double* z_dev, int64_t q, int k, int method,
+               const int32_t* idx_dev, const double* y_dev, int r, double* wts_dev,
+               int32_t* cnt_dev, int32_t* err_dev, double* out_dev, cudaStream_t st);
+// shepmod.cu
+int shepmod_fit(b200_model* m, cudaStream_t st, int* ier);
+int shepmod_predict(b200_model* m, const double* z_dev, int64_t q, int cap, int32_t* ids_dev,
+                    double* wts_dev, int32_t* cnt_dev, int32_t* ier_dev, const double* y_dev, int r,
+                    double* out_dev, cudaStream_t st);
+// lshep.cu
+int lshep_fit(b200_model* m, const double* f_dev, int r, cudaStream_t st, int* ier);
+int lshep_predict(b200_model* m, double radius, const double* z_dev, int64_t q, double* out_dev,
+                  int32_t* ier_dev, cudaStream_t st);
+
+__host__ __device__ inline int64_t imin64(int64_t a, int64_t b) { return a < b ? a : b; }
+
+// Exact fp64 arithmetic with the reference's roundings: no FMA contraction.
+__device__ __forceinline__ double sqdist_seq(const double* __restrict__ a,
+                                             const double* __restrict__ b, int d) {
+  double s = 0.0;
+  for (int j = 0; j < d; ++j) {
+    double t = __dsub_rn(a[j], b[j]);
+    s = __dadd_rn(s, __dmul_rn(t, t));
+  }
+  return s;
+}
+
+}  // namespace b200

@@ -1,0 +1,255 @@
+// knn_exact.cu -- exact fp64 brute-force kNN on CUDA cores.
+//
+// Replaces sklearn BallTree.query as NearestNeighbor calls it
+// (nearest_neighbor/__init__.py:75-76) and the all-pairs scans of SHEPMOD / LSHEP
+// (modified_shepard.f95:45-55, linear_shepard.f95:105-115).  Squared distances
+// are formed exactly as the reference does -- direct differences summed over
+// ascending dimension with separate multiply and add roundings
+// (sklearn metrics/_dist_metrics.pxd rdist) -- so (d2, index) ordering and the
+// returned d2 are bit-identical.  This is the small-problem path, the fallback
+// for queries the tensor path cannot certify, and the scan used by the fits.
+//
+// Layout: one thread owns one query (its running top-k in local memory, its
+// coordinates in a transposed shared tile), data rows stream through shared
+// memory in tiles and are broadcast-read by the whole block.  The data range is
+// split across blockIdx.y so small query batches still fill 148 SMs; partial
+// lists land in scratch and are merged by merge_topk_kernel.
+#include "common.cuh"
+
+namespace b200 {
+
+namespace {
+
+template <int KMAX>
+__device__ __forceinline__ void topk_insert(double* bd, int* bi, int k, double d2, int gi) {
+  int j = k - 1;
+  while (j > 0 && bd[j - 1] > d2) {  // strict: equal distances keep the earlier (lower) index
+    bd[j] = bd[j - 1];
+    bi[j] = bi[j - 1];
+    --j;
+  }
+  bd[j] = d2;
+  bi[j] = gi;
+}
+
+template <int KMAX, int QB>
+__global__ void __launch_bounds__(QB)
+knn_exact_kernel(const double* __restrict__ x, int64_t n, int d, const double* __restrict__ z,
+                 int64_t q, int k, int64_t self_offset, const int32_t* __restrict__ qsel,
+                 int64_t split_len, int tile_pts, int32_t* __restrict__ out_idx,
+                 double* __restrict__ out_d2, int direct) {
+  extern __shared__ double sm[];
+  double* zs = sm;                    // [d][QB] transposed queries
+  double* xs = sm + (size_t)d * QB;   // [tile_pts][d] data tile
+  const int t = threadIdx.x;
+  const int64_t slot = (int64_t)blockIdx.x * QB + t;  // position in the (selected) query list
+  const bool live = slot < q;
+  const int64_t p = live ? (qsel ? (int64_t)qsel[slot] : slot) : 0;
+
+  for (int e = t; e < d * QB; e += QB) {
+    int qq = e / d, j = e - qq * d;
+    int64_t s2 = (int64_t)blockIdx.x * QB + qq;
+    double v = 0.0;
+    if (s2 < q) {
+      int64_t pp = qsel ? (int64_t)qsel[s2] : s2;
+      v = z[pp * d + j];
+    }
+    zs[(size_t)j * QB + qq] = v;
+  }
+
+  double bd[KMAX];
+  int bi[KMAX];
+#pragma unroll 1
+  for (int j = 0; j < k; ++j) {
+    bd[j] = CUDART_INF;
+    bi[j] = -1;
+  }
+  double worst = CUDART_INF;
+  const int64_t self = (self_offset >= 0) ? self_offset + p : -1;
+
+  const int64_t lo = (int64_t)blockIdx.y * split_len;
+  const int64_t hi = min(n, lo + split_len);
+  for (int64_t base = lo; base < hi; base += tile_pts) {
+    const int cnt = (int)imin64(tile_pts, hi - base);
+    __syncthreads();
+    {
+      const double* src = x + base * d;
+      const int tot = cnt * d;
+      for (int e = t; e < tot; e += QB) xs[e] = src[e];
+    }
+    __syncthreads();
+    if (live) {
+      int i = 0;
+      for (; i + 4 <= cnt; i += 4) {
+        double a0 = 0, a1 = 0, a2 = 0, a3 = 0;
+        const double* r0 = xs + (size_t)i * d;
+        const double* r1 = r0 + d;
+        const double* r2 = r1 + d;
+        const double* r3 = r2 + d;
+#pragma unroll 4
+        for (int j = 0; j < d; ++j) {
+          const double zj = zs[(size_t)j * QB + t];
+          double t0 = __dsub_rn(zj, r0[j]), t1 = __dsub_rn(zj, r1[j]);
+          double t2 = __dsub_rn(zj, r2[j]), t3 = __dsub_rn(zj, r3[j]);
+          a0 = __dadd_rn(a0, __dmul_rn(t0, t0));
+          a1 = __dadd_rn(a1, __dmul_rn(t1, t1));
+          a2 = __dadd_rn(a2, __dmul_rn(t2, t2));
+          a3 = __dadd_rn(a3, __dmul_rn(t3, t3));
+        }
+        const int g = (int)(base + i);
+        if (a0 < worst && g != self) { topk_insert<KMAX>(bd, bi, k, a0, g); worst = bd[k - 1]; }
+        if (a1 < worst && g + 1 != self) { topk_insert<KMAX>(bd, bi, k, a1, g + 1); worst = bd[k - 1]; }
+        if (a2 < worst && g + 2 != self) { topk_insert<KMAX>(bd, bi, k, a2, g + 2); worst = bd[k - 1]; }
+        if (a3 < worst && g + 3 != self) { topk_insert<KMAX>(bd, bi, k, a3, g + 3); worst = bd[k - 1]; }
+      }
+      for (; i < cnt; ++i) {
+        double a0 = 0;
+        const double* r0 = xs + (size_t)i * d;
+        for (int j = 0; j < d; ++j) {
+          double t0 = __dsub_rn(zs[(size_t)j * QB + t], r0[j]);
+          a0 = __dadd_rn(a0, __dmul_rn(t0, t0));
+        }
+        const int g = (int)(base + i);
+        if (a0 < worst && g != self) { topk_insert<KMAX>(bd, bi, k, a0, g); worst = bd[k - 1]; }
+      }
+    }
+  }
+  if (live) {
+    const int64_t o = direct ? p * k : ((int64_t)blockIdx.y * q + slot) * k;
+    for (int j = 0; j < k; ++j) {
+      out_idx[o + j] = bi[j];
+      if (out_d2) out_d2[o + j] = bd[j];
+    }
+  }
+}
+
+// k-way merge of `parts` ascending (d2, idx) lists per query.  Lists are
+// (parts, q, k); idx -1 marks an empty slot (d2 = +inf).  Output position is
+// qsel[slot] when qsel != NULL.
+__global__ void merge_topk_kernel(const double* __restrict__ pd2, const int32_t* __restrict__ pidx,
+                                  int parts, int64_t q, int k, const int32_t* __restrict__ qsel,
+                                  double* __restrict__ od2, int32_t* __restrict__ oidx) {
+  const int64_t slot = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
+  if (slot >= q) return;
+  const int64_t p = qsel ? (int64_t)qsel[slot] : slot;
+  unsigned short head[512];
+  for (int s = 0; s < parts; ++s) head[s] = 0;
+  for (int j = 0; j < k; ++j) {
+    double best = CUDART_INF;
+    int bidx = 0x7fffffff, bs = -1;
+    for (int s = 0; s < parts; ++s) {
+      const int h = head[s];
+      if (h >= k) continue;
+      const int64_t o = ((int64_t)s * q + slot) * k + h;
+      const int id = pidx[o];
+      if (id < 0) continue;
+      const double v = pd2[o];
+      if (v < best || (v == best && id < bidx)) {
+        best = v;
+        bidx = id;
+        bs = s;
+      }
+    }
+    if (bs >= 0) head[bs]++;
+    oidx[p * k + j] = bs >= 0 ? bidx : -1;
+    if (od2) od2[p * k + j] = best;
+  }
+}
+
+template <int KMAX>
+int launch_exact(b200_model* m, const double* z, int64_t q, int k, int64_t self_offset,
+                 const int32_t* qsel, int32_t* idx, double* d2, cudaStream_t st) {
+  const int d = m->d;
+  const int64_t n = m->n;
+  // block size / tile size from the shared-memory budget
+  int QB = d <= 96 ? 128 : (d <= 256 ? 64 : 32);
+  size_t zbytes = (size_t)d * QB * 8;
+  int tile_pts = (int)((160 * 1024 - zbytes) / ((size_t)d * 8));
+  if (tile_pts > 256) tile_pts = 256;
+  tile_pts &= ~3;
+  if (tile_pts < 4) {
+    set_error("knn_exact: dimension %d too large for the shared-memory tiling", d);
+    return 3;
+  }
+  const size_t smem = zbytes + (size_t)tile_pts * d * 8;
+  const int64_t qblocks = (q + QB - 1) / QB;
+  // split the data range so that the grid covers >= 2 waves of the SMs
+  int64_t S = 1;
+  const int64_t want = 2 * (int64_t)m->sm_count;
+  if (qblocks < want) S = (want + qblocks - 1) / qblocks;
+  const int64_t max_s = (n + (int64_t)4 * tile_pts - 1) / ((int64_t)4 * tile_pts);
+  if (S > max_s) S = max_s;
+  if (S > 512) S = 512;
+  if (S < 1) S = 1;
+  int64_t split_len = (n + S - 1) / S;
+  split_len = (split_len + 3) & ~(int64_t)3;
+  S = (n + split_len - 1) / split_len;
+  const int direct = (S == 1);
+  int32_t* oi = idx;
+  double* od = d2;
+  if (!direct) {
+    B200_TRY(m->part_idx.reserve((size_t)S * q * k * sizeof(int32_t)));
+    B200_TRY(m->part_d2.reserve((size_t)S * q * k * sizeof(double)));
+    oi = m->part_idx.as<int32_t>();
+    od = m->part_d2.as<double>();
+  } else if (!od) {
+    od = nullptr;
+  }
+  dim3 grid((unsigned)qblocks, (unsigned)S);
+#define LAUNCH_QB(QBV)                                                                          \
+  do {                                                                                          \
+    auto kern = knn_exact_kernel<KMAX, QBV>;                                                    \
+    B200_CUDA(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem)); \
+    kern<<<grid, QBV, smem, st>>>(m->x, n, d, z, q, k, self_offset, qsel, split_len, tile_pts, oi, \
+                                  od, direct);                                                  \
+  } while (0)
+  if (QB == 128) LAUNCH_QB(128);
+  else if (QB == 64) LAUNCH_QB(64);
+  else LAUNCH_QB(32);
+#undef LAUNCH_QB
+  B200_CUDA(cudaGetLastError());
+  m->st.launches += 1;
+  if (!direct) {
+    merge_topk_kernel<<<(unsigned)((q + 127) / 128), 128, 0, st>>>(od, oi, (int)S, q, k, qsel, d2, idx);
+    B200_CUDA(cudaGetLastError());
+    m->st.launches += 1;
+  }
+  return 0;
+}
+
+}  // namespace
+
+// z_dev (>= max query index, d).  qsel == NULL: queries 0..q-1 -> rows 0..q-1 of the
+// outputs.  qsel != NULL: nsel selected query indices; results are written to
+// the rows they name (fallback for uncertified tensor-path queries).
+int knn_exact(b200_model* m, const double* z_dev, int64_t q, int k, int64_t self_offset,
+              int32_t* idx_dev, double* d2_dev, const int32_t* qsel, int64_t nsel,
+              cudaStream_t st) {
+  const int64_t cntq = qsel ? nsel : q;
+  if (cntq == 0) return 0;
+  if (k < 1 || k > m->n - (self_offset >= 0 ? 1 : 0)) {
+    set_error("knn: k=%d out of range for n=%lld", k, (long long)m->n);
+    return 1;
+  }
+  if (k <= 8) return launch_exact<8>(m, z_dev, cntq, k, self_offset, qsel, idx_dev, d2_dev, st);
+  if (k <= 32) return launch_exact<32>(m, z_dev, cntq, k, self_offset, qsel, idx_dev, d2_dev, st);
+  if (k <= 128) return launch_exact<128>(m, z_dev, cntq, k, self_offset, qsel, idx_dev, d2_dev, st);
+  if (k <= 1024) return launch_exact<1024>(m, z_dev, cntq, k, self_offset, qsel, idx_dev, d2_dev, st);
+  set_error("knn: k=%d > 1024 unsupported", k);
+  return 1;
+}
+
+int merge_topk(const double* d2_parts, const int32_t* idx_parts, int parts, int64_t q, int k,
+               double* d2_out, int32_t* idx_out, cudaStream_t st) {
+  if (parts > 512) {
+    set_error("merge_topk: parts=%d > 512", parts);
+    return 1;
+  }
+  if (q == 0) return 0;
+  merge_topk_kernel<<<(unsigned)((q + 127) / 128), 128, 0, st>>>(d2_parts, idx_parts, parts, q, k,
+                                                                  nullptr, d2_out, idx_out);
+  B200_CUDA(cudaGetLastError());
+  return 0;
+}
+
+}  // namespace b200

@@ -1,0 +1,487 @@
+// lshep.cu -- linear Shepard (LSHEP) fit and predict.
+//
+// Fit  = LSHEP, non-robust branch (linear_shepard.f95:91-134,177; the Python
+//        wrapper never passes RLSHEP, linear_shepard/__init__.py:36,53):
+//          1. self-excluding kNN with NP = min(N-1,(3M+1)/2) neighbours (:98-115)
+//          2. per node a weighted NP x M least-squares problem (:116-134).  The
+//             reference calls LAPACK DGELSS (SVD, minimum norm); here it is a
+//             batched Householder QR with column pivoting, one thread per node,
+//             the systems stored [element][node] in scratch so loads coalesce.
+//             Full-rank systems agree with DGELSS to rounding; a node whose
+//             pivot falls below NP*eps*|R11| is flagged (IER=2) and gets the
+//             basic solution of its leading full-rank block.
+//          3. DIAM = max pairwise squared distance (:114) only enters through
+//             RW = min(sqrt(DIAM)/2, RW) (:177).  A lower bound L <= DIAM from two
+//             farthest-point sweeps proves the clamp inactive when
+//             max RW <= sqrt(L)/2; otherwise the exact O(N^2) maximum is taken.
+// Eval = LSHEPVAL over the query batch (linear_shepard.f95:365-472): one thread
+//        per query, nodes stream through shared memory in index order.  With the
+//        wrapper's radius=2 thousands of nodes contribute per query, so this is
+//        a dense fp64 CUDA-core pass: sum(W), sum(W*nodal value), the weighted
+//        slope; a second pass applies the slope-angle test (:460-469).
+#include <math_constants.h>
+
+#include "common.cuh"
+
+namespace b200 {
+
+namespace {
+
+// ---------------------------------------------------------------- fit kernels
+__global__ void lshep_build_kernel(const double* __restrict__ x, int64_t n, int d, int np,
+                                   const int32_t* __restrict__ idx, const double* __restrict__ d2,
+                                   const double* __restrict__ f, double* __restrict__ W,
+                                   double* __restrict__ rw) {
+  // W: [(np*(d+1))][n]; element (i, j) of node k at W[(j*np + i)*n + k], j = d is the rhs
+  const int64_t k = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
+  if (k >= n) return;
+  const double rk = sqrt(d2[k * np + np - 1]);  // :116,:121
+  rw[k] = rk;
+  const double rp = __dmul_rn(1.1, rk);  // :125
+  const double fk = f[k];
+  for (int i = 0; i < np; ++i) {
+    const int nb = idx[k * np + i];
+    const double dist = sqrt(d2[k * np + i]);
+    const double om = __ddiv_rn(__dsub_rn(rp, dist), __dmul_rn(rp, dist));  // :126
+    for (int j = 0; j < d; ++j)
+      W[((size_t)j * np + i) * n + k] = __dmul_rn(om, __dsub_rn(x[(int64_t)nb * d + j], x[k * d + j]));  // :118-120,:129-131
+    W[((size_t)d * np + i) * n + k] = __dmul_rn(om, __dsub_rn(f[nb], fk));  // :117,:128
+  }
+}
+
+// Householder QR with column pivoting, one thread per node, in place on W.
+// a (n,d) gets the solution; rank (n) the numerical rank.
+template <int DMAX>
+__global__ void lshep_qr_kernel(double* __restrict__ W, int64_t n, int d, int np,
+                                double* __restrict__ a, int32_t* __restrict__ rank_out,
+                                int32_t* __restrict__ flag) {
+  const int64_t k = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
+  if (k >= n) return;
+#define A_(i, j) W[((size_t)(j) * np + (i)) * n + k]
+  int perm[DMAX];
+  double cn[DMAX];
+  for (int j = 0; j < d; ++j) {
+    perm[j] = j;
+    double s = 0.0;
+    for (int i = 0; i < np; ++i) s += A_(i, j) * A_(i, j);
+    cn[j] = s;
+  }
+  int rank = d;
+  double r00 = 0.0;
+  const double tol = (double)np * 2.220446049250313e-16;  // RCOND, :100
+  for (int c = 0; c < d; ++c) {
+    // pivot: remaining column with the largest norm (recomputed for accuracy)
+    int pv = c;
+    double best = -1.0;
+    for (int j = c; j < d; ++j) {
+      double s = 0.0;
+      for (int i = c; i < np; ++i) s += A_(i, j) * A_(i, j);
+      cn[j] = s;
+      if (s > best) { best = s; pv = j; }
+    }
+    if (pv != c) {
+      for (int i = 0; i < np; ++i) { const double tmp = A_(i, c); A_(i, c) = A_(i, pv); A_(i, pv) = tmp; }
+      const int tp = perm[c]; perm[c] = perm[pv]; perm[pv] = tp;
+    }
+    const double nrm = sqrt(best);
+    if (c == 0) r00 = nrm;
+    if (!(nrm > tol * r00) || nrm == 0.0) { rank = c; break; }
+    const double a0 = A_(c, c);
+    const double alpha = a0 >= 0 ? -nrm : nrm;
+    const double v0 = a0 - alpha;
+    // v = (v0, A(c+1.., c)); beta = 2 / (v.v)
+    double vv = v0 * v0;
+    for (int i = c + 1; i < np; ++i) vv += A_(i, c) * A_(i, c);
+    const double beta = vv > 0 ? 2.0 / vv : 0.0;
+    for (int j = c + 1; j <= d; ++j) {  // includes the rhs column j = d
+      double s = v0 * A_(c, j);
+      for (int i = c + 1; i < np; ++i) s += A_(i, c) * A_(i, j);
+      s *= beta;
+      A_(c, j) -= s * v0;
+      for (int i = c + 1; i < np; ++i) A_(i, j) -= s * A_(i, c);
+    }
+    A_(c, c) = alpha;
+  }
+  // back substitution on the leading rank x rank block
+  double sol[DMAX];
+  for (int j = 0; j < d; ++j) sol[j] = 0.0;
+  for (int c = rank - 1; c >= 0; --c) {
+    double s = A_(c, d);
+    for (int j = c + 1; j < rank; ++j) s -= A_(c, j) * sol[j];
+    sol[c] = s / A_(c, c);
+  }
+  for (int j = 0; j < d; ++j) a[k * d + perm[j]] = sol[j];  // :134
+  if (rank_out) rank_out[k] = rank;
+  if (rank < d) atomicMax(flag, 2);  // :135
+#undef A_
+}
+
+// squared distance of every node to one anchor row; block max -> atomic max (as ordered uint64)
+__global__ void far_from_kernel(const double* __restrict__ x, int64_t n, int d,
+                                const double* __restrict__ anchor, unsigned long long* __restrict__ best) {
+  const int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
+  double v = -1.0;
+  if (i < n) v = sqdist_seq(x + i * d, anchor, d);
+  // pack (d2 bits, index) so the max also yields the farthest row; d2 >= 0 so bits order as uint
+  unsigned long long key = i < n ? ((unsigned long long)__double_as_longlong(v) & ~0xFFFFFULL) : 0ULL;
+  unsigned long long mx = key;
+  for (int o = 16; o > 0; o >>= 1) {
+    unsigned long long t = __shfl_xor_sync(0xffffffffu, mx, o);
+    mx = t > mx ? t : mx;
+  }
+  if ((threadIdx.x & 31) == 0) atomicMax(best, mx);
+  (void)key;
+}
+__global__ void far_pick_kernel(const double* __restrict__ x, int64_t n, int d,
+                                const double* __restrict__ anchor, const unsigned long long* best,
+                                int* __restrict__ pick) {
+  const int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
+  if (i >= n) return;
+  const double v = sqdist_seq(x + i * d, anchor, d);
+  if (((unsigned long long)__double_as_longlong(v) & ~0xFFFFFULL) == *best) atomicMin(pick, (int)i);
+}
+__global__ void col_mean_kernel(const double* __restrict__ x, int64_t n, int d, double* __restrict__ mu) {
+  // one block per dimension
+  __shared__ double sh[256];
+  const int j = blockIdx.x;
+  double s = 0.0;
+  for (int64_t i = threadIdx.x; i < n; i += blockDim.x) s += x[i * d + j];
+  sh[threadIdx.x] = s;
+  __syncthreads();
+  for (int o = 128; o > 0; o >>= 1) {
+    if (threadIdx.x < o) sh[threadIdx.x] += sh[threadIdx.x + o];
+    __syncthreads();
+  }
+  if (threadIdx.x == 0) mu[j] = sh[0] / (double)n;
+}
+__global__ void max_reduce_kernel(const double* __restrict__ v, int64_t n, unsigned long long* __restrict__ best) {
+  const int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
+  unsigned long long mx = i < n ? (unsigned long long)__double_as_longlong(v[i]) : 0ULL;
+  for (int o = 16; o > 0; o >>= 1) {
+    unsigned long long t = __shfl_xor_sync(0xffffffffu, mx, o);
+    mx = t > mx ? t : mx;
+  }
+  if ((threadIdx.x & 31) == 0) atomicMax(best, mx);
+}
+// exact DIAM: thread per row i, all rows j stream through shared memory
+__global__ void __launch_bounds__(128)
+diam_exact_kernel(const double* __restrict__ x, int64_t n, int d, int tile_pts,
+                  unsigned long long* __restrict__ best) {
+  extern __shared__ double sm[];
+  double* zs = sm;
+  double* xs = sm + (size_t)d * 128;
+  const int t = threadIdx.x;
+  const int64_t p = (int64_t)blockIdx.x * 128 + t;
+  for (int e = t; e < d * 128; e += 128) {
+    const int qq = e / d, j = e - qq * d;
+    const int64_t pp = (int64_t)blockIdx.x * 128 + qq;
+    zs[(size_t)j * 128 + qq] = pp < n ? x[pp * d + j] : 0.0;
+  }
+  double mx = 0.0;
+  for (int64_t base = 0; base < n; base += tile_pts) {
+    const int tc = (int)imin64(tile_pts, n - base);
+    __syncthreads();
+    for (int e = t; e < tc * d; e += 128) xs[e] = x[base * d + e];
+    __syncthreads();
+    if (p < n)
+      for (int i = 0; i < tc; ++i) {
+        double a = 0.0;
+        for (int j = 0; j < d; ++j) {
+          const double df = __dsub_rn(xs[(size_t)i * d + j], zs[(size_t)j * 128 + t]);
+          a = __dadd_rn(a, __dmul_rn(df, df));
+        }
+        mx = fmax(mx, a);
+      }
+  }
+  unsigned long long key = (unsigned long long)__double_as_longlong(mx);
+  for (int o = 16; o > 0; o >>= 1) {
+    unsigned long long tt = __shfl_xor_sync(0xffffffffu, key, o);
+    key = tt > key ? tt : key;
+  }
+  if ((t & 31) == 0) atomicMax(best, key);
+}
+__global__ void clamp_rw_kernel(double* __restrict__ rw, int64_t n, double half) {
+  const int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
+  if (i < n) rw[i] = fmin(half, rw[i]);  // :177
+}
+// unit normals [A(:,K); -1] / ||.|| used by the slope-angle test (:463-464)
+__global__ void unit_slope_kernel(const double* __restrict__ a, int64_t n, int d, double* __restrict__ ah) {
+  const int64_t k = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
+  if (k >= n) return;
+  double s = 0.0;
+  for (int j = 0; j < d; ++j) s = __dadd_rn(s, __dmul_rn(a[k * d + j], a[k * d + j]));
+  s = sqrt(__dadd_rn(s, 1.0));
+  for (int j = 0; j < d; ++j) ah[k * (d + 1) + j] = __ddiv_rn(a[k * d + j], s);
+  ah[k * (d + 1) + d] = __ddiv_rn(-1.0, s);
+}
+
+// --------------------------------------------------------------- eval kernel
+constexpr int LS_QB = 128;
+
+template <int DMAX>
+__global__ void __launch_bounds__(LS_QB)
+lshep_eval_kernel(const double* __restrict__ x, const double* __restrict__ f, const double* __restrict__ a,
+                  const double* __restrict__ ah, const double* __restrict__ rw, double radius, int64_t n,
+                  int d, const double* __restrict__ z, int64_t q, int tile_pts, double* __restrict__ out,
+                  int32_t* __restrict__ ier, int ostride) {
+  extern __shared__ double sm[];
+  double* xs = sm;                          // [tile][d]
+  double* as = xs + (size_t)tile_pts * d;   // [tile][d]   gradients, later unit normals [tile][d+1]
+  double* fs = as + (size_t)tile_pts * (d + 1);
+  double* rs = fs + tile_pts;
+  const int t = threadIdx.x;
+  const int64_t p = (int64_t)blockIdx.x * LS_QB + t;
+  const bool live = p < q;
+  double zq[DMAX], slope[DMAX + 1];
+#pragma unroll
+  for (int j = 0; j < DMAX; ++j) {
+    zq[j] = (live && j < d) ? z[p * d + j] : 0.0;
+    slope[j] = 0.0;
+  }
+  slope[DMAX] = 0.0;
+  double D[DMAX + 1];
+  int DI[DMAX + 1];
+#pragma unroll
+  for (int j = 0; j <= DMAX; ++j) { D[j] = 0.0; DI[j] = 0; }
+  int J = 0, c = 0, hit = -1;
+  double temp = 0.0, sw = 0.0, sv = 0.0;
+  const int m1 = d + 1;
+
+  for (int64_t base = 0; base < n; base += tile_pts) {
+    const int tc = (int)imin64(tile_pts, n - base);
+    __syncthreads();
+    for (int e = t; e < tc * d; e += LS_QB) { xs[e] = x[base * d + e]; as[e] = a[base * d + e]; }
+    for (int e = t; e < tc; e += LS_QB) { fs[e] = f[base + e]; rs[e] = __dmul_rn(rw[base + e], radius); }
+    __syncthreads();
+    if (!live || hit >= 0) continue;
+    for (int i = 0; i < tc; ++i) {
+      const double* xr = xs + (size_t)i * d;
+      double df[DMAX];
+      double acc = 0.0;
+#pragma unroll
+      for (int j = 0; j < DMAX; ++j)
+        if (j < d) {
+          df[j] = __dsub_rn(zq[j], xr[j]);
+          acc = __dadd_rn(acc, __dmul_rn(df[j], df[j]));
+        }
+      const double dist = sqrt(acc);  // :426
+      const double rk = rs[i];
+      if (dist < rk) {
+        if (__dsub_rn(rk, dist) == rk) { hit = (int)(base + i); break; }  // :428-431
+        const double u = __ddiv_rn(__dsub_rn(rk, dist), __dmul_rn(rk, dist));
+        const double w = __dmul_rn(u, u);  // :433
+        const double* ar = as + (size_t)i * d;
+        double nv = 0.0;  // :435
+#pragma unroll
+        for (int j = 0; j < DMAX; ++j)
+          if (j < d) {
+            nv = __dadd_rn(nv, __dmul_rn(ar[j], df[j]));
+            slope[j] = fma(ar[j], w, slope[j]);
+          }
+        nv = __dadd_rn(nv, fs[i]);
+        slope[DMAX] -= w;
+        sw = __dadd_rn(sw, w);
+        sv = fma(w, nv, sv);
+        ++c;
+      } else if (c == 0) {
+        const double w = __ddiv_rn(1.0, dist);  // :439-445
+        if (w > temp) {
+#pragma unroll
+          for (int u2 = 0; u2 <= DMAX; ++u2)
+            if (u2 == J) { D[u2] = w; DI[u2] = (int)(base + i); }
+          int jm = 0;
+          double dm = D[0];
+#pragma unroll
+          for (int u2 = 1; u2 <= DMAX; ++u2)
+            if (u2 < m1 && D[u2] < dm) { dm = D[u2]; jm = u2; }
+          J = jm;
+          temp = dm;
+        }
+      }
+    }
+  }
+  int e = 0;
+  double val = 0.0;
+  bool need2 = false;
+  if (live) {
+    if (hit >= 0) {
+      val = f[hit];
+    } else if (c == 0) {  // :450-454
+      e = 1;
+      double sd = 0.0;
+#pragma unroll
+      for (int u2 = 0; u2 <= DMAX; ++u2)
+        if (u2 < m1) { D[u2] = __dmul_rn(D[u2], D[u2]); sd = __dadd_rn(sd, D[u2]); }
+#pragma unroll
+      for (int u2 = 0; u2 <= DMAX; ++u2)
+        if (u2 < m1) val = __dadd_rn(val, __dmul_rn(__ddiv_rn(D[u2], sd), f[DI[u2]]));
+    } else {
+      val = sv / sw;  // :456-457 up to summation order
+      need2 = true;
+      double nn = slope[DMAX] * slope[DMAX];
+#pragma unroll
+      for (int j = 0; j < DMAX; ++j) nn = fma(slope[j], slope[j], nn);
+      nn = sqrt(nn);
+#pragma unroll
+      for (int j = 0; j <= DMAX; ++j) slope[j] = slope[j] / nn;  // :462 (scale of SW cancels)
+    }
+  }
+  // second pass: IER = 2 iff some contributing normal has cosine < 0.9 with the mean (:460-469)
+  for (int64_t base = 0; base < n; base += tile_pts) {
+    const int tc = (int)imin64(tile_pts, n - base);
+    __syncthreads();
+    for (int e2 = t; e2 < tc * d; e2 += LS_QB) xs[e2] = x[base * d + e2];
+    for (int e2 = t; e2 < tc * (d + 1); e2 += LS_QB) as[e2] = ah[base * (d + 1) + e2];
+    for (int e2 = t; e2 < tc; e2 += LS_QB) rs[e2] = __dmul_rn(rw[base + e2], radius);
+    __syncthreads();
+    if (!need2 || e == 2) continue;
+    for (int i = 0; i < tc; ++i) {
+      const double* xr = xs + (size_t)i * d;
+      double acc = 0.0;
+#pragma unroll
+      for (int j = 0; j < DMAX; ++j)
+        if (j < d) {
+          const double dfj = __dsub_rn(zq[j], xr[j]);
+          acc = __dadd_rn(acc, __dmul_rn(dfj, dfj));
+        }
+      if (sqrt(acc) < rs[i]) {
+        const double* hr = as + (size_t)i * (d + 1);
+        double dp = slope[DMAX] * hr[d];
+#pragma unroll
+        for (int j = 0; j < DMAX; ++j)
+          if (j < d) dp = fma(slope[j], hr[j], dp);
+        if (dp < 0.9) { e = 2; break; }
+      }
+    }
+  }
+  if (live) {
+    out[p * ostride] = val;
+    ier[p * ostride] = e;
+  }
+}
+
+}  // namespace
+
+int lshep_fit(b200_model* m, const double* f_dev, int r, cudaStream_t st, int* ier) {
+  const int64_t n = m->n;
+  const int d = m->d;
+  *ier = 0;
+  if (d < 1 || n <= d + 1) {  // :91-94
+    *ier = 1;
+    return 0;
+  }
+  if (d > 64) {
+    set_error("lshep_fit: dimension %d > 64 unsupported", d);
+    return 1;
+  }
+  const int np = (int)imin64(n - 1, (3 * d + 1) / 2);  // :98
+  B200_TRY(m->idx32.reserve((size_t)n * np * 4));
+  B200_TRY(m->d2.reserve((size_t)n * np * 8));
+  B200_TRY(m->rw.reserve((size_t)n * 8));
+  B200_TRY(m->lf.reserve((size_t)r * n * 8));
+  B200_TRY(m->la.reserve((size_t)r * n * (2 * d + 1) * 8));  // a (r,n,d) then unit normals (r,n,d+1)
+  B200_TRY(m->misc.reserve((size_t)np * (d + 1) * n * 8 + 64));
+  B200_TRY(m->flags.reserve(256));
+  B200_CUDA(cudaMemcpyAsync(m->lf.p, f_dev, (size_t)r * n * 8, cudaMemcpyDeviceToDevice, st));
+  B200_TRY(knn_dispatch(m, m->x, n, np, 0, m->idx32.as<int32_t>(), m->d2.as<double>(), st));
+  B200_CUDA(cudaMemsetAsync(m->flags.p, 0, 256, st));
+  int32_t* flag = m->flags.as<int32_t>();
+  const unsigned gb = (unsigned)((n + 127) / 128);
+  for (int c = 0; c < r; ++c) {
+    double* ac = m->la.as<double>() + (size_t)c * n * d;
+    lshep_build_kernel<<<gb, 128, 0, st>>>(m->x, n, d, np, m->idx32.as<int32_t>(), m->d2.as<double>(),
+                                           m->lf.as<double>() + (size_t)c * n, m->misc.as<double>(),
+                                           m->rw.as<double>());
+    if (d <= 16) lshep_qr_kernel<16><<<gb, 128, 0, st>>>(m->misc.as<double>(), n, d, np, ac, nullptr, flag);
+    else lshep_qr_kernel<64><<<gb, 128, 0, st>>>(m->misc.as<double>(), n, d, np, ac, nullptr, flag);
+    unit_slope_kernel<<<gb, 128, 0, st>>>(ac, n, d, m->la.as<double>() + (size_t)r * n * d + (size_t)c * n * (d + 1));
+    B200_CUDA(cudaGetLastError());
+    m->st.launches += 3;
+  }
+  // ---- DIAM clamp (:114,:177)
+  unsigned long long* best = reinterpret_cast<unsigned long long*>(m->flags.as<char>() + 64);
+  int* pick = reinterpret_cast<int*>(m->flags.as<char>() + 128);
+  double* mu = reinterpret_cast<double*>(m->misc.p);  // scratch free again (QR done, stream ordered)
+  unsigned long long h_best[3];
+  col_mean_kernel<<<d, 256, 0, st>>>(m->x, n, d, mu);
+  const double* anchor = mu;
+  for (int sweep = 0; sweep < 2; ++sweep) {
+    B200_CUDA(cudaMemsetAsync(best + sweep, 0, 8, st));
+    int big = 0x7fffffff;
+    B200_CUDA(cudaMemcpyAsync(pick, &big, 4, cudaMemcpyHostToDevice, st));
+    far_from_kernel<<<gb, 128, 0, st>>>(m->x, n, d, anchor, best + sweep);
+    far_pick_kernel<<<gb, 128, 0, st>>>(m->x, n, d, anchor, best + sweep, pick);
+    int h_pick = 0;
+    B200_CUDA(cudaMemcpyAsync(&h_pick, pick, 4, cudaMemcpyDeviceToHost, st));
+    B200_CUDA(cudaStreamSynchronize(st));
+    anchor = m->x + (int64_t)h_pick * d;
+    m->st.launches += 2;
+  }
+  B200_CUDA(cudaMemsetAsync(best + 2, 0, 8, st));
+  max_reduce_kernel<<<gb, 128, 0, st>>>(m->rw.as<double>(), n, best + 2);
+  B200_CUDA(cudaMemcpyAsync(h_best, best, 24, cudaMemcpyDeviceToHost, st));
+  int h_flag = 0;
+  B200_CUDA(cudaMemcpyAsync(&h_flag, flag, 4, cudaMemcpyDeviceToHost, st));
+  B200_CUDA(cudaStreamSynchronize(st));
+  double lower, maxrw;
+  memcpy(&lower, &h_best[1], 8);  // truncated key: a valid lower bound of the true d2
+  memcpy(&maxrw, &h_best[2], 8);
+  if (!(maxrw <= sqrt(lower) / 2.0)) {
+    // the clamp may bind: take the exact diameter
+    const size_t zb = (size_t)d * 128 * 8;
+    int tile_pts = (int)((96 * 1024 - zb) / ((size_t)d * 8));
+    if (tile_pts > 256) tile_pts = 256;
+    const size_t smem = zb + (size_t)tile_pts * d * 8;
+    B200_CUDA(cudaFuncSetAttribute(diam_exact_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+    B200_CUDA(cudaMemsetAsync(best, 0, 8, st));
+    diam_exact_kernel<<<gb, 128, smem, st>>>(m->x, n, d, tile_pts, best);
+    B200_CUDA(cudaMemcpyAsync(h_best, best, 8, cudaMemcpyDeviceToHost, st));
+    B200_CUDA(cudaStreamSynchronize(st));
+    double diam;
+    memcpy(&diam, &h_best[0], 8);
+    clamp_rw_kernel<<<gb, 128, 0, st>>>(m->rw.as<double>(), n, sqrt(diam) / 2.0);
+    B200_CUDA(cudaGetLastError());
+    m->st.launches += 2;
+  }
+  *ier = h_flag;
+  m->lshep_r = r;
+  m->lshep_ready = true;
+  return 0;
+}
+
+int lshep_predict(b200_model* m, double radius, const double* z_dev, int64_t q, double* out_dev,
+                  int32_t* ier_dev, cudaStream_t st) {
+  if (!m->lshep_ready) {
+    set_error("lshep_predict: model not fitted (call b200_lshep_fit)");
+    return 1;
+  }
+  if (q == 0) return 0;
+  const int64_t n = m->n;
+  const int d = m->d, r = m->lshep_r;
+  int tile_pts = 256;
+  const size_t smem = ((size_t)tile_pts * (2 * d + 3)) * 8;
+  const unsigned gb = (unsigned)((q + LS_QB - 1) / LS_QB);
+  for (int c = 0; c < r; ++c) {
+    const double* fc = m->lf.as<double>() + (size_t)c * n;
+    const double* ac = m->la.as<double>() + (size_t)c * n * d;
+    const double* hc = m->la.as<double>() + (size_t)r * n * d + (size_t)c * n * (d + 1);
+#define LS_LAUNCH(DM)                                                                                 \
+  do {                                                                                                \
+    auto kern = lshep_eval_kernel<DM>;                                                                \
+    B200_CUDA(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));    \
+    kern<<<gb, LS_QB, smem, st>>>(m->x, fc, ac, hc, m->rw.as<double>(), radius, n, d, z_dev, q,        \
+                                  tile_pts, out_dev + c, ier_dev + c, r);                             \
+  } while (0)
+    if (d <= 4) LS_LAUNCH(4);
+    else if (d <= 8) LS_LAUNCH(8);
+    else if (d <= 16) LS_LAUNCH(16);
+    else if (d <= 32) LS_LAUNCH(32);
+    else LS_LAUNCH(64);
+#undef LS_LAUNCH
+    B200_CUDA(cudaGetLastError());
+    m->st.launches += 1;
+  }
+  return 0;
+}
+
+}  // namespace b200

@@ -1,0 +1,216 @@
+// shepmod.cu -- modified Shepard (ShepMod) fit and predict.
+//
+// Fit  = SHEPMOD (modified_shepard.f95:10-60): rw[K] is the distance from node K
+//        to its (M+1)-th nearest OTHER node -> one self-excluding kNN with
+//        k = M+1 (tensor or exact path) and a square root of the last column.
+// Eval = SHEPMODVAL over the whole query batch (modified_shepard.f95:83-176) fused
+//        with ShepMod._predict's `wts > 0` compaction
+//        (modified_shepard/__init__.py:44-55) and WeightedApproximator.predict's
+//        weighted sum (base.py:169).
+//
+// Eval kernel: one thread per query, nodes stream through shared memory in
+// ascending index order, so the hit list, SUM(WTS) (f95:172) and the weighted
+// sum are accumulated in exactly the reference's order; distances use direct
+// differences in dimension order without FMA contraction.  Work per pair is
+// 3M+2 fp64 operations: this stage is fp64-pipe bound, not HBM bound.
+#include <math_constants.h>
+
+#include "common.cuh"
+
+namespace b200 {
+
+int knn_dispatch(b200_model* m, const double* z_dev, int64_t q, int k, int64_t self_offset,
+                 int32_t* idx_dev, double* d2_dev, cudaStream_t st);
+
+namespace {
+
+__global__ void rw_from_knn_kernel(const double* __restrict__ d2, int64_t n, int k,
+                                   double* __restrict__ rw) {
+  const int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
+  if (i < n) rw[i] = sqrt(d2[i * k + (k - 1)]);  // modified_shepard.f95:57
+}
+
+constexpr int SM_QB = 128;   // queries per block
+constexpr int SM_FB = 72;    // fallback slots kept per thread (M+1 <= SM_FB)
+
+__global__ void __launch_bounds__(SM_QB)
+shepmod_eval_kernel(const double* __restrict__ x, const double* __restrict__ rw, int64_t n, int d,
+                    const double* __restrict__ z, int64_t q, int cap, int tile_pts,
+                    int32_t* __restrict__ ids, double* __restrict__ wts, int32_t* __restrict__ cnt,
+                    int32_t* __restrict__ ier, const double* __restrict__ y, int r,
+                    double* __restrict__ out) {
+  extern __shared__ double sm[];
+  double* zs = sm;                        // [d][QB]
+  double* xs = zs + (size_t)d * SM_QB;    // [tile_pts][d]
+  double* rs = xs + (size_t)tile_pts * d; // [tile_pts]
+  const int t = threadIdx.x;
+  const int64_t p = (int64_t)blockIdx.x * SM_QB + t;
+  const bool live = p < q;
+  for (int e = t; e < d * SM_QB; e += SM_QB) {
+    const int qq = e / d, j = e - qq * d;
+    const int64_t pp = (int64_t)blockIdx.x * SM_QB + qq;
+    zs[(size_t)j * SM_QB + qq] = pp < q ? z[pp * d + j] : 0.0;
+  }
+  const int m1 = d + 1;
+  double D[SM_FB];
+  int DI[SM_FB];
+  for (int i = 0; i < m1; ++i) { D[i] = 0.0; DI[i] = -1; }  // :124-125
+  int J = 0;
+  double temp = 0.0;   // :126
+  int c = 0;           // nodes whose radius contains the query (I in the source)
+  double s = 0.0;      // running SUM(WTS) in index order
+  int hit = -1;        // exact-hit node
+  int32_t* myid = ids + p * cap;
+  double* myw = wts + p * cap;
+
+  for (int64_t base = 0; base < n; base += tile_pts) {
+    const int tc = (int)imin64(tile_pts, n - base);
+    __syncthreads();
+    for (int e = t; e < tc * d; e += SM_QB) xs[e] = x[base * d + e];
+    for (int e = t; e < tc; e += SM_QB) rs[e] = rw[base + e];
+    __syncthreads();
+    if (!live || hit >= 0) continue;
+    for (int i = 0; i < tc; ++i) {
+      const double* xr = xs + (size_t)i * d;
+      double a = 0.0;
+#pragma unroll 4
+      for (int j = 0; j < d; ++j) {
+        const double df = __dsub_rn(zs[(size_t)j * SM_QB + t], xr[j]);
+        a = __dadd_rn(a, __dmul_rn(df, df));
+      }
+      const double dist = sqrt(a);  // :132
+      const double rk = rs[i];
+      if (dist < rk) {
+        if (__dsub_rn(rk, dist) == rk) {  // :136-140
+          hit = (int)(base + i);
+          break;
+        }
+        const double u = __ddiv_rn(__dsub_rn(rk, dist), __dmul_rn(rk, dist));  // :143
+        const double w = __dmul_rn(u, u);
+        if (c < cap) {
+          myid[c] = (int)(base + i);
+          myw[c] = w;
+        }
+        s = __dadd_rn(s, w);
+        ++c;
+      } else if (c == 0) {
+        const double w = __ddiv_rn(1.0, dist);  // :150
+        if (w > temp) {                          // :152-158
+          D[J] = w;
+          DI[J] = (int)(base + i);
+          int jm = 0;
+          double dm = D[0];
+          for (int u2 = 1; u2 < m1; ++u2)
+            if (D[u2] < dm) { dm = D[u2]; jm = u2; }  // MINLOC: first minimum
+          J = jm;
+          temp = dm;
+        }
+      }
+    }
+  }
+  if (!live) return;
+  int e = 0;
+  if (hit >= 0) {  // one-hot (:137-139)
+    myid[0] = hit;
+    myw[0] = 1.0;
+    c = 1;
+  } else if (c == 0) {  // :163-170 original Shepard on the M+1 kept nodes
+    e = 1;
+    double sd = 0.0;
+    for (int i = 0; i < m1; ++i) { D[i] = __dmul_rn(D[i], D[i]); }
+    for (int i = 0; i < m1; ++i) sd = __dadd_rn(sd, D[i]);
+    // ascending node index, as `base[wts > 0]` returns them
+    for (int i = 1; i < m1; ++i) {
+      const double dv = D[i];
+      const int iv = DI[i];
+      int j = i;
+      while (j > 0 && DI[j - 1] > iv) { D[j] = D[j - 1]; DI[j] = DI[j - 1]; --j; }
+      D[j] = dv;
+      DI[j] = iv;
+    }
+    for (int i = 0; i < m1; ++i) {
+      if (DI[i] < 0) continue;
+      const double w = __ddiv_rn(D[i], sd);
+      if (w > 0) {
+        if (c < cap) { myid[c] = DI[i]; myw[c] = w; }
+        ++c;
+      }
+    }
+  } else {  // :172
+    const int lim = c < cap ? c : cap;
+    int kept = 0;
+    for (int i = 0; i < lim; ++i) {
+      const double w = __ddiv_rn(myw[i], s);
+      if (w > 0) {  // a weight can underflow to zero; the wrapper drops those
+        myid[kept] = myid[i];
+        myw[kept] = w;
+        ++kept;
+      }
+    }
+    if (c <= cap) c = kept;
+  }
+  cnt[p] = c;
+  ier[p] = e;
+  if (out) {
+    const int lim = c < cap ? c : cap;
+    for (int col = 0; col < r; ++col) {
+      double acc = 0.0;  // base.py:169
+      for (int i = 0; i < lim; ++i) acc = __dadd_rn(acc, __dmul_rn(y[(int64_t)myid[i] * r + col], myw[i]));
+      out[p * r + col] = acc;
+    }
+  }
+}
+
+}  // namespace
+
+int shepmod_fit(b200_model* m, cudaStream_t st, int* ier) {
+  const int64_t n = m->n;
+  const int d = m->d;
+  *ier = 0;
+  if (d < 1 || n <= d + 1) {  // :37-40
+    *ier = 1;
+    return 0;
+  }
+  const int k = d + 1;  // :42
+  B200_TRY(m->idx32.reserve((size_t)n * k * 4));
+  B200_TRY(m->d2.reserve((size_t)n * k * 8));
+  B200_TRY(m->rw.reserve((size_t)n * 8));
+  B200_TRY(knn_dispatch(m, m->x, n, k, 0, m->idx32.as<int32_t>(), m->d2.as<double>(), st));
+  rw_from_knn_kernel<<<(unsigned)((n + 255) / 256), 256, 0, st>>>(m->d2.as<double>(), n, k, m->rw.as<double>());
+  B200_CUDA(cudaGetLastError());
+  m->st.launches += 1;
+  m->shepmod_ready = true;
+  return 0;
+}
+
+int shepmod_predict(b200_model* m, const double* z_dev, int64_t q, int cap, int32_t* ids_dev,
+                    double* wts_dev, int32_t* cnt_dev, int32_t* ier_dev, const double* y_dev, int r,
+                    double* out_dev, cudaStream_t st) {
+  if (!m->shepmod_ready) {
+    set_error("shepmod_predict: model not fitted (call b200_shepmod_fit)");
+    return 1;
+  }
+  if (q == 0) return 0;
+  const int d = m->d;
+  if (d + 1 > SM_FB) {
+    set_error("shepmod_predict: dimension %d > %d unsupported", d, SM_FB - 1);
+    return 1;
+  }
+  if (cap < d + 1) {
+    set_error("shepmod_predict: cap=%d must be at least M+1=%d", cap, d + 1);
+    return 1;
+  }
+  const size_t zb = (size_t)d * SM_QB * 8;
+  int tile_pts = (int)((128 * 1024 - zb) / ((size_t)(d + 1) * 8));
+  if (tile_pts > 512) tile_pts = 512;
+  const size_t smem = zb + (size_t)tile_pts * (d + 1) * 8;
+  B200_CUDA(cudaFuncSetAttribute(shepmod_eval_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+  shepmod_eval_kernel<<<(unsigned)((q + SM_QB - 1) / SM_QB), SM_QB, smem, st>>>(
+      m->x, m->rw.as<double>(), m->n, d, z_dev, q, cap, tile_pts, ids_dev, wts_dev, cnt_dev, ier_dev,
+      y_dev, r, y_dev ? out_dev : nullptr);
+  B200_CUDA(cudaGetLastError());
+  m->st.launches += 1;
+  return 0;
+}
+
+}  // namespace b200

@@ -1,0 +1,279 @@
+// weights.cu -- sub-model weights on the k nearest neighbours and the weighted sums.
+//
+// Replaces, for the whole query batch, the per-query body of
+// NearestNeighbor._predict (nearest_neighbor/__init__.py:78-83: construct
+// self.method(), fit it on the k neighbours, predict the query) and
+// WeightedApproximator.predict's sum(self.y[i]*w) (base.py:159-169):
+//   Average  nearest_neighbor/__init__.py:7-14
+//   Shepard  WEIGHT, shepard/weight.f90:1-34
+//   Voronoi  PREDICT, voronoi/voronoi.f90:57-155 on the k neighbours
+// These are gather/stream kernels bound by HBM: each query reads its k fitted
+// rows once.  fp64 arithmetic keeps the reference's operand grouping and
+// dimension-order sums without FMA contraction.
+#include <math_constants.h>
+
+#include "common.cuh"
+
+namespace b200 {
+
+namespace {
+
+// One warp per query; lane i owns neighbour i (+32, ...).  KL = ceil(k/32) <= 4.
+__global__ void __launch_bounds__(256)
+avg_shepard_kernel(const double* __restrict__ x, int d, const double* __restrict__ z, int64_t q,
+                   int k, int method, const int32_t* __restrict__ idx,
+                   const double* __restrict__ y, int r, double* __restrict__ wts,
+                   int32_t* __restrict__ cnt, int32_t* __restrict__ err, double* __restrict__ out) {
+  const int lane = threadIdx.x & 31;
+  const int64_t p = ((int64_t)blockIdx.x * blockDim.x + threadIdx.x) >> 5;
+  if (p >= q) return;
+  const double* pt = z + p * d;
+  const int32_t* id = idx + p * k;
+  constexpr int KL = 4;
+  double w[KL];
+  int nb[KL];
+  if (method == B200_AVERAGE) {
+    const double a = 1.0 / (double)k;  // nearest_neighbor/__init__.py:12
+#pragma unroll
+    for (int u = 0; u < KL; ++u) {
+      const int i = lane + 32 * u;
+      nb[u] = i < k ? id[i] : -1;
+      w[u] = a;
+    }
+  } else {
+    double dist[KL];
+    double mn = CUDART_INF, mx = 0.0;
+#pragma unroll
+    for (int u = 0; u < KL; ++u) {
+      const int i = lane + 32 * u;
+      nb[u] = i < k ? id[i] : -1;
+      dist[u] = 0.0;
+      if (i < k) {
+        dist[u] = sqrt(sqdist_seq(x + (int64_t)nb[u] * d, pt, d));  // weight.f90:13-15
+        mn = fmin(mn, dist[u]);
+        mx = fmax(mx, dist[u]);
+      }
+    }
+#pragma unroll
+    for (int o = 16; o > 0; o >>= 1) {
+      mn = fmin(mn, __shfl_xor_sync(0xffffffffu, mn, o));
+      mx = fmax(mx, __shfl_xor_sync(0xffffffffu, mx, o));
+    }
+    const double eps = 1.4901161193847656e-08;  // SQRT(EPSILON(1d0)), weight.f90:17
+#pragma unroll
+    for (int u = 0; u < KL; ++u) {
+      if (mx < eps) w[u] = 1.0;                                  // :22-24
+      else if (mn < eps) w[u] = dist[u] < eps ? 1.0 : 0.0;        // :25-28
+      else w[u] = __ddiv_rn(1.0, __dmul_rn(dist[u], dist[u]));   // :29-31
+    }
+    // SUM(WTS) in index order (:34): serial over k through shuffles
+    double s = 0.0;
+#pragma unroll
+    for (int u = 0; u < KL; ++u) {
+      const int lim = min(32, k - 32 * u);
+      for (int l = 0; l < lim; ++l) s = __dadd_rn(s, __shfl_sync(0xffffffffu, w[u], l));
+    }
+#pragma unroll
+    for (int u = 0; u < KL; ++u) w[u] = __ddiv_rn(w[u], s);
+  }
+  if (wts) {
+#pragma unroll
+    for (int u = 0; u < KL; ++u) {
+      const int i = lane + 32 * u;
+      if (i < k) wts[p * k + i] = w[u];
+    }
+  }
+  if (lane == 0) {
+    if (cnt) cnt[p] = k;
+    if (err) err[p] = 0;
+  }
+  if (out) {
+    for (int c = 0; c < r; ++c) {
+      double yv[KL];
+#pragma unroll
+      for (int u = 0; u < KL; ++u) yv[u] = nb[u] >= 0 ? __dmul_rn(y[(int64_t)nb[u] * r + c], w[u]) : 0.0;
+      double s = 0.0;  // base.py:169: left to right from 0
+#pragma unroll
+      for (int u = 0; u < KL; ++u) {
+        const int lim = min(32, k - 32 * u);
+        for (int l = 0; l < lim; ++l) s = __dadd_rn(s, __shfl_sync(0xffffffffu, yv[u], l));
+      }
+      if (lane == 0) out[p * r + c] = s;
+    }
+  }
+}
+
+// Voronoi weights on the k neighbours: one block per query.  Shared memory holds
+// the k rows, their Gram matrix G (the reference's DOTS cache, voronoi.f90:105-129),
+// p.x_i and the per-centre maximum ratio.  Evaluated in the closed form the
+// sorted / SKIP / CYCLE control flow prunes towards:
+//   w_c = max(0, 1 - max_o max(0, num/den)),
+//   num = (p.x_o + x_c.x_c) - (p.x_c + x_c.x_o), den = x_o.x_o + x_c.x_c - 2 x_c.x_o
+// with the operand grouping of voronoi.f90:131-134.  ERROR=2 is raised when any
+// pair among the k neighbours has |den| <= sqrt(eps) (:137,145-148).
+__global__ void __launch_bounds__(128)
+voronoi_kernel(const double* __restrict__ x, int d, const double* __restrict__ z, int64_t q, int k,
+               const int32_t* __restrict__ idx, const double* __restrict__ y, int r,
+               double* __restrict__ wts, int32_t* __restrict__ cnt, int32_t* __restrict__ err,
+               double* __restrict__ out, int32_t* __restrict__ ids_out) {
+  extern __shared__ double sm[];
+  const int dp = d | 1;                 // odd row stride: conflict-free column walks
+  double* P = sm;                       // [k][dp]
+  double* G = P + (size_t)k * dp;       // [k][k+1]
+  double* pdot = G + (size_t)k * (k + 1);
+  double* w = pdot + k;
+  double* pts = w + k;                  // [d] query
+  __shared__ int s_err;
+  __shared__ int s_cnt;
+  const int64_t p = blockIdx.x;
+  const int t = threadIdx.x, nt = blockDim.x;
+  const int32_t* id = idx + p * k;
+  if (t == 0) { s_err = 0; s_cnt = 0; }
+  for (int j = t; j < d; j += nt) pts[j] = z[p * d + j];
+  for (int e = t; e < k * d; e += nt) {
+    const int i = e / d, j = e - i * d;
+    P[(size_t)i * dp + j] = x[(int64_t)id[i] * d + j];
+  }
+  __syncthreads();
+  const double HUGEV = 1.7976931348623157e308;
+  for (int e = t; e < k * (k + 1) / 2 + k; e += nt) {
+    if (e < k) {  // p . x_i  (SUM(EVAL_PT * POINTS(:,I)), :131)
+      double s = 0.0;
+      for (int j = 0; j < d; ++j) s = __dadd_rn(s, __dmul_rn(pts[j], P[(size_t)e * dp + j]));
+      pdot[e] = s;
+      double dd = 0.0;  // :83-91 overflow check on the squared distance
+      for (int j = 0; j < d; ++j) {
+        double df = __dsub_rn(pts[j], P[(size_t)e * dp + j]);
+        dd = __dadd_rn(dd, __dmul_rn(df, df));
+      }
+      if (dd > HUGEV) atomicMax(&s_err, 1);
+    } else {
+      // unrank e-k -> (a<=b) over the upper triangle
+      int f = e - k, a = 0;
+      while (f >= k - a) { f -= k - a; ++a; }
+      const int b = a + f;
+      double s = 0.0;
+      for (int j = 0; j < d; ++j) s = __dadd_rn(s, __dmul_rn(P[(size_t)a * dp + j], P[(size_t)b * dp + j]));
+      G[(size_t)a * (k + 1) + b] = s;
+      G[(size_t)b * (k + 1) + a] = s;
+      if (s > HUGEV) atomicMax(&s_err, 1);
+    }
+  }
+  __syncthreads();
+  const double MINV = 1.4901161193847656e-08;
+  for (int c = t; c < k; c += nt) {
+    double mr = 0.0;
+    const double gcc = G[(size_t)c * (k + 1) + c], pc = pdot[c];
+    for (int o = 0; o < k; ++o) {
+      if (o == c) continue;
+      const double gco = G[(size_t)c * (k + 1) + o];
+      const double num = __dsub_rn(__dadd_rn(pdot[o], gcc), __dadd_rn(pc, gco));                 // :131-132
+      const double den = __dsub_rn(__dadd_rn(G[(size_t)o * (k + 1) + o], gcc), __dmul_rn(2.0, gco));  // :134
+      if (fabs(den) > MINV) {
+        const double ratio = __ddiv_rn(num, den);
+        if (ratio > mr) mr = ratio;
+      } else {
+        atomicMax(&s_err, 2);
+      }
+    }
+    w[c] = fmax(__dsub_rn(1.0, mr), 0.0);  // :151
+  }
+  __syncthreads();
+  if (t == 0) {
+    const int e = s_err;
+    double s = 0.0;
+    for (int i = 0; i < k; ++i) s = __dadd_rn(s, w[i]);  // :154
+    int m = 0;
+    double acc[8];
+    const int rr = r < 8 ? r : 8;
+    for (int c = 0; c < rr; ++c) acc[c] = 0.0;
+    for (int i = 0; i < k; ++i) {
+      const double wi = __ddiv_rn(w[i], s);
+      if (e == 0 && wi > 0) {  // voronoi/__init__.py:58 support > 0
+        if (wts) wts[p * k + m] = wi;
+        if (ids_out) ids_out[p * k + m] = id[i];
+        if (out)
+          for (int c = 0; c < rr; ++c) acc[c] = __dadd_rn(acc[c], __dmul_rn(y[(int64_t)id[i] * r + c], wi));
+        ++m;
+      }
+    }
+    for (int i = m; i < k; ++i) {
+      if (wts) wts[p * k + i] = 0.0;
+      if (ids_out) ids_out[p * k + i] = -1;
+    }
+    if (out)
+      for (int c = 0; c < rr; ++c) out[p * r + c] = acc[c];
+    if (cnt) cnt[p] = m;
+    if (err) err[p] = e;
+  }
+}
+
+// Remaining response columns (r > 8) for Voronoi: plain weighted sums from ids/wts.
+__global__ void wsum_kernel(const int32_t* __restrict__ ids, const double* __restrict__ wts,
+                            const int32_t* __restrict__ cnt, int64_t q, int stride,
+                            const double* __restrict__ y, int r, int c0, double* __restrict__ out) {
+  const int64_t e = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
+  const int rc = r - c0;
+  if (e >= q * rc) return;
+  const int64_t p = e / rc;
+  const int c = c0 + (int)(e - p * rc);
+  double s = 0.0;
+  for (int i = 0; i < cnt[p]; ++i)
+    s = __dadd_rn(s, __dmul_rn(y[(int64_t)ids[p * stride + i] * r + c], wts[p * stride + i]));
+  out[p * r + c] = s;
+}
+
+}  // namespace
+
+// idx_dev (q,k) int32 neighbours, ascending distance.  For Voronoi the kept
+// neighbours' global ids are compacted in place into m->idx32-compatible layout
+// through ids_out = idx_dev is NOT done; callers read m->misc (q,k) instead.
+int nn_weights(b200_model* m, const double* z_dev, int64_t q, int k, int method,
+               const int32_t* idx_dev, const double* y_dev, int r, double* wts_dev,
+               int32_t* cnt_dev, int32_t* err_dev, double* out_dev, cudaStream_t st) {
+  if (q == 0) return 0;
+  if (method == B200_AVERAGE || method == B200_SHEPARD) {
+    if (k > 128) {
+      set_error("nn_weights: k=%d > 128 unsupported for Average/Shepard weighting", k);
+      return 1;
+    }
+    const int64_t threads = q * 32;
+    avg_shepard_kernel<<<(unsigned)((threads + 255) / 256), 256, 0, st>>>(
+        m->x, m->d, z_dev, q, k, method, idx_dev, y_dev, r, wts_dev, cnt_dev, err_dev,
+        y_dev ? out_dev : nullptr);
+    B200_CUDA(cudaGetLastError());
+    m->st.launches += 1;
+    return 0;
+  }
+  if (method == B200_VORONOI) {
+    const int d = m->d;
+    const size_t smem = ((size_t)k * (d | 1) + (size_t)k * (k + 1) + 2 * (size_t)k + d) * 8;
+    if (smem > 200 * 1024) {
+      set_error("nn_weights: Voronoi on k=%d neighbours in %d-D needs %zu B shared memory", k, d, smem);
+      return 1;
+    }
+    B200_TRY(m->misc.reserve((size_t)q * k * sizeof(int32_t)));
+    B200_TRY(m->wts.reserve((size_t)q * k * sizeof(double)));
+    B200_TRY(m->cnt.reserve((size_t)q * sizeof(int32_t)));
+    double* wbuf = wts_dev ? wts_dev : m->wts.as<double>();
+    int32_t* cbuf = cnt_dev ? cnt_dev : m->cnt.as<int32_t>();
+    B200_CUDA(cudaFuncSetAttribute(voronoi_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+    voronoi_kernel<<<(unsigned)q, 128, smem, st>>>(m->x, d, z_dev, q, k, idx_dev, y_dev, r, wbuf, cbuf,
+                                                   err_dev, y_dev ? out_dev : nullptr,
+                                                   m->misc.as<int32_t>());
+    B200_CUDA(cudaGetLastError());
+    m->st.launches += 1;
+    if (y_dev && out_dev && r > 8) {
+      const int64_t tot = q * (r - 8);
+      wsum_kernel<<<(unsigned)((tot + 255) / 256), 256, 0, st>>>(m->misc.as<int32_t>(), wbuf, cbuf, q, k,
+                                                                  y_dev, r, 8, out_dev);
+      B200_CUDA(cudaGetLastError());
+      m->st.launches += 1;
+    }
+    return 0;
+  }
+  set_error("nn_weights: unknown method %d", method);
+  return 1;
+}
+
+}  // namespace b200
