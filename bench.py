@@ -1,0 +1,334 @@
+#!/usr/bin/env python
+"""bench.py -- query points/sec of the kNN + Shepard predict hot path.
+
+    python bench.py --gpus N --steps K --warmup W            # this repo's CUDA path
+    python bench.py --impl reference --gpus N --steps K ...  # the reference's CPU algorithm (oracle port)
+
+Workload (BASELINE.json configs[4], SURVEY.md 8d "C5"): X 1,000,000 x 64 uniform
+[0,1) (seed 0), Z 1,000,000 x 64 (seed 1), k = 16, NearestNeighbor(method=Shepard),
+y = 3x0 + .5cos(8x0) + sin(5x_{d-1}).  One step = one pass of the hot path over
+the whole query batch.  `value` is timed on the device with the inputs resident
+in HBM; `e2e` goes through the host-buffer C-ABI call (pinned host memory in,
+host results out, copies inside the timed region).  For N > 1 the data set is
+sharded over the ranks (local top-k, NCCL all-to-all of the partial lists,
+on-device merge): total work is fixed, so scaling is "strong".
+"""
+import argparse
+import ctypes as C
+import json
+import os
+import subprocess
+import sys
+import threading
+import time
+
+import numpy as np
+
+ROOT = os.path.dirname(os.path.abspath(__file__))
+if ROOT not in sys.path:
+    sys.path.insert(0, ROOT)
+
+CONFIGS = {
+    # name: (n, q, d, k)
+    "c5": (1_000_000, 1_000_000, 64, 16),
+    "c5small": (200_000, 100_000, 64, 16),
+    "c1": (10_000, 1_000, 8, 1),
+}
+
+
+def fun(x):
+    return 3 * x[:, 0] + .5 * np.cos(8 * x[:, 0]) + np.sin(5 * x[:, -1])
+
+
+def peaks():
+    p = os.path.join(ROOT, "MEASURED_PEAKS.json")
+    if os.path.exists(p):
+        j = json.load(open(p))
+        return dict(tensor=float(j["bf16_tflops_sustained"]), tensor_burst=float(j["bf16_tflops"]),
+                    hbm=float(j["hbm_gbs"]), src="measured")
+    return dict(tensor=1400.0, tensor_burst=1590.0, hbm=6650.0, src="fallback")
+
+
+class ClockSampler(threading.Thread):
+    """nvidia-smi clocks / throttle reasons during the timed region (B200_PROFILING.md)."""
+    Q = ("clocks.sm,clocks.max.sm,clocks_event_reasons.hw_slowdown,clocks_event_reasons.hw_thermal_slowdown,"
+         "clocks_event_reasons.sw_thermal_slowdown,clocks_event_reasons.sw_power_cap")
+
+    def __init__(self, index):
+        super().__init__(daemon=True)
+        self.index, self.rows, self.stop_flag = index, [], False
+
+    def run(self):
+        while not self.stop_flag:
+            try:
+                out = subprocess.run(["nvidia-smi", "-i", str(self.index), "--query-gpu=" + self.Q,
+                                      "--format=csv,noheader,nounits"], capture_output=True, text=True, timeout=5).stdout
+                self.rows.append([c.strip() for c in out.strip().split(",")])
+            except Exception:
+                pass
+            time.sleep(0.2)
+
+    def summary(self):
+        sm = [float(r[0]) for r in self.rows if len(r) >= 6 and r[0].replace(".", "").isdigit()]
+        mx = [float(r[1]) for r in self.rows if len(r) >= 6 and r[1].replace(".", "").isdigit()]
+        names = ["hw_slowdown", "hw_thermal_slowdown", "sw_thermal_slowdown", "sw_power_cap"]
+        reasons = [n for i, n in enumerate(names) if any(len(r) >= 6 and r[2 + i].lower() == "active" for r in self.rows)]
+        return {"sm_mhz": float(np.median(sm)) if sm else None, "sm_max_mhz": max(mx) if mx else None,
+                "reasons": reasons, "samples": len(sm)}
+
+
+def cpu_port(x, y, z, k, seconds=15.0, threads=None):
+    """The oracle (CPU restatement of the reference algorithm) on a bounded query sample."""
+    from oracle import harness as H
+    cores = threads or os.cpu_count() or 1
+    H.set_threads(cores)
+    probe = z[:max(2, cores)]
+    t0 = time.perf_counter()
+    H.nn_predict(x, probe, k, "shepard")
+    per = (time.perf_counter() - t0) / len(probe)
+    s = int(max(cores, min(len(z), seconds / max(per, 1e-9))))
+    s = max(1, min(s, len(z)))
+    t0 = time.perf_counter()
+    ids, w, cnt, _ = H.nn_predict(x, z[:s], k, "shepard")
+    out = H.weighted_sum(ids, w, cnt, y)
+    dt = time.perf_counter() - t0
+    return s / dt, s, dt, cores, (ids, out)
+
+
+def run_reference(args, n, q, d, k):
+    rank = int(os.environ.get("RANK", "0"))
+    if rank != 0:
+        return
+    x = np.random.default_rng(0).random((n, d))
+    z = np.random.default_rng(1).random((q, d))
+    y = fun(x)
+    from oracle import harness as H
+    cores = os.cpu_count() or 1
+    H.set_threads(cores)
+    # size one step at ~ (120 s budget) / (steps + warmup)
+    probe = z[:max(2, cores)]
+    t0 = time.perf_counter()
+    H.nn_predict(x, probe, k, "shepard")
+    per = (time.perf_counter() - t0) / len(probe)
+    budget = 120.0 / (args.steps + args.warmup)
+    s = int(max(cores, min(q, budget / max(per, 1e-9))))
+    for _ in range(args.warmup):
+        H.nn_predict(x, z[:s], k, "shepard")
+    t0 = time.perf_counter()
+    for i in range(args.steps):
+        ids, w, cnt, _ = H.nn_predict(x, z[:s], k, "shepard")
+        H.weighted_sum(ids, w, cnt, y)
+    dt = (time.perf_counter() - t0) / args.steps
+    val = s / dt
+    line = {"impl": "reference", "metric": "query points/sec (kNN+Shepard predict)", "value": val,
+            "unit": "queries/s", "n_gpus": args.gpus, "steps": args.steps, "warmup": args.warmup,
+            "ms_per_step": dt * 1e3, "higher_is_better": True, "scaling": "strong", "vs_baseline": None,
+            "dtype": "f64", "data": "synthetic",
+            "config": {"workload": f"NearestNeighbor(k={k}, method=Shepard) predict, {n}x{d} data, {q} queries",
+                       "n": n, "q": q, "d": d, "k": k},
+            "cpu_baseline": {"value": val, "unit": "queries/s", "cores": cores, "kind": "port",
+                             "sample": f"{s} of {q} queries per step against all {n} points, OpenMP over queries"},
+            "e2e": {"value": val, "unit": "queries/s", "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0}}
+    print(json.dumps(line), flush=True)
+
+
+def main():
+    ap = argparse.ArgumentParser()
+    ap.add_argument("--gpus", type=int, default=1)
+    ap.add_argument("--steps", type=int, default=5)
+    ap.add_argument("--warmup", type=int, default=3)
+    ap.add_argument("--impl", default="ours")
+    ap.add_argument("--config", default="c5")
+    ap.add_argument("--shard", default="data", choices=["data", "query"])
+    ap.add_argument("--cpu-seconds", type=float, default=15.0)
+    ap.add_argument("--no-cpu", action="store_true")
+    ap.add_argument("--path", type=int, default=0, help="0 auto, 1 exact, 2 tensor")
+    ap.add_argument("--margin", type=int, default=-1)
+    args = ap.parse_args()
+    n, q, d, k = CONFIGS[args.config]
+    if args.warmup < 3:
+        args.warmup = 3
+
+    if args.impl == "reference":
+        return run_reference(args, n, q, d, k)
+
+    import torch
+    import torch.distributed as dist
+    from util_b200 import _lib
+    lib = _lib.lib()
+    rank = int(os.environ.get("RANK", "0"))
+    world = int(os.environ.get("WORLD_SIZE", "1"))
+    local = int(os.environ.get("LOCAL_RANK", "0"))
+    torch.cuda.set_device(local)
+    dev = torch.device("cuda", local)
+    if world > 1:
+        dist.init_process_group("nccl", device_id=dev)
+    G = world
+
+    x = np.random.default_rng(0).random((n, d))
+    z = np.random.default_rng(1).random((q, d))
+    y = fun(x)
+
+    # ---- data layout: rank r owns rows [lo, hi) of the fitted points (all of them when G == 1
+    # or when sharding queries); queries are padded to a multiple of G for the all-to-all.
+    if G > 1 and args.shard == "data":
+        per = (n + G - 1) // G
+        lo, hi = rank * per, min(n, (rank + 1) * per)
+    else:
+        lo, hi = 0, n
+    model = _lib.Model(x[lo:hi], device=local)
+    model.set_option("knn_path", args.path)
+    model.set_option("margin", args.margin)
+    h = model.handle
+    if G > 1 and args.shard == "query":
+        qs = (q + G - 1) // G
+        zl = z[rank * qs:min(q, (rank + 1) * qs)]
+    else:
+        zl = z
+    ql = zl.shape[0]
+    z_pin = torch.from_numpy(zl).pin_memory()
+    z_dev = z_pin.to(dev, non_blocking=False)
+    y_dev = torch.from_numpy(y).to(dev)
+    idx = torch.empty((ql, k), dtype=torch.int32, device=dev)
+    d2 = torch.empty((ql, k), dtype=torch.float64, device=dev)
+    data_sharded = G > 1 and args.shard == "data"
+    if data_sharded:
+        assert q % G == 0, "query count must divide by the number of ranks"
+        qm = q // G
+        rd2 = torch.empty((G, qm, k), dtype=torch.float64, device=dev)
+        ridx = torch.empty((G, qm, k), dtype=torch.int32, device=dev)
+        md2 = torch.empty((qm, k), dtype=torch.float64, device=dev)
+        midx = torch.empty((qm, k), dtype=torch.int32, device=dev)
+        out = torch.empty((qm,), dtype=torch.float64, device=dev)
+    else:
+        out = torch.empty((ql,), dtype=torch.float64, device=dev)
+    stream = torch.cuda.current_stream().cuda_stream
+
+    def step_device():
+        _lib.check(lib.b200_knn_dev(h, z_dev.data_ptr(), ql, k, -1, idx.data_ptr(), d2.data_ptr(), stream))
+        if data_sharded:
+            idx.add_(lo)  # local -> global row ids
+            dist.all_to_all_single(rd2.view(-1), d2.view(-1))
+            dist.all_to_all_single(ridx.view(-1), idx.view(-1))
+            _lib.check(lib.b200_merge_topk_dev(local, rd2.data_ptr(), ridx.data_ptr(), G, qm, k,
+                                               md2.data_ptr(), midx.data_ptr(), stream))
+            _lib.check(lib.b200_nn_weights_dev(h, None, qm, k, _lib.SHEPARD, midx.data_ptr(), md2.data_ptr(),
+                                               y_dev.data_ptr(), 1, None, None, None, out.data_ptr(), stream))
+        else:
+            _lib.check(lib.b200_nn_weights_dev(h, None, ql, k, _lib.SHEPARD, idx.data_ptr(), d2.data_ptr(),
+                                               y_dev.data_ptr(), 1, None, None, None, out.data_ptr(), stream))
+
+    def sync_all():
+        torch.cuda.synchronize()
+        if G > 1:
+            dist.barrier()
+            torch.cuda.synchronize()
+
+    for _ in range(args.warmup):
+        step_device()
+    sync_all()
+    model.set_option("reset_stats", 1)
+    sampler = ClockSampler(local)
+    if rank == 0:
+        sampler.start()
+    e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    e0.record()
+    for _ in range(args.steps):
+        step_device()
+    e1.record()
+    sync_all()
+    ms = e0.elapsed_time(e1) / args.steps
+    stats = {s: model.stat(s) / args.steps for s in
+             ("ms_prep", "ms_stage1", "ms_rerank", "ms_exact", "launches", "uncertified")}
+    if G > 1:
+        t = torch.tensor([ms], device=dev)
+        dist.all_reduce(t, op=dist.ReduceOp.MAX)
+        ms = float(t.item())
+    value = q / (ms * 1e-3) if not (G > 1 and args.shard == "query") else q / (ms * 1e-3)
+
+    # ---- end to end through the host-buffer C-ABI (pinned inputs, host outputs, copies timed)
+    e2e = None
+    h2d = d2h = 0
+    if not data_sharded:
+        zp = z_pin.numpy()
+        for _ in range(2):
+            model.nn_predict(zp, k, _lib.SHEPARD, y=y, want_weights=False)
+        sync_all()
+        t0 = time.perf_counter()
+        for _ in range(args.steps):
+            res = model.nn_predict(zp, k, _lib.SHEPARD, y=y, want_weights=False)
+        torch.cuda.synchronize()
+        dt = (time.perf_counter() - t0) / args.steps
+        h2d = zp.nbytes + y.nbytes
+        d2h = ql * 8 + ql * 4 * 2
+    else:
+        # host queries -> every rank (each needs all of them), host <- this rank's slice of predictions
+        out_host = torch.empty((qm,), dtype=torch.float64).pin_memory()
+
+        def step_e2e():
+            z_dev.copy_(z_pin, non_blocking=True)
+            step_device()
+            out_host.copy_(out, non_blocking=True)
+            torch.cuda.synchronize()
+        for _ in range(2):
+            step_e2e()
+        sync_all()
+        t0 = time.perf_counter()
+        for _ in range(args.steps):
+            step_e2e()
+        dt = (time.perf_counter() - t0) / args.steps
+        h2d = z_pin.numel() * 8
+        d2h = qm * 8
+    if G > 1:
+        t = torch.tensor([dt], device=dev)
+        dist.all_reduce(t, op=dist.ReduceOp.MAX)
+        dt = float(t.item())
+    e2e = {"value": q / dt, "unit": "queries/s", "h2d_bytes_per_step": int(h2d), "d2h_bytes_per_step": int(d2h),
+           "ms_per_step": dt * 1e3}
+    sampler.stop_flag = True
+
+    if rank == 0:
+        pk = peaks()
+        nloc = hi - lo
+        flops = 2.0 * ql * nloc * d  # algorithmic: the -2 Z X^T term only
+        s1 = stats["ms_stage1"]
+        tensor_path = s1 > 0
+        if tensor_path:
+            ach = flops / (s1 * 1e-3) / 1e12
+            roof = {"bound": "tensor", "kernel": "knn_tc_kernel", "achieved": ach, "peak": pk["tensor"],
+                    "unit": "TFLOP/s", "frac": ach / pk["tensor"], "traffic": None,
+                    "peak_source": pk["src"] + " bf16_tflops_sustained", "ms_per_launch": s1,
+                    "algorithmic_flops_per_launch": flops}
+        else:
+            ach = flops / (stats["ms_exact"] * 1e-3) / 1e12 if stats["ms_exact"] else 0.0
+            roof = {"bound": "tensor", "kernel": "knn_exact_kernel (fp64 CUDA cores)", "achieved": ach,
+                    "peak": pk["tensor"], "unit": "TFLOP/s", "frac": ach / pk["tensor"], "traffic": None,
+                    "peak_source": pk["src"]}
+        line = {"metric": "query points/sec (kNN+Shepard predict)", "value": value, "unit": "queries/s",
+                "n_gpus": G, "steps": args.steps, "warmup": args.warmup, "ms_per_step": ms,
+                "higher_is_better": True, "scaling": "strong", "vs_baseline": None, "dtype": "f16 filter + f64 re-rank",
+                "data": "synthetic",
+                "config": {"workload": f"NearestNeighbor(k={k}, method=Shepard) predict, {n}x{d} data, {q} queries",
+                           "n": n, "q": q, "d": d, "k": k, "parallelism": (f"{args.shard}-shard x{G}" if G > 1 else "single"),
+                           "l2": "inputs larger than L2 (queries %d MB, operand images %d MB)" % (zl.nbytes >> 20, (nloc * 80 * 2) >> 20)},
+                "roofline": roof,
+                "stages_ms": {kk: vv for kk, vv in stats.items() if kk.startswith("ms_")},
+                "uncertified_per_step": stats["uncertified"],
+                "gpu_launches": int(round(stats["launches"] * args.steps)),
+                "e2e": e2e, "clocks": sampler.summary()}
+        if G == 1 and not args.no_cpu:
+            v, s, dtc, cores, (cids, cout) = cpu_port(x, y, z, k, seconds=args.cpu_seconds)
+            line["cpu_baseline"] = {"value": v, "unit": "queries/s", "cores": cores, "kind": "port",
+                                    "sample": f"first {s} of {q} queries against all {n} points in {dtc:.1f} s, OpenMP over queries"}
+            # the timed GPU outputs must agree with the CPU sample: indices bit-exact, values 1e-12
+            gi = idx[:s].cpu().numpy().astype(np.int64)
+            go = out[:s].cpu().numpy()
+            line["parity_on_sample"] = {"indices_equal": bool(np.array_equal(gi, cids)),
+                                        "max_rel_err": float(np.max(np.abs(go - cout) / np.maximum(np.abs(cout), 1e-3)))}
+        print(json.dumps(line), flush=True)
+    if G > 1:
+        dist.destroy_process_group()
+
+
+if __name__ == "__main__":
+    main()

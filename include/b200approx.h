@@ -94,8 +94,9 @@ int b200_lshep_predict(b200_model* m, double radius, const double* z, int64_t q,
 int b200_knn_dev(b200_model* m, const double* z_dev, int64_t q, int32_t k, int64_t self_offset,
                  int32_t* idx_dev, double* d2_dev, void* stream);
 int b200_nn_weights_dev(b200_model* m, const double* z_dev, int64_t q, int32_t k, int32_t method,
-                        const int32_t* idx_dev, const double* y_dev, int32_t r, double* wts_dev,
-                        int32_t* cnt_dev, int32_t* err_dev, double* out_dev, void* stream);
+                        const int32_t* idx_dev, const double* d2_dev, const double* y_dev, int32_t r,
+                        double* wts_dev, int32_t* cnt_dev, int32_t* err_dev, double* out_dev,
+                        void* stream);
 /* Data-sharded kNN merge: `parts` lists of (q,k) sorted (d2, global idx) -> the k
  * best per query by (d2, idx).  d2_parts/idx_parts are (parts,q,k) contiguous. */
 int b200_merge_topk_dev(int32_t device, const double* d2_parts, const int32_t* idx_parts,

@@ -152,6 +152,7 @@ int b200_create(const double* x, int64_t n, int32_t d, int32_t device, b200_mode
   B200_CUDA(cudaEventCreate(&m->ev0));
   B200_CUDA(cudaEventCreate(&m->ev1));
   B200_CUDA(cudaEventCreate(&m->ev2));
+  B200_CUDA(cudaEventCreate(&m->ev3));
   *out = m;
   return 0;
 }
@@ -168,6 +169,7 @@ int b200_destroy(b200_model* m) {
   if (m->ev0) cudaEventDestroy(m->ev0);
   if (m->ev1) cudaEventDestroy(m->ev1);
   if (m->ev2) cudaEventDestroy(m->ev2);
+  if (m->ev3) cudaEventDestroy(m->ev3);
   delete m;
   return 0;
 }
@@ -191,6 +193,7 @@ int b200_get_stat(b200_model* m, const char* key, double* value) {
   if (!strcmp(key, "uncertified")) *value = s.uncertified;
   else if (!strcmp(key, "ms_stage1")) *value = s.ms_stage1;
   else if (!strcmp(key, "ms_rerank")) *value = s.ms_rerank;
+  else if (!strcmp(key, "ms_prep")) *value = s.ms_prep;
   else if (!strcmp(key, "ms_weights")) *value = s.ms_weights;
   else if (!strcmp(key, "ms_exact")) *value = s.ms_exact;
   else if (!strcmp(key, "launches")) *value = s.launches;
@@ -247,7 +250,7 @@ int b200_nn_predict(b200_model* m, const double* z, int64_t q, int32_t k, int32_
   B200_TRY(knn_dispatch(m, m->zq.as<double>(), q, k, -1, m->idx32.as<int32_t>(), m->d2.as<double>(), 0));
   {
     Timer t(m, 0, &m->st.ms_weights);
-    B200_TRY(nn_weights(m, m->zq.as<double>(), q, k, method, m->idx32.as<int32_t>(),
+    B200_TRY(nn_weights(m, m->zq.as<double>(), q, k, method, m->idx32.as<int32_t>(), m->d2.as<double>(),
                         y ? m->y.as<double>() : nullptr, r, m->wts.as<double>(), m->cnt.as<int32_t>(),
                         m->err.as<int32_t>(), y ? m->out.as<double>() : nullptr, 0));
   }
@@ -276,10 +279,11 @@ int b200_knn_dev(b200_model* m, const double* z_dev, int64_t q, int32_t k, int64
 }
 
 int b200_nn_weights_dev(b200_model* m, const double* z_dev, int64_t q, int32_t k, int32_t method,
-                        const int32_t* idx_dev, const double* y_dev, int32_t r, double* wts_dev,
-                        int32_t* cnt_dev, int32_t* err_dev, double* out_dev, void* stream) {
+                        const int32_t* idx_dev, const double* d2_dev, const double* y_dev, int32_t r,
+                        double* wts_dev, int32_t* cnt_dev, int32_t* err_dev, double* out_dev,
+                        void* stream) {
   B200_TRY(use(m));
-  return nn_weights(m, z_dev, q, k, method, idx_dev, y_dev, r, wts_dev, cnt_dev, err_dev, out_dev,
+  return nn_weights(m, z_dev, q, k, method, idx_dev, d2_dev, y_dev, r, wts_dev, cnt_dev, err_dev, out_dev,
                     (cudaStream_t)stream);
 }
 

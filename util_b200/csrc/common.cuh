@@ -72,7 +72,7 @@ struct TcData {
 
 struct Stats {
   double uncertified = 0, ms_stage1 = 0, ms_rerank = 0, ms_weights = 0, ms_exact = 0,
-         launches = 0, tc_queries = 0, exact_queries = 0, last_cap = 0;
+         launches = 0, tc_queries = 0, exact_queries = 0, last_cap = 0, ms_prep = 0;
 };
 
 }  // namespace b200
@@ -98,7 +98,7 @@ struct b200_model {
   int margin = -1;  // extra candidates kept by the tensor filter (-1: = k)
   int64_t rows_per_call = 1 << 20;
   b200::Stats st;
-  cudaEvent_t ev0 = nullptr, ev1 = nullptr, ev2 = nullptr;
+  cudaEvent_t ev0 = nullptr, ev1 = nullptr, ev2 = nullptr, ev3 = nullptr;
   float* dbg_scores = nullptr;  // tests only: raw tensor-path scores are dumped here
 };
 
@@ -119,8 +119,8 @@ int knn_tc(b200_model* m, const double* z_dev, int64_t q, int k, int64_t self_of
            int32_t* idx_dev, double* d2_dev, cudaStream_t st);
 // weights.cu
 int nn_weights(b200_model* m, const double* z_dev, int64_t q, int k, int method,
-               const int32_t* idx_dev, const double* y_dev, int r, double* wts_dev,
-               int32_t* cnt_dev, int32_t* err_dev, double* out_dev, cudaStream_t st);
+               const int32_t* idx_dev, const double* d2_dev, const double* y_dev, int r,
+               double* wts_dev, int32_t* cnt_dev, int32_t* err_dev, double* out_dev, cudaStream_t st);
 // shepmod.cu
 int shepmod_fit(b200_model* m, cudaStream_t st, int* ier);
 int shepmod_predict(b200_model* m, const double* z_dev, int64_t q, int cap, int32_t* ids_dev,

@@ -19,15 +19,17 @@ namespace b200 {
 namespace {
 
 // One warp per query; lane i owns neighbour i (+32, ...).  KL = ceil(k/32) <= 4.
+// Distances come from the kNN stage (d2 is bit-identical to the reference's
+// sum of squared differences), so no fitted row is read again here: per query
+// this stage moves k*(8+4+8) bytes in and k*8 (+8r) bytes out.
 __global__ void __launch_bounds__(256)
-avg_shepard_kernel(const double* __restrict__ x, int d, const double* __restrict__ z, int64_t q,
+avg_shepard_kernel(const double* __restrict__ d2, int64_t q,
                    int k, int method, const int32_t* __restrict__ idx,
                    const double* __restrict__ y, int r, double* __restrict__ wts,
                    int32_t* __restrict__ cnt, int32_t* __restrict__ err, double* __restrict__ out) {
   const int lane = threadIdx.x & 31;
   const int64_t p = ((int64_t)blockIdx.x * blockDim.x + threadIdx.x) >> 5;
   if (p >= q) return;
-  const double* pt = z + p * d;
   const int32_t* id = idx + p * k;
   constexpr int KL = 4;
   double w[KL];
@@ -49,7 +51,7 @@ avg_shepard_kernel(const double* __restrict__ x, int d, const double* __restrict
       nb[u] = i < k ? id[i] : -1;
       dist[u] = 0.0;
       if (i < k) {
-        dist[u] = sqrt(sqdist_seq(x + (int64_t)nb[u] * d, pt, d));  // weight.f90:13-15
+        dist[u] = sqrt(d2[p * k + i]);  // weight.f90:13-15 (the kNN stage's exact d2, same arithmetic)
         mn = fmin(mn, dist[u]);
         mx = fmax(mx, dist[u]);
       }
@@ -229,7 +231,7 @@ __global__ void wsum_kernel(const int32_t* __restrict__ ids, const double* __res
 // neighbours' global ids are compacted in place into m->idx32-compatible layout
 // through ids_out = idx_dev is NOT done; callers read m->misc (q,k) instead.
 int nn_weights(b200_model* m, const double* z_dev, int64_t q, int k, int method,
-               const int32_t* idx_dev, const double* y_dev, int r, double* wts_dev,
+               const int32_t* idx_dev, const double* d2_dev, const double* y_dev, int r, double* wts_dev,
                int32_t* cnt_dev, int32_t* err_dev, double* out_dev, cudaStream_t st) {
   if (q == 0) return 0;
   if (method == B200_AVERAGE || method == B200_SHEPARD) {
@@ -238,8 +240,12 @@ int nn_weights(b200_model* m, const double* z_dev, int64_t q, int k, int method,
       return 1;
     }
     const int64_t threads = q * 32;
+    if (method == B200_SHEPARD && !d2_dev) {
+      set_error("nn_weights: Shepard weighting needs the kNN squared distances");
+      return 1;
+    }
     avg_shepard_kernel<<<(unsigned)((threads + 255) / 256), 256, 0, st>>>(
-        m->x, m->d, z_dev, q, k, method, idx_dev, y_dev, r, wts_dev, cnt_dev, err_dev,
+        d2_dev, q, k, method, idx_dev, y_dev, r, wts_dev, cnt_dev, err_dev,
         y_dev ? out_dev : nullptr);
     B200_CUDA(cudaGetLastError());
     m->st.launches += 1;
