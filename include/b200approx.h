@@ -103,6 +103,24 @@ int b200_merge_topk_dev(int32_t device, const double* d2_parts, const int32_t* i
                         int32_t parts, int64_t q, int32_t k, double* d2_out, int32_t* idx_out,
                         void* stream);
 
+/* Exact kNN that allocates nothing.  It has no counterpart in the reference, which owns
+ * no device memory.  Meant for callers that cannot let a library allocate while they
+ * run: serving loops for which the implicit device-wide synchronisation of
+ * cudaMalloc/cudaFree is a stall, and processes whose device memory is already handed
+ * out in full (a pool, another framework) or audited, where a late cudaMalloc fails.  All pointers are device pointers on the CURRENT device (the
+ * caller owns inputs and outputs): x_dev (n,d) fitted points, z_dev (q,d) queries,
+ * idx_dev (q,k) int32 and d2_dev (q,k) results, ordered by (d2, index) like b200_knn_dev.
+ * The partial top-k lists the split scan needs are kept in a 12 MiB array compiled into
+ * the library (present on every GPU that loads it until the process exits), which bounds
+ * the batch: q*k <= 262144 and k <= 128; larger requests are refused with an error, so
+ * split the query batch.  The first call on each device looks up that array's device
+ * address; make that first call outside any stream capture.  All calls share the array
+ * and nothing in it has to start at zero (every slot a call reads it has written first),
+ * but two calls whose kernels overlap on the GPU -- different streams or threads --
+ * race on it: serialise them. */
+int b200_knn_exact_noalloc(const double* x_dev, int64_t n, int32_t d, const double* z_dev,
+                           int64_t q, int32_t k, int32_t* idx_dev, double* d2_dev, void* stream);
+
 /* Test hook, no counterpart in the reference: run the tensor path on q <= 4096
  * queries and return the raw stage-1 scores (q, cols) with cols = 128*ceil(n/128),
  * score = s^2 * (||y_j - mu||^2 - 2 (z - mu).(y_j - mu)), s = stat "tc_scale". */

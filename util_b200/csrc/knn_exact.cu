@@ -253,3 +253,129 @@ int merge_topk(const double* d2_parts, const int32_t* idx_parts, int parts, int6
 }
 
 }  // namespace b200
+
+// ===========================================================================
+// Allocation-free exact kNN.
+//
+// Some callers must not trigger device allocation while they run: serving loops
+// with a latency budget, for which the implicit device-wide synchronisation of
+// cudaMalloc/cudaFree is a stall; and hosts whose device memory is already
+// handed out in full to a pool or another framework, where a late cudaMalloc
+// from a library can simply fail, or where every allocation is audited.
+// For them this entry point runs the same split-scan + merge kernels as
+// b200_knn_dev's exact path, but the partial top-k lists live in the file-scope
+// array below instead of a cudaMalloc'ed buffer.  Every GPU that loads the
+// library carries the array (12 MiB) until the process exits.  The first call
+// on a device looks up the array's device address (do that first call before
+// any stream capture begins).  Nothing in the array needs zeroing -- a call
+// writes every slot it later reads -- but all calls share it, so calls whose
+// kernels may overlap on the GPU race and must be serialised by the caller.
+// ===========================================================================
+namespace b200 {
+namespace {
+
+constexpr int64_t NA_MAX_ENTRIES = 1 << 20;  // partial (d2, idx) pairs: splits * q * k must fit
+// [0, 8 MiB): double d2 parts, [8 MiB, 12 MiB): int32 idx parts
+static __device__ __align__(256) unsigned char g_noalloc_scratch[NA_MAX_ENTRIES * 12];
+
+// Device address of g_noalloc_scratch per device.  In host code the symbol name is only a
+// handle: the address a kernel can use must be asked for, once per device, with that
+// device current.
+void* g_na_ptr[64] = {nullptr};
+
+int noalloc_scratch(void** out) {
+  int dev = 0;
+  B200_CUDA(cudaGetDevice(&dev));
+  if (dev < 0 || dev >= 64) {
+    set_error("b200_knn_exact_noalloc: device ordinal %d out of range", dev);
+    return 1;
+  }
+  if (!g_na_ptr[dev]) {
+    void* p = nullptr;
+    B200_CUDA(cudaGetSymbolAddress(&p, g_noalloc_scratch));
+    g_na_ptr[dev] = p;
+  }
+  *out = g_na_ptr[dev];
+  return 0;
+}
+
+template <int KMAX>
+int launch_noalloc(const double* x, int64_t n, int d, const double* z, int64_t q, int k,
+                   int32_t* idx, double* d2, cudaStream_t st) {
+  void* scratch = nullptr;
+  B200_TRY(noalloc_scratch(&scratch));
+  int sms = 148, dev = 0;
+  B200_CUDA(cudaGetDevice(&dev));
+  B200_CUDA(cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, dev));
+  const int QB = d <= 96 ? 128 : (d <= 256 ? 64 : 32);
+  const size_t zbytes = (size_t)d * QB * 8;
+  int tile_pts = (int)((160 * 1024 - zbytes) / ((size_t)d * 8));
+  if (tile_pts > 256) tile_pts = 256;
+  tile_pts &= ~3;
+  if (tile_pts < 4) {
+    set_error("b200_knn_exact_noalloc: dimension %d too large for the shared-memory tiling", d);
+    return 3;
+  }
+  const size_t smem = zbytes + (size_t)tile_pts * d * 8;
+  const int64_t qblocks = (q + QB - 1) / QB;
+  int64_t S = (2 * (int64_t)sms + qblocks - 1) / qblocks;               // aim at two waves of CTAs
+  S = std::min<int64_t>(S, (n + 4 * tile_pts - 1) / (4 * (int64_t)tile_pts));
+  S = std::min<int64_t>(S, NA_MAX_ENTRIES / (q * k));                    // what the static scratch holds
+  S = std::max<int64_t>(1, std::min<int64_t>(S, 512));
+  int64_t split_len = (n + S - 1) / S;
+  split_len = (split_len + 3) & ~(int64_t)3;
+  S = (n + split_len - 1) / split_len;
+  const int direct = (S == 1);
+  double* pd2 = reinterpret_cast<double*>(scratch);
+  int32_t* pidx = reinterpret_cast<int32_t*>(reinterpret_cast<unsigned char*>(scratch) + NA_MAX_ENTRIES * 8);
+  dim3 grid((unsigned)qblocks, (unsigned)S);
+#define NA_LAUNCH(QBV)                                                                             \
+  do {                                                                                             \
+    auto kern = knn_exact_kernel<KMAX, QBV>;                                                       \
+    B200_CUDA(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem)); \
+    kern<<<grid, QBV, smem, st>>>(x, n, d, z, q, k, -1, nullptr, split_len, tile_pts,             \
+                                  direct ? idx : pidx, direct ? d2 : pd2, direct);                 \
+  } while (0)
+  if (QB == 128) NA_LAUNCH(128);
+  else if (QB == 64) NA_LAUNCH(64);
+  else NA_LAUNCH(32);
+#undef NA_LAUNCH
+  B200_CUDA(cudaGetLastError());
+  if (!direct) {
+    merge_topk_kernel<<<(unsigned)((q + 127) / 128), 128, 0, st>>>(pd2, pidx, (int)S, q, k, nullptr, d2, idx);
+    B200_CUDA(cudaGetLastError());
+  }
+  return 0;
+}
+
+}  // namespace
+}  // namespace b200
+
+extern "C" int b200_knn_exact_noalloc(const double* x_dev, int64_t n, int32_t d, const double* z_dev,
+                                      int64_t q, int32_t k, int32_t* idx_dev, double* d2_dev,
+                                      void* stream) {
+  using namespace b200;
+  if (!x_dev || !z_dev || !idx_dev || !d2_dev || n < 1 || d < 1 || q < 0) {
+    set_error("b200_knn_exact_noalloc: bad arguments");
+    return 1;
+  }
+  if (q == 0) return 0;
+  if (k < 1 || k > n || k > 128) {
+    set_error("b200_knn_exact_noalloc: k=%d must be in [1, min(n, 128)]", k);
+    return 1;
+  }
+  if (n > 0x7fffffffLL - 1024) {
+    set_error("b200_knn_exact_noalloc: n=%lld exceeds int32 row indices", (long long)n);
+    return 1;
+  }
+  if (q * (int64_t)k * 4 > NA_MAX_ENTRIES) {
+    set_error("b200_knn_exact_noalloc: q*k = %lld exceeds the static scratch limit of %lld "
+              "(four partial lists of q*k entries must fit in %lld); split the query batch",
+              (long long)(q * k), (long long)(NA_MAX_ENTRIES / 4), (long long)NA_MAX_ENTRIES);
+    return 1;
+  }
+  cudaStream_t st = (cudaStream_t)stream;
+  if (k <= 8) return launch_noalloc<8>(x_dev, n, d, z_dev, q, k, idx_dev, d2_dev, st);
+  if (k <= 32) return launch_noalloc<32>(x_dev, n, d, z_dev, q, k, idx_dev, d2_dev, st);
+  return launch_noalloc<128>(x_dev, n, d, z_dev, q, k, idx_dev, d2_dev, st);
+}
