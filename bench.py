@@ -144,6 +144,7 @@ def main():
     ap.add_argument("--no-cpu", action="store_true")
     ap.add_argument("--path", type=int, default=0, help="0 auto, 1 exact, 2 tensor")
     ap.add_argument("--margin", type=int, default=-1)
+    ap.add_argument("--tc-mode", type=int, default=0, help="debug ceilings: 1 TMEM reads only, 2 no epilogue")
     args = ap.parse_args()
     n, q, d, k = CONFIGS[args.config]
     if args.warmup < 3:
@@ -179,6 +180,7 @@ def main():
     model = _lib.Model(x[lo:hi], device=local)
     model.set_option("knn_path", args.path)
     model.set_option("margin", args.margin)
+    model.set_option("tc_mode", args.tc_mode)
     h = model.handle
     if G > 1 and args.shard == "query":
         qs = (q + G - 1) // G
@@ -314,6 +316,8 @@ def main():
                 "roofline": roof,
                 "stages_ms": {kk: vv for kk, vv in stats.items() if kk.startswith("ms_")},
                 "uncertified_per_step": stats["uncertified"],
+                "tc": {"cap": model.stat("tc_cap"), "keep": model.stat("tc_keep"), "slots": model.stat("tc_slots"),
+                       "K": model.stat("tc_K"), "mode": args.tc_mode},
                 "gpu_launches": int(round(stats["launches"] * args.steps)),
                 "e2e": e2e, "clocks": sampler.summary()}
         if G == 1 and not args.no_cpu:

@@ -178,6 +178,7 @@ int b200_set_option(b200_model* m, const char* key, double value) {
   B200_TRY(use(m));
   if (!strcmp(key, "knn_path")) m->knn_path = (int)value;
   else if (!strcmp(key, "margin")) m->margin = (int)value;
+  else if (!strcmp(key, "tc_mode")) m->tc_mode = (int)value;
   else if (!strcmp(key, "rows_per_call")) m->rows_per_call = (int64_t)value;
   else if (!strcmp(key, "reset_stats")) m->st = Stats();
   else {
@@ -203,6 +204,8 @@ int b200_get_stat(b200_model* m, const char* key, double* value) {
   else if (!strcmp(key, "tc_scale")) *value = m->tc.scale;
   else if (!strcmp(key, "tc_ymax")) *value = m->tc.ymax;
   else if (!strcmp(key, "tc_cap")) *value = s.last_cap;
+  else if (!strcmp(key, "tc_keep")) *value = s.last_keep;
+  else if (!strcmp(key, "tc_slots")) *value = s.last_slots;
   else if (!strcmp(key, "sm_count")) *value = m->sm_count;
   else {
     set_error("unknown stat '%s'", key);

@@ -72,7 +72,7 @@ struct TcData {
 
 struct Stats {
   double uncertified = 0, ms_stage1 = 0, ms_rerank = 0, ms_weights = 0, ms_exact = 0,
-         launches = 0, tc_queries = 0, exact_queries = 0, last_cap = 0, ms_prep = 0;
+         launches = 0, tc_queries = 0, exact_queries = 0, last_cap = 0, ms_prep = 0, last_keep = 0, last_slots = 0;
 };
 
 }  // namespace b200
@@ -95,7 +95,8 @@ struct b200_model {
       flags, misc, ids64;
   // options
   int knn_path = 0;
-  int margin = -1;  // extra candidates kept by the tensor filter (-1: = k)
+  int margin = -1;  // extra candidates kept by the tensor filter (-1: min(k, 16))
+  int tc_mode = 0;  // debug: 1/2 strip the epilogue to measure the MMA/TMA pipeline ceiling
   int64_t rows_per_call = 1 << 20;
   b200::Stats st;
   cudaEvent_t ev0 = nullptr, ev1 = nullptr, ev2 = nullptr, ev3 = nullptr;

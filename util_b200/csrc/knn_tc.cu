@@ -34,7 +34,8 @@ namespace b200 {
 
 namespace tc {
 
-constexpr int TILE = 128;          // rows per operand tile (queries per half, data points per tile)
+constexpr int TILE = 128;          // query rows per accumulator half = data columns per epilogue tile
+constexpr int SUBROWS = 64;        // data rows per operand sub-tile image (one bulk copy, one UMMA N)
 constexpr int NORM_SLOTS = 3;
 constexpr double U16 = 4.8828125e-4;             // 2^-11: fp16 unit roundoff
 constexpr double TINY16 = 2.98023223876953125e-8;  // 2^-25: half the smallest fp16 subnormal
@@ -84,9 +85,9 @@ __global__ void data_img_kernel(const double* __restrict__ x, int64_t n, int d, 
   const int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
   double nm = 0.0;
   if (i < npad) {
-    const int64_t t = i / TILE;
-    const int r = (int)(i - t * TILE);
-    uint4* dst = reinterpret_cast<uint4*>(img + (size_t)t * TILE * K);  // chunk c at dst[c*TILE + r]
+    const int64_t t = i / SUBROWS;
+    const int r = (int)(i - t * SUBROWS);
+    uint4* dst = reinterpret_cast<uint4*>(img + (size_t)t * SUBROWS * K);  // chunk c at dst[c*SUBROWS + r]
     const int KC = K / 8;
     double n2 = 0.0, n2h = 0.0;
     for (int c = 0; c < KC; ++c) {
@@ -118,7 +119,7 @@ __global__ void data_img_kernel(const double* __restrict__ x, int64_t n, int d, 
         }
         h[e] = __float2half_rn(hv);
       }
-      dst[(size_t)c * TILE + r] = *reinterpret_cast<uint4*>(h);
+      dst[(size_t)c * SUBROWS + r] = *reinterpret_cast<uint4*>(h);
     }
     nm = sqrt(fmax(n2, n2h));
   }
@@ -184,51 +185,80 @@ __global__ void query_img_kernel(const double* __restrict__ z, int64_t q, int d,
 // ------------------------------------------------------------------ main kernel
 struct KParams {
   const __half* a_img;   // query tile images  [qtiles][K/8][128][8]
-  const __half* b_img;   // data tile images   [ntiles][K/8][128][8]
+  const __half* b_img;   // data sub-tile images [2*ntiles][K/8][64][8]
   int K;                 // contraction length, multiple of 16
-  int ntiles;            // data tiles
+  int ntiles;            // 128-column data tiles (two 64-row sub-tiles each)
   int qblocks;           // query blocks of HALVES*128 rows
-  int stages;            // B pipeline depth
+  int slots;             // depth of the B ring, in 64-row sub-tiles
+  int keep;              // C: candidates a compaction keeps (<= CAP - 8)
+  int mode;              // 0 normal; debug ceilings: 1 = epilogue reads TMEM only, 2 = epilogue only releases
   int32_t* cand_idx;     // [qpad][CAP]
   int32_t* cand_cnt;     // [qpad]
   float* cand_tau;       // [qpad]
   float* dbg;            // optional [qpad][ntiles*128] raw scores (tests only)
 };
 
+constexpr int SUB = 64;  // data rows per B sub-tile (one TMA copy, one UMMA N)
+
 __device__ __forceinline__ float min3(float a, float b, float c) { return fminf(fminf(a, b), c); }
 
-// Trim row `r` of this warp (buffer column `col`) to its C best entries; returns the new
-// threshold (the C-th smallest score).  Warp-cooperative, all lanes must call.
-template <int CAP, int ROWS>
-__device__ __forceinline__ float compact_row(float2* buf, int col, int n_valid, int lane) {
-  constexpr int C = CAP / 2;
+// Trim buffer column `col` (one query row) to its `keep` best entries; returns the new
+// threshold (the keep-th smallest score).  Warp-cooperative, all lanes must call.
+// bsc/bid are [CAP][RS] (slot-major, RS = rows + 1 keeps slot walks conflict-free).
+template <int CAP>
+__device__ __noinline__ float compact_row(float* bsc, int* bid, int RS, int col, int n_valid, int keep,
+                                          int lane) {
   constexpr int U = CAP / 32;
   float sc[U];
-  int id[U], rank[U];
+  int id[U], rank[U], eq[U];
 #pragma unroll
   for (int u = 0; u < U; ++u) {
     const int j = lane + 32 * u;
-    float2 e = buf[(size_t)j * ROWS + col];
-    sc[u] = j < n_valid ? e.x : CUDART_INF_F;
-    id[u] = __float_as_int(e.y);
+    sc[u] = j < n_valid ? bsc[j * RS + col] : CUDART_INF_F;
+    id[u] = bid[j * RS + col];
     rank[u] = 0;
+    eq[u] = 0;
   }
-  for (int i = 0; i < n_valid; ++i) {
-    const float si = buf[(size_t)i * ROWS + col].x;  // broadcast read
+  const float* ps = bsc + col;
+  int i = 0;
+  for (; i + 4 <= n_valid; i += 4) {
+    const float s0 = ps[(i + 0) * RS], s1 = ps[(i + 1) * RS], s2 = ps[(i + 2) * RS], s3 = ps[(i + 3) * RS];
 #pragma unroll
     for (int u = 0; u < U; ++u) {
-      const int j = lane + 32 * u;
-      rank[u] += (si < sc[u] || (si == sc[u] && i < j)) ? 1 : 0;
+      rank[u] += (s0 < sc[u]) + (s1 < sc[u]) + (s2 < sc[u]) + (s3 < sc[u]);
+      eq[u] += (s0 == sc[u]) + (s1 == sc[u]) + (s2 == sc[u]) + (s3 == sc[u]);
+    }
+  }
+  for (; i < n_valid; ++i) {
+    const float s0 = ps[i * RS];
+#pragma unroll
+    for (int u = 0; u < U; ++u) {
+      rank[u] += (s0 < sc[u]);
+      eq[u] += (s0 == sc[u]);
+    }
+  }
+  bool tie = false;
+#pragma unroll
+  for (int u = 0; u < U; ++u) tie |= (lane + 32 * u < n_valid) && eq[u] > 1;
+  if (__any_sync(0xffffffffu, tie)) {  // equal scores: redo with the slot number as tie-break
+#pragma unroll
+    for (int u = 0; u < U; ++u) rank[u] = 0;
+    for (i = 0; i < n_valid; ++i) {
+      const float s0 = ps[i * RS];
+#pragma unroll
+      for (int u = 0; u < U; ++u) rank[u] += (s0 < sc[u] || (s0 == sc[u] && i < lane + 32 * u)) ? 1 : 0;
     }
   }
   __syncwarp();
   float tau = 0.0f;
 #pragma unroll
   for (int u = 0; u < U; ++u) {
-    const int j = lane + 32 * u;
-    const bool valid = j < n_valid;
-    if (valid && rank[u] < C) buf[(size_t)rank[u] * ROWS + col] = make_float2(sc[u], __int_as_float(id[u]));
-    const unsigned bm = __ballot_sync(0xffffffffu, valid && rank[u] == C - 1);
+    const bool valid = lane + 32 * u < n_valid;
+    if (valid && rank[u] < keep) {
+      bsc[rank[u] * RS + col] = sc[u];
+      bid[rank[u] * RS + col] = id[u];
+    }
+    const unsigned bm = __ballot_sync(0xffffffffu, valid && rank[u] == keep - 1);
     if (bm) tau = __shfl_sync(0xffffffffu, sc[u], __ffs(bm) - 1);
   }
   __syncwarp();
@@ -238,16 +268,18 @@ __device__ __forceinline__ float compact_row(float2* buf, int col, int n_valid, 
 template <int CAP, int HALVES, bool DBG>
 __global__ void __launch_bounds__((HALVES * 4 + 2) * 32, 1) knn_tc_kernel(const KParams p) {
   constexpr int ROWS = HALVES * TILE;
+  constexpr int RS = ROWS + 1;
   constexpr int EPI_WARPS = HALVES * 4;
-  constexpr int C = CAP / 2;
   constexpr uint32_t ACC_COLS = HALVES * TILE;  // TMEM columns per accumulator stage
   extern __shared__ __align__(1024) uint8_t smem[];
   const int K = p.K;
-  const uint32_t tile_bytes = (uint32_t)TILE * K * 2;
-  uint8_t* sA = smem;                                   // HALVES tiles
-  uint8_t* sB = sA + (size_t)HALVES * tile_bytes;       // stages tiles
-  float2* buf = reinterpret_cast<float2*>(sB + (size_t)p.stages * tile_bytes);  // [CAP][ROWS]
-  uint64_t* bars = reinterpret_cast<uint64_t*>(buf + (size_t)CAP * ROWS);
+  const uint32_t tile_bytes = (uint32_t)TILE * K * 2;  // one 128-row query tile
+  const uint32_t sub_bytes = (uint32_t)SUB * K * 2;    // one 64-row data sub-tile
+  uint8_t* sA = smem;                                  // HALVES query tiles
+  uint8_t* sB = sA + (size_t)HALVES * tile_bytes;      // ring of p.slots sub-tiles
+  float* bsc = reinterpret_cast<float*>(sB + (size_t)p.slots * sub_bytes);  // [CAP][RS] scores
+  int* bid = reinterpret_cast<int*>(bsc + (size_t)CAP * RS);                // [CAP][RS] data indices
+  uint64_t* bars = reinterpret_cast<uint64_t*>((reinterpret_cast<uintptr_t>(bid + (size_t)CAP * RS) + 15) & ~(uintptr_t)15);
   // bars: full[8], empty[8], accf[2], acce[2], afull, aempty
   uint64_t* bar_full = bars;
   uint64_t* bar_empty = bars + 8;
@@ -260,7 +292,7 @@ __global__ void __launch_bounds__((HALVES * 4 + 2) * 32, 1) knn_tc_kernel(const 
   const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
 
   if (threadIdx.x == 0) {
-    for (int s = 0; s < p.stages; ++s) {
+    for (int s = 0; s < p.slots; ++s) {
       ptx::mbar_init(ptx::smem_u32(&bar_full[s]), 1);
       ptx::mbar_init(ptx::smem_u32(&bar_empty[s]), 1);
     }
@@ -282,23 +314,24 @@ __global__ void __launch_bounds__((HALVES * 4 + 2) * 32, 1) knn_tc_kernel(const 
   const uint32_t tmem_base = *tmem_slot;
 
   const int nqb = (p.qblocks - (int)blockIdx.x + (int)gridDim.x - 1) / (int)gridDim.x;  // my query blocks
+  const int nsub = 2 * p.ntiles;
 
   if (warp == EPI_WARPS) {
     // ===================== producer: bulk copies on the TMA engine =====================
     if (lane == 0) {
-      uint32_t it = 0;
+      uint32_t jt = 0;
       for (int b = 0; b < nqb; ++b) {
         const int qb = (int)blockIdx.x + b * (int)gridDim.x;
         ptx::mbar_wait(ptx::smem_u32(bar_aempty), (b & 1) ^ 1);
         ptx::mbar_arrive_expect_tx(ptx::smem_u32(bar_afull), HALVES * tile_bytes);
         ptx::bulk_g2s(ptx::smem_u32(sA), reinterpret_cast<const uint8_t*>(p.a_img) + (size_t)qb * HALVES * tile_bytes,
                       HALVES * tile_bytes, ptx::smem_u32(bar_afull));
-        for (int t = 0; t < p.ntiles; ++t, ++it) {
-          const uint32_t s = it % p.stages, ph = (it / p.stages) & 1;
+        for (int st = 0; st < nsub; ++st, ++jt) {
+          const uint32_t s = jt % p.slots, ph = (jt / p.slots) & 1;
           ptx::mbar_wait(ptx::smem_u32(&bar_empty[s]), ph ^ 1);
-          ptx::mbar_arrive_expect_tx(ptx::smem_u32(&bar_full[s]), tile_bytes);
-          ptx::bulk_g2s(ptx::smem_u32(sB + (size_t)s * tile_bytes),
-                        reinterpret_cast<const uint8_t*>(p.b_img) + (size_t)t * tile_bytes, tile_bytes,
+          ptx::mbar_arrive_expect_tx(ptx::smem_u32(&bar_full[s]), sub_bytes);
+          ptx::bulk_g2s(ptx::smem_u32(sB + (size_t)s * sub_bytes),
+                        reinterpret_cast<const uint8_t*>(p.b_img) + (size_t)st * sub_bytes, sub_bytes,
                         ptx::smem_u32(&bar_full[s]));
         }
       }
@@ -306,39 +339,46 @@ __global__ void __launch_bounds__((HALVES * 4 + 2) * 32, 1) knn_tc_kernel(const 
   } else if (warp == EPI_WARPS + 1) {
     // ===================== MMA issuer: one thread drives the tensor core =====================
     if (lane == 0) {
-      constexpr uint32_t idesc = ptx::umma_idesc_f16(TILE, TILE);
+      constexpr uint32_t idesc = ptx::umma_idesc_f16(TILE, SUB);
       const int ksteps = K / 16;
-      uint32_t it = 0;
+      uint32_t it = 0, jt = 0;
       for (int b = 0; b < nqb; ++b) {
         ptx::mbar_wait(ptx::smem_u32(bar_afull), b & 1);
         for (int t = 0; t < p.ntiles; ++t, ++it) {
-          const uint32_t s = it % p.stages, ph = (it / p.stages) & 1;
           const uint32_t a = it & 1, aph = (it >> 1) & 1;
           ptx::mbar_wait(ptx::smem_u32(&bar_acce[a]), aph ^ 1);
-          ptx::mbar_wait(ptx::smem_u32(&bar_full[s]), ph);
-          ptx::tc_fence_after();
-          const uint32_t b_addr = ptx::smem_u32(sB + (size_t)s * tile_bytes);
 #pragma unroll
-          for (int h = 0; h < HALVES; ++h) {
-            const uint32_t a_addr = ptx::smem_u32(sA + (size_t)h * tile_bytes);
-            const uint32_t d_tmem = tmem_base + a * ACC_COLS + h * TILE;
-            for (int ks = 0; ks < ksteps; ++ks) {
-              const uint64_t ad = ptx::umma_desc(a_addr + ks * 4096, 2048, 128);
-              const uint64_t bd = ptx::umma_desc(b_addr + ks * 4096, 2048, 128);
-              ptx::umma_f16(d_tmem, ad, bd, idesc, ks > 0 ? 1u : 0u);
+          for (int hs = 0; hs < 2; ++hs, ++jt) {
+            const uint32_t s = jt % p.slots, ph = (jt / p.slots) & 1;
+            ptx::mbar_wait(ptx::smem_u32(&bar_full[s]), ph);
+            ptx::tc_fence_after();
+            const uint32_t b_addr = ptx::smem_u32(sB + (size_t)s * sub_bytes);
+#pragma unroll
+            for (int h = 0; h < HALVES; ++h) {
+              const uint32_t a_addr = ptx::smem_u32(sA + (size_t)h * tile_bytes);
+              const uint32_t d_tmem = tmem_base + a * ACC_COLS + h * TILE + hs * SUB;
+              for (int ks = 0; ks < ksteps; ++ks) {
+                const uint64_t ad = ptx::umma_desc(a_addr + ks * 4096, 2048, 128);
+                const uint64_t bd = ptx::umma_desc(b_addr + ks * 2048, 1024, 128);
+                ptx::umma_f16(d_tmem, ad, bd, idesc, ks > 0 ? 1u : 0u);
+              }
             }
+            ptx::umma_commit(ptx::smem_u32(&bar_empty[s]));  // sub-tile slot free once these MMAs retire
           }
-          ptx::umma_commit(ptx::smem_u32(&bar_empty[s]));  // B stage free once these MMAs retire
-          ptx::umma_commit(ptx::smem_u32(&bar_accf[a]));   // accumulator ready for the epilogue
+          ptx::umma_commit(ptx::smem_u32(&bar_accf[a]));     // 128 columns ready for the epilogue
         }
-        ptx::umma_commit(ptx::smem_u32(bar_aempty));       // A tile may be replaced
+        ptx::umma_commit(ptx::smem_u32(bar_aempty));         // A tiles may be replaced
       }
     }
   } else {
     // ===================== epilogue: threshold filter + candidate buffers =====================
     const int half = warp >> 2, quad = warp & 3;
-    const int row = half * TILE + quad * 32 + lane;  // my query row inside the block
+    const int row0 = half * TILE + quad * 32;
+    const int row = row0 + lane;  // my query row inside the block
     const uint32_t t_lane = tmem_base + ((uint32_t)(quad * 32) << 16) + half * TILE;
+    const int keep = p.keep;
+    float* my_sc = bsc + row;
+    int* my_id = bid + row;
     uint32_t it = 0;
     for (int b = 0; b < nqb; ++b) {
       const int qb = (int)blockIdx.x + b * (int)gridDim.x;
@@ -348,51 +388,61 @@ __global__ void __launch_bounds__((HALVES * 4 + 2) * 32, 1) knn_tc_kernel(const 
         const uint32_t a = it & 1, aph = (it >> 1) & 1;
         ptx::mbar_wait(ptx::smem_u32(&bar_accf[a]), aph);
         ptx::tc_fence_after();
+        if (p.mode != 2) {
+          const uint32_t t_acc = t_lane + a * ACC_COLS;
+          float va[32], vb[32];
+          ptx::tmem_ld32(t_acc, va);
 #pragma unroll 1
-        for (int c = 0; c < TILE / 32; ++c) {
-          float v[32];
-          ptx::tmem_ld32(t_lane + a * ACC_COLS + c * 32, v);
-          ptx::tmem_ld_wait();
-          if (DBG) {
-            if (p.dbg) {
-              float* o = p.dbg + ((size_t)qb * ROWS + row) * ((size_t)p.ntiles * TILE) + (size_t)t * TILE + c * 32;
-#pragma unroll
-              for (int i = 0; i < 32; ++i) o[i] = v[i];
-            }
-          }
-          float g[4];
-#pragma unroll
-          for (int gi = 0; gi < 4; ++gi) {
-            const float* w = v + gi * 8;
-            g[gi] = fminf(min3(w[0], w[1], w[2]), min3(min3(w[3], w[4], w[5]), w[6], w[7]));
-          }
-          const float m = fminf(fminf(g[0], g[1]), fminf(g[2], g[3]));
-          if (__any_sync(0xffffffffu, m < tau)) {
-            const int base = t * TILE + c * 32;
-#pragma unroll
-            for (int gi = 0; gi < 4; ++gi) {
-              if (g[gi] < tau) {
-#pragma unroll
-                for (int i = 0; i < 8; ++i) {
-                  const float s = v[gi * 8 + i];
-                  if (s < tau) {
-                    buf[(size_t)cnt * ROWS + row] = make_float2(s, __int_as_float(base + gi * 8 + i));
-                    ++cnt;
-                  }
-                }
-              }
-              unsigned need = __ballot_sync(0xffffffffu, cnt > CAP - 8);
-              while (need) {
-                const int r = __ffs(need) - 1;
-                need &= need - 1;
-                const int nv = __shfl_sync(0xffffffffu, cnt, r);
-                const float nt = compact_row<CAP, ROWS>(buf, half * TILE + quad * 32 + r, nv, lane);
-                if (lane == r) {
-                  tau = nt;
-                  cnt = C;
-                }
-              }
-            }
+          for (int c = 0; c < TILE / 32; c += 2) {
+            // software pipeline: the next 32 columns are in flight while these are filtered
+#define B200_PROCESS(v, cc)                                                                        \
+  do {                                                                                             \
+    if (DBG) {                                                                                     \
+      if (p.dbg) {                                                                                 \
+        float* o = p.dbg + ((size_t)qb * ROWS + row) * ((size_t)p.ntiles * TILE) + (size_t)t * TILE + (cc) * 32; \
+        _Pragma("unroll") for (int i = 0; i < 32; ++i) o[i] = v[i];                                \
+      }                                                                                            \
+    }                                                                                              \
+    float g[4];                                                                                    \
+    _Pragma("unroll") for (int gi = 0; gi < 4; ++gi) {                                             \
+      const float* w = v + gi * 8;                                                                 \
+      g[gi] = fminf(min3(w[0], w[1], w[2]), min3(min3(w[3], w[4], w[5]), w[6], w[7]));             \
+    }                                                                                              \
+    const float m = fminf(fminf(g[0], g[1]), fminf(g[2], g[3]));                                   \
+    if (p.mode == 0 && __any_sync(0xffffffffu, m < tau)) {                                         \
+      const int base = t * TILE + (cc) * 32;                                                       \
+      _Pragma("unroll") for (int gi = 0; gi < 4; ++gi) {                                           \
+        if (g[gi] < tau) {                                                                         \
+          _Pragma("unroll") for (int i = 0; i < 8; ++i) {                                          \
+            const float s = v[gi * 8 + i];                                                         \
+            if (s < tau) {                                                                         \
+              my_sc[cnt * RS] = s;                                                                 \
+              my_id[cnt * RS] = base + gi * 8 + i;                                                 \
+              ++cnt;                                                                               \
+            }                                                                                      \
+          }                                                                                        \
+        }                                                                                          \
+        unsigned need = __ballot_sync(0xffffffffu, cnt > CAP - 8);                                 \
+        while (need) {                                                                             \
+          const int r = __ffs(need) - 1;                                                           \
+          need &= need - 1;                                                                        \
+          const int nv = __shfl_sync(0xffffffffu, cnt, r);                                         \
+          const float nt = compact_row<CAP>(bsc, bid, RS, row0 + r, nv, keep, lane);               \
+          if (lane == r) {                                                                         \
+            tau = nt;                                                                              \
+            cnt = keep;                                                                            \
+          }                                                                                        \
+        }                                                                                          \
+      }                                                                                            \
+    }                                                                                              \
+  } while (0)
+            ptx::tmem_ld_wait();
+            ptx::tmem_ld32(t_acc + (c + 1) * 32, vb);
+            B200_PROCESS(va, c);
+            ptx::tmem_ld_wait();
+            if (c + 2 < TILE / 32) ptx::tmem_ld32(t_acc + (c + 2) * 32, va);
+            B200_PROCESS(vb, c + 1);
+#undef B200_PROCESS
           }
         }
         ptx::tc_fence_before();
@@ -400,13 +450,12 @@ __global__ void __launch_bounds__((HALVES * 4 + 2) * 32, 1) knn_tc_kernel(const 
         if (lane == 0) ptx::mbar_arrive(ptx::smem_u32(&bar_acce[a]));
       }
       // ---- flush this block's candidate lists (coalesced, one row at a time)
-      const int64_t q0 = (int64_t)qb * ROWS + half * TILE + quad * 32;
+      const int64_t q0 = (int64_t)qb * ROWS + row0;
       p.cand_cnt[q0 + lane] = cnt;
       p.cand_tau[q0 + lane] = tau;
       for (int r = 0; r < 32; ++r) {
         const int nv = __shfl_sync(0xffffffffu, cnt, r);
-        for (int j = lane; j < nv; j += 32)
-          p.cand_idx[(q0 + r) * CAP + j] = __float_as_int(buf[(size_t)j * ROWS + (half * TILE + quad * 32 + r)].y);
+        for (int j = lane; j < nv; j += 32) p.cand_idx[(q0 + r) * CAP + j] = bid[j * RS + row0 + r];
       }
       __syncwarp();
     }
@@ -500,7 +549,7 @@ int tc_prepare(b200_model* m, cudaStream_t st) {
   const int64_t n = m->n;
   const int d = m->d;
   t.K = tc::padK(d);
-  t.tiles = (n + tc::TILE - 1) / tc::TILE;
+  t.tiles = (n + tc::TILE - 1) / tc::TILE;  // 128-column tiles = pairs of 64-row sub-tile images
   const int64_t npad = t.tiles * tc::TILE;
   B200_TRY(t.mu.reserve((size_t)d * 8 + 64));
   B200_TRY(t.img.reserve((size_t)npad * t.K * 2));
@@ -546,34 +595,33 @@ int tc_prepare(b200_model* m, cudaStream_t st) {
 }
 
 struct TcConfig {
-  int cap, halves, stages;
+  int cap, halves, slots, keep;
   size_t smem;
 };
 
-// Pick candidate capacity (CAP = 2 * kept) and CTA shape for k (+1 when the query's own row
-// must be dropped later) and the shared-memory budget.
+// Candidate capacity and CTA shape for k (+1 when the query's own row is dropped later):
+// a compaction keeps `keep` = k + margin entries of a CAP-slot buffer; CAP leaves room for
+// at least 16 appends between compactions; the B ring gets whatever shared memory is left.
 bool tc_config(int d, int k, int margin, bool self, TcConfig* c) {
   const int K = tc::padK(d);
-  const int need = k + (self ? 1 : 0) + (margin < 0 ? k : margin);
+  const int base = k + (self ? 1 : 0);
+  int keep = base + (margin < 0 ? std::min(k, 16) : margin);
   int cap = 32;
-  while (cap / 2 < need) cap *= 2;
-  if (cap > 128) {
-    cap = 128;
-    if (k + (self ? 1 : 0) > cap / 2) return false;
-  }
-  const size_t tile = (size_t)tc::TILE * K * 2;
+  while (cap < keep + 24 && cap < 128) cap *= 2;
+  if (keep > cap - 24) keep = cap - 24;
+  if (keep < base) return false;
+  const size_t tile = (size_t)tc::TILE * K * 2, sub = (size_t)tc::SUBROWS * K * 2;
   const size_t limit = 227 * 1024 - 512;
   for (int halves = 2; halves >= 1; --halves) {
-    const size_t fixed = halves * tile + (size_t)cap * halves * tc::TILE * 8 + 256;
-    for (int stages = 4; stages >= 2; --stages) {
-      if (fixed + stages * tile <= limit) {
-        c->cap = cap;
-        c->halves = halves;
-        c->stages = stages;
-        c->smem = fixed + stages * tile;
-        return true;
-      }
-    }
+    const size_t fixed = halves * tile + (size_t)cap * (halves * tc::TILE + 1) * 8 + 256;
+    if (fixed + 3 * sub > limit) continue;
+    const int slots = (int)std::min<size_t>(8, (limit - fixed) / sub);
+    c->cap = cap;
+    c->halves = halves;
+    c->slots = slots;
+    c->keep = keep;
+    c->smem = fixed + slots * sub;
+    return true;
   }
   return false;
 }
@@ -642,7 +690,9 @@ int knn_tc(b200_model* m, const double* z_dev, int64_t q, int k, int64_t self_of
   kp.K = t.K;
   kp.ntiles = (int)t.tiles;
   kp.qblocks = qblocks;
-  kp.stages = cfg.stages;
+  kp.slots = cfg.slots;
+  kp.keep = cfg.keep;
+  kp.mode = m->tc_mode;
   kp.cand_idx = m->cand.as<int32_t>();
   kp.cand_cnt = cand_cnt;
   kp.cand_tau = cand_tau;
@@ -684,6 +734,8 @@ int knn_tc(b200_model* m, const double* z_dev, int64_t q, int k, int64_t self_of
   m->st.tc_queries += q;
   m->st.uncertified += h_fail;
   m->st.last_cap = cfg.cap;
+  m->st.last_keep = cfg.keep;
+  m->st.last_slots = cfg.slots;
   if (h_fail > 0) {
     cudaEventRecord(m->ev0, st);
     B200_TRY(knn_exact(m, z_dev, q, k, self_offset, idx_dev, d2_dev, fail_list, h_fail, st));
