@@ -33,6 +33,7 @@ CONFIGS = {
     "c5": (1_000_000, 1_000_000, 64, 16),
     "c5small": (200_000, 100_000, 64, 16),
     "c1": (10_000, 1_000, 8, 1),
+    "c5q": (1_000_000, 37_888, 64, 16),   # one 256-query block per SM: quick kernel experiments
 }
 
 
@@ -142,8 +143,12 @@ def main():
     ap.add_argument("--shard", default="data", choices=["data", "query"])
     ap.add_argument("--cpu-seconds", type=float, default=15.0)
     ap.add_argument("--no-cpu", action="store_true")
+    ap.add_argument("--no-e2e", action="store_true", help="kernel experiments only: skip the host-buffer leg")
     ap.add_argument("--path", type=int, default=0, help="0 auto, 1 exact, 2 tensor")
     ap.add_argument("--margin", type=int, default=-1)
+    ap.add_argument("--tc-sub", type=int, default=128)
+    ap.add_argument("--tc-flags", type=int, default=0)
+    ap.add_argument("--tc-halves", type=int, default=0)
     ap.add_argument("--tc-mode", type=int, default=0, help="debug ceilings: 1 TMEM reads only, 2 no epilogue")
     args = ap.parse_args()
     n, q, d, k = CONFIGS[args.config]
@@ -181,6 +186,9 @@ def main():
     model.set_option("knn_path", args.path)
     model.set_option("margin", args.margin)
     model.set_option("tc_mode", args.tc_mode)
+    model.set_option("tc_sub", args.tc_sub)
+    model.set_option("tc_flags", args.tc_flags)
+    model.set_option("tc_halves", args.tc_halves)
     h = model.handle
     if G > 1 and args.shard == "query":
         qs = (q + G - 1) // G
@@ -251,7 +259,9 @@ def main():
     # ---- end to end through the host-buffer C-ABI (pinned inputs, host outputs, copies timed)
     e2e = None
     h2d = d2h = 0
-    if not data_sharded:
+    if args.no_e2e:
+        dt = float("nan")
+    elif not data_sharded:
         zp = z_pin.numpy()
         for _ in range(2):
             model.nn_predict(zp, k, _lib.SHEPARD, y=y, want_weights=False)
@@ -316,8 +326,8 @@ def main():
                 "roofline": roof,
                 "stages_ms": {kk: vv for kk, vv in stats.items() if kk.startswith("ms_")},
                 "uncertified_per_step": stats["uncertified"],
-                "tc": {"cap": model.stat("tc_cap"), "keep": model.stat("tc_keep"), "slots": model.stat("tc_slots"),
-                       "K": model.stat("tc_K"), "mode": args.tc_mode},
+                "tc": {"cap": model.stat("tc_cap"), "keep": model.stat("tc_keep"), "slots": model.stat("tc_slots"), "halves": model.stat("tc_halves"),
+                       "K": model.stat("tc_K"), "mode": args.tc_mode, "sub": args.tc_sub, "flags": args.tc_flags},
                 "gpu_launches": int(round(stats["launches"] * args.steps)),
                 "e2e": e2e, "clocks": sampler.summary()}
         if G == 1 and not args.no_cpu:

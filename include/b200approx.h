@@ -127,6 +127,11 @@ int b200_knn_exact_noalloc(const double* x_dev, int64_t n, int32_t d, const doub
 int b200_tc_debug_scores(b200_model* m, const double* z, int64_t q, int32_t k, float* scores,
                          int64_t cols);
 
+/* Tuning hook, no counterpart in the reference: clock64 stamps of the producer / MMA /
+ * epilogue roles of CTA 0 for the first 96 tiles, stamps (3, 96, 4) int64. */
+int b200_tc_debug_trace(b200_model* m, const double* z, int64_t q, int32_t k, int64_t* stamps,
+                        int64_t count);
+
 #ifdef __cplusplus
 }
 #endif

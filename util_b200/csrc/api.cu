@@ -179,6 +179,16 @@ int b200_set_option(b200_model* m, const char* key, double value) {
   if (!strcmp(key, "knn_path")) m->knn_path = (int)value;
   else if (!strcmp(key, "margin")) m->margin = (int)value;
   else if (!strcmp(key, "tc_mode")) m->tc_mode = (int)value;
+  else if (!strcmp(key, "tc_flags")) m->tc_flags = (int)value;
+  else if (!strcmp(key, "tc_halves")) m->tc_halves = (int)value;
+  else if (!strcmp(key, "tc_trace_start")) m->tc_trace_start = (int)value;
+  else if (!strcmp(key, "tc_sub")) {
+    if ((int)value != 64 && (int)value != 128) {
+      set_error("tc_sub must be 64 or 128");
+      return 1;
+    }
+    m->tc_sub = (int)value;
+  }
   else if (!strcmp(key, "rows_per_call")) m->rows_per_call = (int64_t)value;
   else if (!strcmp(key, "reset_stats")) m->st = Stats();
   else {
@@ -206,6 +216,7 @@ int b200_get_stat(b200_model* m, const char* key, double* value) {
   else if (!strcmp(key, "tc_cap")) *value = s.last_cap;
   else if (!strcmp(key, "tc_keep")) *value = s.last_keep;
   else if (!strcmp(key, "tc_slots")) *value = s.last_slots;
+  else if (!strcmp(key, "tc_halves")) *value = s.last_halves;
   else if (!strcmp(key, "sm_count")) *value = m->sm_count;
   else {
     set_error("unknown stat '%s'", key);
@@ -312,6 +323,27 @@ int b200_tc_debug_scores(b200_model* m, const double* z, int64_t q, int32_t k, f
     rc = 2;
   }
   dump.release();
+  return rc;
+}
+
+int b200_tc_debug_trace(b200_model* m, const double* z, int64_t q, int32_t k, int64_t* stamps,
+                        int64_t count) {
+  B200_TRY(use(m));
+  if (count != 3 * 96 * 4) {
+    set_error("b200_tc_debug_trace: count must be %d", 3 * 96 * 4);
+    return 1;
+  }
+  DevBuf tr;
+  B200_TRY(tr.reserve((size_t)count * 8));
+  B200_CUDA(cudaMemset(tr.p, 0, (size_t)count * 8));
+  B200_TRY(upload_queries(m, z, q));
+  B200_TRY(m->idx32.reserve((size_t)q * k * 4));
+  B200_TRY(m->d2.reserve((size_t)q * k * 8));
+  m->dbg_trace = tr.as<long long>();
+  int rc = knn_tc(m, m->zq.as<double>(), q, k, -1, m->idx32.as<int32_t>(), m->d2.as<double>(), 0);
+  m->dbg_trace = nullptr;
+  if (rc == 0 && cudaMemcpy(stamps, tr.p, (size_t)count * 8, cudaMemcpyDeviceToHost) != cudaSuccess) rc = 2;
+  tr.release();
   return rc;
 }
 

@@ -62,6 +62,8 @@ struct DevBuf {
 struct TcData {
   bool ready = false;
   int K = 0;            // padded contraction length (multiple of 16)
+  int sub = 128;        // rows per data sub-tile image (64 or 128)
+  int rg = 0;           // 1: row-group-major image layout
   int64_t tiles = 0;    // 128-point tiles
   double scale = 1.0;   // power of two applied after centring
   double ymax = 0.0;    // max over points of max(||yc||, ||fp16(yc)||) (scaled units)
@@ -72,7 +74,7 @@ struct TcData {
 
 struct Stats {
   double uncertified = 0, ms_stage1 = 0, ms_rerank = 0, ms_weights = 0, ms_exact = 0,
-         launches = 0, tc_queries = 0, exact_queries = 0, last_cap = 0, ms_prep = 0, last_keep = 0, last_slots = 0;
+         launches = 0, tc_queries = 0, exact_queries = 0, last_cap = 0, ms_prep = 0, last_keep = 0, last_slots = 0, last_halves = 0;
 };
 
 }  // namespace b200
@@ -95,11 +97,16 @@ struct b200_model {
       flags, misc, ids64;
   // options
   int knn_path = 0;
-  int margin = -1;  // extra candidates kept by the tensor filter (-1: min(k, 16))
+  int margin = -1;  // extra candidates kept by the tensor filter (-1: max(4, min(k/2, 16)))
+  int tc_sub = 128;   // data rows per sub-tile image / UMMA N (64 or 128)
+  int tc_halves = 0;  // force 128*halves query rows per CTA (0: automatic)
+  int tc_trace_start = 0;
+  int tc_flags = 0;   // bit 0: suspend-time hint on mbarrier waits
   int tc_mode = 0;  // debug: 1/2 strip the epilogue to measure the MMA/TMA pipeline ceiling
   int64_t rows_per_call = 1 << 20;
   b200::Stats st;
   cudaEvent_t ev0 = nullptr, ev1 = nullptr, ev2 = nullptr, ev3 = nullptr;
+  long long* dbg_trace = nullptr;  // tuning only: clock stamps of CTA 0
   float* dbg_scores = nullptr;  // tests only: raw tensor-path scores are dumped here
 };
 

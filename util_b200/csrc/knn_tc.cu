@@ -35,7 +35,6 @@ namespace b200 {
 namespace tc {
 
 constexpr int TILE = 128;          // query rows per accumulator half = data columns per epilogue tile
-constexpr int SUBROWS = 64;        // data rows per operand sub-tile image (one bulk copy, one UMMA N)
 constexpr int NORM_SLOTS = 3;
 constexpr double U16 = 4.8828125e-4;             // 2^-11: fp16 unit roundoff
 constexpr double TINY16 = 2.98023223876953125e-8;  // 2^-25: half the smallest fp16 subnormal
@@ -79,7 +78,7 @@ __global__ void maxabs_kernel(const double* __restrict__ x, int64_t n, int d, co
 // ------------------------------------------------------------- operand images
 // Data side: one thread per (padded) point; writes its row of the tile image and
 // folds max(||yc||, ||fp16(yc)||) into ymax.
-__global__ void data_img_kernel(const double* __restrict__ x, int64_t n, int d, int K,
+__global__ void data_img_kernel(const double* __restrict__ x, int64_t n, int d, int K, int SUBROWS, int rg,
                                 const double* __restrict__ mu, double scale, __half* __restrict__ img,
                                 int64_t npad, unsigned long long* __restrict__ ymax_bits) {
   const int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
@@ -119,7 +118,7 @@ __global__ void data_img_kernel(const double* __restrict__ x, int64_t n, int d, 
         }
         h[e] = __float2half_rn(hv);
       }
-      dst[(size_t)c * SUBROWS + r] = *reinterpret_cast<uint4*>(h);
+      dst[rg ? ((size_t)(r >> 3) * KC + c) * 8 + (r & 7) : (size_t)c * SUBROWS + r] = *reinterpret_cast<uint4*>(h);
     }
     nm = sqrt(fmax(n2, n2h));
   }
@@ -134,7 +133,7 @@ struct QMeta {
 };
 
 // Query side: x~ = fp16(-2 * (z - mu) * scale), then the three 1.0 slots.
-__global__ void query_img_kernel(const double* __restrict__ z, int64_t q, int d, int K,
+__global__ void query_img_kernel(const double* __restrict__ z, int64_t q, int d, int K, int rg,
                                  const double* __restrict__ mu, double scale, double ymax,
                                  __half* __restrict__ img, int64_t qpad, QMeta* __restrict__ meta) {
   const int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
@@ -166,7 +165,7 @@ __global__ void query_img_kernel(const double* __restrict__ z, int64_t q, int d,
       if (i < q && j >= d && j < d + NORM_SLOTS) hv = 1.0f;
       h[e] = __float2half_rn(hv);
     }
-    dst[(size_t)c * TILE + r] = *reinterpret_cast<uint4*>(h);
+    dst[rg ? ((size_t)(r >> 3) * KC + c) * 8 + (r & 7) : (size_t)c * TILE + r] = *reinterpret_cast<uint4*>(h);
   }
   if (i < q) {
     const double xn = sqrt(xn2) * 1.001;
@@ -189,16 +188,26 @@ struct KParams {
   int K;                 // contraction length, multiple of 16
   int ntiles;            // 128-column data tiles (two 64-row sub-tiles each)
   int qblocks;           // query blocks of HALVES*128 rows
-  int slots;             // depth of the B ring, in 64-row sub-tiles
+  int sub;               // data rows per B sub-tile: 64 or 128 (one TMA copy, one UMMA N)
+  int flags;             // bit 0: mbarrier waits pass a suspend-time hint
+  int slots;             // depth of the B ring, in sub-tiles
   int keep;              // C: candidates a compaction keeps (<= CAP - 8)
   int mode;              // 0 normal; debug ceilings: 1 = epilogue reads TMEM only, 2 = epilogue only releases
   int32_t* cand_idx;     // [qpad][CAP]
   int32_t* cand_cnt;     // [qpad]
   float* cand_tau;       // [qpad]
   float* dbg;            // optional [qpad][ntiles*128] raw scores (tests only)
+  int trace_start;       // first tile recorded in `trace`
+  long long* trace;      // optional [3 roles][TRACE_TILES][4] clock64 stamps of CTA 0 (tuning only)
 };
+constexpr int TRACE_TILES = 96;
+#define B200_TRACE(role, tile, ev)                                                         \
+  do {                                                                                     \
+    const int tt_ = (int)(tile) - p.trace_start;                                           \
+    if (p.trace && blockIdx.x == 0 && tt_ >= 0 && tt_ < TRACE_TILES)                       \
+      p.trace[((role) * TRACE_TILES + tt_) * 4 + (ev)] = clock64();                        \
+  } while (0)
 
-constexpr int SUB = 64;  // data rows per B sub-tile (one TMA copy, one UMMA N)
 
 __device__ __forceinline__ float min3(float a, float b, float c) { return fminf(fminf(a, b), c); }
 
@@ -208,14 +217,14 @@ __device__ __forceinline__ float min3(float a, float b, float c) { return fminf(
 template <int CAP>
 __device__ __noinline__ float compact_row(float* bsc, int* bid, int RS, int col, int n_valid, int keep,
                                           int lane) {
-  constexpr int U = CAP / 32;
+  constexpr int U = (CAP + 31) / 32;
   float sc[U];
   int id[U], rank[U], eq[U];
 #pragma unroll
   for (int u = 0; u < U; ++u) {
     const int j = lane + 32 * u;
     sc[u] = j < n_valid ? bsc[j * RS + col] : CUDART_INF_F;
-    id[u] = bid[j * RS + col];
+    id[u] = j < n_valid ? bid[j * RS + col] : 0;
     rank[u] = 0;
     eq[u] = 0;
   }
@@ -266,7 +275,7 @@ __device__ __noinline__ float compact_row(float* bsc, int* bid, int RS, int col,
 }
 
 template <int CAP, int HALVES, bool DBG>
-__global__ void __launch_bounds__((HALVES * 4 + 2) * 32, 1) knn_tc_kernel(const KParams p) {
+__global__ void __launch_bounds__((HALVES * 4 + 3) * 32, 1) knn_tc_kernel(const KParams p) {
   constexpr int ROWS = HALVES * TILE;
   constexpr int RS = ROWS + 1;
   constexpr int EPI_WARPS = HALVES * 4;
@@ -274,34 +283,37 @@ __global__ void __launch_bounds__((HALVES * 4 + 2) * 32, 1) knn_tc_kernel(const 
   extern __shared__ __align__(1024) uint8_t smem[];
   const int K = p.K;
   const uint32_t tile_bytes = (uint32_t)TILE * K * 2;  // one 128-row query tile
-  const uint32_t sub_bytes = (uint32_t)SUB * K * 2;    // one 64-row data sub-tile
+  const int SUB = p.sub;
+  const uint32_t sub_bytes = (uint32_t)SUB * K * 2;    // one data sub-tile
   uint8_t* sA = smem;                                  // HALVES query tiles
   uint8_t* sB = sA + (size_t)HALVES * tile_bytes;      // ring of p.slots sub-tiles
   float* bsc = reinterpret_cast<float*>(sB + (size_t)p.slots * sub_bytes);  // [CAP][RS] scores
   int* bid = reinterpret_cast<int*>(bsc + (size_t)CAP * RS);                // [CAP][RS] data indices
   uint64_t* bars = reinterpret_cast<uint64_t*>((reinterpret_cast<uintptr_t>(bid + (size_t)CAP * RS) + 15) & ~(uintptr_t)15);
-  // bars: full[8], empty[8], accf[2], acce[2], afull, aempty
+  // bars: full[8], empty[8], accf[stage][half], acce[stage][half], afull, aempty
   uint64_t* bar_full = bars;
   uint64_t* bar_empty = bars + 8;
   uint64_t* bar_accf = bars + 16;
-  uint64_t* bar_acce = bars + 18;
-  uint64_t* bar_afull = bars + 20;
-  uint64_t* bar_aempty = bars + 21;
-  uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(bars + 22);
+  uint64_t* bar_acce = bars + 20;
+  uint64_t* bar_afull = bars + 24;
+  uint64_t* bar_aempty = bars + 25;
+  uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(bars + 26);
 
-  const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+  // shfl-broadcast so the compiler knows the role index is warp-uniform: the role bodies then run on
+  // the uniform datapath (UR operands for UTCHMMA / UBLKCP without R2UR round trips)
+  const int warp = __shfl_sync(0xffffffffu, (int)(threadIdx.x >> 5), 0), lane = threadIdx.x & 31;
 
   if (threadIdx.x == 0) {
     for (int s = 0; s < p.slots; ++s) {
       ptx::mbar_init(ptx::smem_u32(&bar_full[s]), 1);
       ptx::mbar_init(ptx::smem_u32(&bar_empty[s]), 1);
     }
-    for (int a = 0; a < 2; ++a) {
+    for (int a = 0; a < 4; ++a) {
       ptx::mbar_init(ptx::smem_u32(&bar_accf[a]), 1);
-      ptx::mbar_init(ptx::smem_u32(&bar_acce[a]), EPI_WARPS);
+      ptx::mbar_init(ptx::smem_u32(&bar_acce[a]), 4);  // the four warps of one half
     }
     ptx::mbar_init(ptx::smem_u32(bar_afull), 1);
-    ptx::mbar_init(ptx::smem_u32(bar_aempty), 1);
+    ptx::mbar_init(ptx::smem_u32(bar_aempty), 2);  // one commit per issuer warp
     ptx::fence_barrier_init();
   }
   if (warp == EPI_WARPS + 1) {  // MMA warp owns the TMEM allocation
@@ -312,70 +324,138 @@ __global__ void __launch_bounds__((HALVES * 4 + 2) * 32, 1) knn_tc_kernel(const 
   __syncthreads();
   ptx::tc_fence_after();
   const uint32_t tmem_base = *tmem_slot;
+  if (tmem_base != 0) {  // one CTA per SM allocating all 512 columns always gets column 0
+    if (threadIdx.x == 0) printf("b200: unexpected TMEM base %u\n", tmem_base);
+    __trap();
+  }
 
   const int nqb = (p.qblocks - (int)blockIdx.x + (int)gridDim.x - 1) / (int)gridDim.x;  // my query blocks
-  const int nsub = 2 * p.ntiles;
+  const int per_tile = TILE / SUB;
+  const int nsub = per_tile * p.ntiles;
+  const bool hint = p.flags & 1;
+  const uint32_t bsleep = (p.flags & 16) ? 0 : 64;  // ns between barrier probes of the producer / MMA warps
 
   if (warp == EPI_WARPS) {
     // ===================== producer: bulk copies on the TMA engine =====================
     if (lane == 0) {
-      uint32_t jt = 0;
+      uint32_t jt = 0, s = 0, ph = 0;
+      const uint32_t full0 = ptx::smem_u32(&bar_full[0]), empty0 = ptx::smem_u32(&bar_empty[0]);
+      const uint32_t sB0 = ptx::smem_u32(sB);
       for (int b = 0; b < nqb; ++b) {
         const int qb = (int)blockIdx.x + b * (int)gridDim.x;
-        ptx::mbar_wait(ptx::smem_u32(bar_aempty), (b & 1) ^ 1);
+        ptx::mbar_wait(hint, ptx::smem_u32(bar_aempty), (b & 1) ^ 1, bsleep);
         ptx::mbar_arrive_expect_tx(ptx::smem_u32(bar_afull), HALVES * tile_bytes);
         ptx::bulk_g2s(ptx::smem_u32(sA), reinterpret_cast<const uint8_t*>(p.a_img) + (size_t)qb * HALVES * tile_bytes,
                       HALVES * tile_bytes, ptx::smem_u32(bar_afull));
-        for (int st = 0; st < nsub; ++st, ++jt) {
-          const uint32_t s = jt % p.slots, ph = (jt / p.slots) & 1;
-          ptx::mbar_wait(ptx::smem_u32(&bar_empty[s]), ph ^ 1);
-          ptx::mbar_arrive_expect_tx(ptx::smem_u32(&bar_full[s]), sub_bytes);
-          ptx::bulk_g2s(ptx::smem_u32(sB + (size_t)s * sub_bytes),
-                        reinterpret_cast<const uint8_t*>(p.b_img) + (size_t)st * sub_bytes, sub_bytes,
-                        ptx::smem_u32(&bar_full[s]));
+        const uint8_t* src = reinterpret_cast<const uint8_t*>(p.b_img);
+        for (int st = 0; st < nsub; ++st, ++jt, src += sub_bytes) {
+          ptx::mbar_wait(hint, empty0 + s * 8, ph ^ 1, bsleep);
+          B200_TRACE(0, (int)jt, 0);
+          if ((p.mode & 4) && jt >= (uint32_t)p.slots) {  // debug: no copy, the slot keeps its old tile
+            ptx::mbar_arrive(full0 + s * 8);
+          } else {
+            ptx::mbar_arrive_expect_tx(full0 + s * 8, sub_bytes);
+            ptx::bulk_g2s(sB0 + s * sub_bytes, src, sub_bytes, full0 + s * 8);
+          }
+          if (++s == (uint32_t)p.slots) {
+            s = 0;
+            ph ^= 1;
+          }
         }
       }
     }
-  } else if (warp == EPI_WARPS + 1) {
-    // ===================== MMA issuer: one thread drives the tensor core =====================
-    if (lane == 0) {
-      constexpr uint32_t idesc = ptx::umma_idesc_f16(TILE, SUB);
+  } else if (warp > EPI_WARPS) {
+    // ===================== MMA issuers: two warps, alternate tiles =====================
+    // An issuing thread spends, per 128-column tile, ~730 clk issuing 10 MMAs into the short tensor
+    // queue plus ~700 clk in commits and barrier waits during which it queues nothing (measured with
+    // the clock trace, profiles/r01).  Two issuers on alternate tiles (issuer j owns accumulator
+    // stage j) interleave those phases so the tensor pipe always has work.  Each warp runs in uniform
+    // control flow; one elected lane issues the MMAs and the commits that track them.
+    {
+      const int j = warp - (EPI_WARPS + 1);  // issuer index = accumulator stage
+      const uint32_t idesc = ptx::umma_idesc_f16(TILE, SUB);
+      // operand image layout: chunk-major [K/8][rows][16 B] or row-group-major [rows/8][K/8][8][16 B]
+      const bool rg = p.flags & 2;
+      const uint32_t lbo_a = rg ? 128 : TILE * 16, sbo_a = rg ? (K / 8) * 128 : 128, kstep_a = rg ? 256 : TILE * 32;
+      const uint32_t lbo_b = rg ? 128 : SUB * 16, sbo_b = sbo_a, kstep_b = rg ? 256 : SUB * 32;
+      const bool skip_mma = p.mode & 8;
       const int ksteps = K / 16;
-      uint32_t it = 0, jt = 0;
-      for (int b = 0; b < nqb; ++b) {
-        ptx::mbar_wait(ptx::smem_u32(bar_afull), b & 1);
-        for (int t = 0; t < p.ntiles; ++t, ++it) {
-          const uint32_t a = it & 1, aph = (it >> 1) & 1;
-          ptx::mbar_wait(ptx::smem_u32(&bar_acce[a]), aph ^ 1);
+      uint64_t a_desc[HALVES];
 #pragma unroll
-          for (int hs = 0; hs < 2; ++hs, ++jt) {
-            const uint32_t s = jt % p.slots, ph = (jt / p.slots) & 1;
-            ptx::mbar_wait(ptx::smem_u32(&bar_full[s]), ph);
-            ptx::tc_fence_after();
-            const uint32_t b_addr = ptx::smem_u32(sB + (size_t)s * sub_bytes);
+      for (int h = 0; h < HALVES; ++h) a_desc[h] = ptx::umma_desc(ptx::smem_u32(sA + (size_t)h * tile_bytes), lbo_a, sbo_a);
+      const uint64_t b_desc0 = ptx::umma_desc(ptx::smem_u32(sB), lbo_b, sbo_b);
+      const uint32_t a_step = kstep_a >> 4, b_step = kstep_b >> 4, slot_step = sub_bytes >> 4;
+      const uint32_t full0 = ptx::smem_u32(&bar_full[0]), empty0 = ptx::smem_u32(&bar_empty[0]);
+      const uint32_t accf = ptx::smem_u32(&bar_accf[j * 2]), acce = ptx::smem_u32(&bar_acce[j * 2]);
+      const uint32_t slot_mask = p.slots - 1, slot_shift = 31 - __clz(p.slots);  // slots is a power of two
+      uint32_t it0 = 0;   // global index of the current block's first tile
+      uint32_t mine = 0;  // tiles this issuer has done (phase of its accumulator stage)
+      for (int b = 0; b < nqb; ++b, it0 += p.ntiles) {
+        ptx::mbar_wait(hint, ptx::smem_u32(bar_afull), b & 1, bsleep);
+        for (uint32_t t = (j + it0) & 1; t < (uint32_t)p.ntiles; t += 2, ++mine) {
+          const uint32_t it = it0 + t;
+          for (int hs = 0; hs < per_tile; ++hs) {
+            const uint32_t jt = it * per_tile + hs, s = jt & slot_mask, ph = (jt >> slot_shift) & 1;
+            const uint64_t bd = b_desc0 + (uint64_t)(s * slot_step);
+            bool have_b = false;
 #pragma unroll
             for (int h = 0; h < HALVES; ++h) {
-              const uint32_t a_addr = ptx::smem_u32(sA + (size_t)h * tile_bytes);
-              const uint32_t d_tmem = tmem_base + a * ACC_COLS + h * TILE + hs * SUB;
-              for (int ks = 0; ks < ksteps; ++ks) {
-                const uint64_t ad = ptx::umma_desc(a_addr + ks * 4096, 2048, 128);
-                const uint64_t bd = ptx::umma_desc(b_addr + ks * 2048, 1024, 128);
-                ptx::umma_f16(d_tmem, ad, bd, idesc, ks > 0 ? 1u : 0u);
+              // the accumulator half is free once its four epilogue warps have read the previous tile
+              if (hs == 0) ptx::mbar_wait(hint, acce + h * 8, (mine & 1) ^ 1, bsleep);
+              if (!have_b) {
+                ptx::mbar_wait(hint, full0 + s * 8, ph, bsleep);
+                have_b = true;
               }
+              ptx::tc_fence_after();
+              // (the accumulator base is the literal 0: this CTA owns all 512 columns, checked at start)
+              const uint32_t d_tmem = j * ACC_COLS + h * TILE + hs * SUB;
+              if (ptx::elect_one()) {
+                if (h == 0) B200_TRACE(1, (int)it, 0);
+                if (!skip_mma) {
+#define B200_ISSUE(KS)                                                                                   \
+  _Pragma("unroll") for (int ks = 0; ks < KS; ++ks)                                                       \
+    ptx::umma_f16(d_tmem, a_desc[h] + (uint64_t)(ks * a_step), bd + (uint64_t)(ks * b_step), idesc,        \
+                  ks > 0 ? 1u : 0u);
+                  switch (ksteps) {
+                    case 1: B200_ISSUE(1) break;
+                    case 2: B200_ISSUE(2) break;
+                    case 3: B200_ISSUE(3) break;
+                    case 4: B200_ISSUE(4) break;
+                    case 5: B200_ISSUE(5) break;
+                    case 6: B200_ISSUE(6) break;
+                    default:
+                      for (int ks = 0; ks < ksteps; ++ks)
+                        ptx::umma_f16(d_tmem, a_desc[h] + (uint64_t)(ks * a_step), bd + (uint64_t)(ks * b_step),
+                                      idesc, ks > 0 ? 1u : 0u);
+                  }
+#undef B200_ISSUE
+                }
+                if (hs == per_tile - 1) ptx::umma_commit(accf + h * 8);  // this half's 128 columns are ready
+                if (h == HALVES - 1) {
+                  B200_TRACE(1, (int)it, 1);
+                  ptx::umma_commit(empty0 + s * 8);  // sub-tile slot free once these MMAs retire
+                  B200_TRACE(1, (int)it, 3);
+                }
+              }
+              __syncwarp();
             }
-            ptx::umma_commit(ptx::smem_u32(&bar_empty[s]));  // sub-tile slot free once these MMAs retire
           }
-          ptx::umma_commit(ptx::smem_u32(&bar_accf[a]));     // 128 columns ready for the epilogue
         }
-        ptx::umma_commit(ptx::smem_u32(bar_aempty));         // A tiles may be replaced
+        if (ptx::elect_one()) ptx::umma_commit(ptx::smem_u32(bar_aempty));  // my MMAs on these A tiles are tracked
+        __syncwarp();
       }
     }
   } else {
     // ===================== epilogue: threshold filter + candidate buffers =====================
+    // Fast path per 128-column tile: four tcgen05.ld of 32 columns (software pipelined), an FMNMX3
+    // tree per chunk, ONE warp vote per tile.  Only when some lane beats its threshold are the
+    // offending chunks read again from TMEM and scanned.  The four warps of a half synchronise with
+    // the MMA issuers on their own per-half barriers, so a warp that is compacting holds up three
+    // others, not seven.
     const int half = warp >> 2, quad = warp & 3;
     const int row0 = half * TILE + quad * 32;
     const int row = row0 + lane;  // my query row inside the block
-    const uint32_t t_lane = tmem_base + ((uint32_t)(quad * 32) << 16) + half * TILE;
+    const uint32_t t_lane = ((uint32_t)(quad * 32) << 16) + half * TILE;
     const int keep = p.keep;
     float* my_sc = bsc + row;
     int* my_id = bid + row;
@@ -386,16 +466,16 @@ __global__ void __launch_bounds__((HALVES * 4 + 2) * 32, 1) knn_tc_kernel(const 
       int cnt = 0;
       for (int t = 0; t < p.ntiles; ++t, ++it) {
         const uint32_t a = it & 1, aph = (it >> 1) & 1;
-        ptx::mbar_wait(ptx::smem_u32(&bar_accf[a]), aph);
+        ptx::mbar_wait(hint, ptx::smem_u32(&bar_accf[a * 2 + half]), aph);
+        if (warp == 0 && lane == 0) B200_TRACE(2, (int)it, 0);
         ptx::tc_fence_after();
-        if (p.mode != 2) {
-          const uint32_t t_acc = t_lane + a * ACC_COLS;
-          float va[32], vb[32];
-          ptx::tmem_ld32(t_acc, va);
-#pragma unroll 1
-          for (int c = 0; c < TILE / 32; c += 2) {
-            // software pipeline: the next 32 columns are in flight while these are filtered
-#define B200_PROCESS(v, cc)                                                                        \
+        // compaction trigger: while hits are dense (first tiles) keep room for a whole 32-column chunk,
+        // later 8 free slots suffice (a rare overflow only lowers tau, see below)
+        const int high = t < 16 ? max(keep, CAP - 32) : CAP - 8;
+        const uint32_t t_acc = t_lane + a * ACC_COLS;
+        if ((p.mode & 3) != 2) {
+          float va[32], vb[32], mc[4];
+#define B200_CHUNKMIN(v, cc)                                                                       \
   do {                                                                                             \
     if (DBG) {                                                                                     \
       if (p.dbg) {                                                                                 \
@@ -403,51 +483,89 @@ __global__ void __launch_bounds__((HALVES * 4 + 2) * 32, 1) knn_tc_kernel(const 
         _Pragma("unroll") for (int i = 0; i < 32; ++i) o[i] = v[i];                                \
       }                                                                                            \
     }                                                                                              \
-    float g[4];                                                                                    \
+    float g_[4];                                                                                   \
     _Pragma("unroll") for (int gi = 0; gi < 4; ++gi) {                                             \
       const float* w = v + gi * 8;                                                                 \
-      g[gi] = fminf(min3(w[0], w[1], w[2]), min3(min3(w[3], w[4], w[5]), w[6], w[7]));             \
+      g_[gi] = fminf(min3(w[0], w[1], w[2]), min3(min3(w[3], w[4], w[5]), w[6], w[7]));            \
     }                                                                                              \
-    const float m = fminf(fminf(g[0], g[1]), fminf(g[2], g[3]));                                   \
-    if (p.mode == 0 && __any_sync(0xffffffffu, m < tau)) {                                         \
-      const int base = t * TILE + (cc) * 32;                                                       \
-      _Pragma("unroll") for (int gi = 0; gi < 4; ++gi) {                                           \
-        if (g[gi] < tau) {                                                                         \
-          _Pragma("unroll") for (int i = 0; i < 8; ++i) {                                          \
-            const float s = v[gi * 8 + i];                                                         \
-            if (s < tau) {                                                                         \
-              my_sc[cnt * RS] = s;                                                                 \
-              my_id[cnt * RS] = base + gi * 8 + i;                                                 \
-              ++cnt;                                                                               \
-            }                                                                                      \
-          }                                                                                        \
-        }                                                                                          \
-        unsigned need = __ballot_sync(0xffffffffu, cnt > CAP - 8);                                 \
-        while (need) {                                                                             \
-          const int r = __ffs(need) - 1;                                                           \
-          need &= need - 1;                                                                        \
-          const int nv = __shfl_sync(0xffffffffu, cnt, r);                                         \
-          const float nt = compact_row<CAP>(bsc, bid, RS, row0 + r, nv, keep, lane);               \
-          if (lane == r) {                                                                         \
-            tau = nt;                                                                              \
-            cnt = keep;                                                                            \
-          }                                                                                        \
-        }                                                                                          \
-      }                                                                                            \
-    }                                                                                              \
+    mc[cc] = fminf(fminf(g_[0], g_[1]), fminf(g_[2], g_[3]));                                      \
   } while (0)
+          ptx::tmem_ld32(t_acc, va);
+          ptx::tmem_ld_wait();
+          ptx::tmem_ld32(t_acc + 32, vb);
+          B200_CHUNKMIN(va, 0);
+          ptx::tmem_ld_wait();
+          ptx::tmem_ld32(t_acc + 64, va);
+          B200_CHUNKMIN(vb, 1);
+          ptx::tmem_ld_wait();
+          ptx::tmem_ld32(t_acc + 96, vb);
+          B200_CHUNKMIN(va, 2);
+          ptx::tmem_ld_wait();
+          B200_CHUNKMIN(vb, 3);
+#undef B200_CHUNKMIN
+          const float mt = fminf(fminf(mc[0], mc[1]), fminf(mc[2], mc[3]));
+          // which 32-column chunks hold a survivor for some row of this warp: one warp-wide OR
+          unsigned hitc = (mc[0] < tau ? 1u : 0u) | (mc[1] < tau ? 2u : 0u) | (mc[2] < tau ? 4u : 0u) | (mc[3] < tau ? 8u : 0u);
+          hitc = (p.mode & 3) == 0 ? __reduce_or_sync(0xffffffffu, hitc) : 0u;
+          if (p.mode & 128) hitc |= 1u;  // experiment: keep the slow-path code hot (chunk 0 rescanned every tile)
+          // ---- slow path (uniform loop over the flagged chunks): read the chunk again, append every
+          // value below the row's threshold with branch-free predicated stores
+          while (hitc) {
+            const int c = __ffs(hitc) - 1;
+            hitc &= hitc - 1;
+            ptx::tmem_ld32(t_acc + c * 32, va);
             ptx::tmem_ld_wait();
-            ptx::tmem_ld32(t_acc + (c + 1) * 32, vb);
-            B200_PROCESS(va, c);
-            ptx::tmem_ld_wait();
-            if (c + 2 < TILE / 32) ptx::tmem_ld32(t_acc + (c + 2) * 32, va);
-            B200_PROCESS(vb, c + 1);
-#undef B200_PROCESS
+            const int base = t * TILE + c * 32;
+            const float mcc = c == 0 ? mc[0] : (c == 1 ? mc[1] : (c == 2 ? mc[2] : mc[3]));
+            // survivors of my row in this chunk as a bit mask: 32 independent compares, four short
+            // OR chains (a running threshold / counter here would serialise ~30 clk per value)
+            unsigned m4[4] = {0u, 0u, 0u, 0u};
+#pragma unroll
+            for (int i = 0; i < 32; ++i) m4[i & 3] |= va[i] < tau ? (1u << i) : 0u;
+            const unsigned mask = (m4[0] | m4[1]) | (m4[2] | m4[3]);
+            const int nh = __popc(mask);
+            if (nh == 1) {
+              // the usual case: one survivor, and it is the chunk minimum I already hold
+              if (cnt < CAP) {
+                my_sc[cnt * RS] = mcc;
+                my_id[cnt * RS] = base + __ffs(mask) - 1;
+                ++cnt;
+              } else {
+                tau = mcc;  // buffer full: drop it, but then nothing >= it may stay a candidate
+              }
+            } else if (nh > 1) {
+#pragma unroll
+              for (int i = 0; i < 32; ++i) {
+                const float s = va[i];
+                const bool lt = s < tau;
+                const bool put = lt && cnt < CAP;
+                if (put) {
+                  my_sc[cnt * RS] = s;
+                  my_id[cnt * RS] = base + i;
+                }
+                tau = (lt && !put) ? s : tau;
+                cnt += put ? 1 : 0;
+              }
+            }
+            unsigned need = __ballot_sync(0xffffffffu, cnt > high);
+            while (need) {
+              const int r = __ffs(need) - 1;
+              need &= need - 1;
+              const int nv = __shfl_sync(0xffffffffu, cnt, r);
+              if (warp == 0 && lane == 0) B200_TRACE(2, (int)it, 2);
+              const float nt = compact_row<CAP>(bsc, bid, RS, row0 + r, nv, keep, lane);
+              if (warp == 0 && lane == 0) B200_TRACE(2, (int)it, 3);
+              if (lane == r) {
+                tau = fminf(tau, nt);
+                cnt = keep;
+              }
+            }
           }
         }
         ptx::tc_fence_before();
         __syncwarp();
-        if (lane == 0) ptx::mbar_arrive(ptx::smem_u32(&bar_acce[a]));
+        if (lane == 0) ptx::mbar_arrive(ptx::smem_u32(&bar_acce[a * 2 + half]));
+        if (warp == 0 && lane == 0) B200_TRACE(2, (int)it, 1);
       }
       // ---- flush this block's candidate lists (coalesced, one row at a time)
       const int64_t q0 = (int64_t)qb * ROWS + row0;
@@ -471,7 +589,7 @@ __global__ void __launch_bounds__((HALVES * 4 + 2) * 32, 1) knn_tc_kernel(const 
 template <int CAP>
 __global__ void __launch_bounds__(256)
 rerank_kernel(const double* __restrict__ x, int64_t n, int d, const double* __restrict__ z, int64_t q,
-              int k, int64_t self_offset, const int32_t* __restrict__ cand_idx,
+              int k, int64_t self_offset, const int32_t* __restrict__ cand_idx, int cstride,
               const int32_t* __restrict__ cand_cnt, const float* __restrict__ cand_tau,
               const QMeta* __restrict__ meta, double scale, double data_cmax,
               int32_t* __restrict__ out_idx, double* __restrict__ out_d2, int32_t* __restrict__ fail_list,
@@ -483,7 +601,7 @@ rerank_kernel(const double* __restrict__ x, int64_t n, int d, const double* __re
   const int w = threadIdx.x >> 5, lane = threadIdx.x & 31;
   const int64_t p = (int64_t)blockIdx.x * 8 + w;
   if (p >= q) return;
-  const int cnt = min(cand_cnt[p], CAP);
+  const int cnt = min(cand_cnt[p], cstride);
   const int self = self_offset >= 0 ? (int)(self_offset + p) : -1;
   const double* zp = z + p * d;
   double dd[U];
@@ -492,7 +610,7 @@ rerank_kernel(const double* __restrict__ x, int64_t n, int d, const double* __re
 #pragma unroll
   for (int u = 0; u < U; ++u) {
     const int j = lane + 32 * u;
-    int c = j < cnt ? cand_idx[p * CAP + j] : -1;
+    int c = j < cnt ? cand_idx[p * cstride + j] : -1;
     const bool ok = c >= 0 && c < n && c != self;
     dd[u] = ok ? sqdist_seq(x + (int64_t)c * d, zp, d) : CUDART_INF;
     id[u] = ok ? c : 0x7fffffff;
@@ -545,7 +663,9 @@ namespace {
 
 int tc_prepare(b200_model* m, cudaStream_t st) {
   TcData& t = m->tc;
-  if (t.ready) return 0;
+  if (t.ready && t.sub == m->tc_sub && t.rg == ((m->tc_flags >> 1) & 1)) return 0;
+  t.sub = m->tc_sub;
+  t.rg = (m->tc_flags >> 1) & 1;
   const int64_t n = m->n;
   const int d = m->d;
   t.K = tc::padK(d);
@@ -583,7 +703,7 @@ int tc_prepare(b200_model* m, cudaStream_t st) {
   }
   t.cmax = mr;
   B200_CUDA(cudaMemsetAsync(bits, 0, 8, st));
-  tc::data_img_kernel<<<(unsigned)((npad + 127) / 128), 128, 0, st>>>(m->x, n, d, t.K, t.mu.as<double>(), t.scale,
+  tc::data_img_kernel<<<(unsigned)((npad + 127) / 128), 128, 0, st>>>(m->x, n, d, t.K, t.sub, t.rg, t.mu.as<double>(), t.scale,
                                                                        t.img.as<__half>(), npad, bits);
   B200_CUDA(cudaGetLastError());
   B200_CUDA(cudaMemcpyAsync(hb, bits, 8, cudaMemcpyDeviceToHost, st));
@@ -602,20 +722,27 @@ struct TcConfig {
 // Candidate capacity and CTA shape for k (+1 when the query's own row is dropped later):
 // a compaction keeps `keep` = k + margin entries of a CAP-slot buffer; CAP leaves room for
 // at least 16 appends between compactions; the B ring gets whatever shared memory is left.
-bool tc_config(int d, int k, int margin, bool self, TcConfig* c) {
+bool tc_config(int d, int k, int margin, bool self, int subrows, int force_halves, TcConfig* c) {
   const int K = tc::padK(d);
   const int base = k + (self ? 1 : 0);
-  int keep = base + (margin < 0 ? std::min(k, 16) : margin);
-  int cap = 32;
-  while (cap < keep + 24 && cap < 128) cap *= 2;
-  if (keep > cap - 24) keep = cap - 24;
+  int keep = base + (margin < 0 ? std::max(4, std::min(k / 2, 16)) : margin);
+  const int caps[4] = {32, 48, 64, 128};
+  int cap = 128;
+  for (int c0 : caps)
+    if (c0 >= keep + 16) {
+      cap = c0;
+      break;
+    }
+  if (keep > cap - 16) keep = cap - 16;
   if (keep < base) return false;
-  const size_t tile = (size_t)tc::TILE * K * 2, sub = (size_t)tc::SUBROWS * K * 2;
+  const size_t tile = (size_t)tc::TILE * K * 2, sub = (size_t)subrows * K * 2;
   const size_t limit = 227 * 1024 - 512;
   for (int halves = 2; halves >= 1; --halves) {
+    if (force_halves && halves != force_halves) continue;
     const size_t fixed = halves * tile + (size_t)cap * (halves * tc::TILE + 1) * 8 + 256;
-    if (fixed + 3 * sub > limit) continue;
-    const int slots = (int)std::min<size_t>(8, (limit - fixed) / sub);
+    if (fixed + (force_halves ? 2 : 3) * sub > limit) continue;
+    int slots = (int)std::min<size_t>(8, (limit - fixed) / sub);
+    slots = slots >= 8 ? 8 : (slots >= 4 ? 4 : 2);  // power of two: ring index by mask/shift
     c->cap = cap;
     c->halves = halves;
     c->slots = slots;
@@ -628,7 +755,7 @@ bool tc_config(int d, int k, int margin, bool self, TcConfig* c) {
 
 template <int CAP, int HALVES>
 int launch_tc(b200_model* m, const tc::KParams& kp, const TcConfig& cfg, bool dbg, cudaStream_t st) {
-  const int threads = (HALVES * 4 + 2) * 32;
+  const int threads = (HALVES * 4 + 3) * 32;
   const int grid = std::min(kp.qblocks, m->sm_count);
   if (dbg) {
     auto kern = tc::knn_tc_kernel<CAP, HALVES, true>;
@@ -647,7 +774,7 @@ int launch_tc(b200_model* m, const tc::KParams& kp, const TcConfig& cfg, bool db
 
 bool tc_supported(const b200_model* m, int k) {
   TcConfig c;
-  return m->d + tc::NORM_SLOTS <= 256 && tc_config(m->d, k, 0, true, &c);
+  return m->d + tc::NORM_SLOTS <= 256 && tc_config(m->d, k, 0, true, 128, 0, &c);
 }
 
 int knn_tc(b200_model* m, const double* z_dev, int64_t q, int k, int64_t self_offset,
@@ -659,7 +786,7 @@ int knn_tc(b200_model* m, const double* z_dev, int64_t q, int k, int64_t self_of
   }
   B200_TRY(tc_prepare(m, st));
   TcConfig cfg;
-  if (!tc_config(m->d, k, m->margin, self_offset >= 0, &cfg)) {
+  if (!tc_config(m->d, k, m->margin, self_offset >= 0, m->tc.sub, m->tc_halves, &cfg)) {
     set_error("tensor kNN path unsupported for d=%d k=%d", m->d, k);
     return 1;
   }
@@ -680,7 +807,7 @@ int knn_tc(b200_model* m, const double* z_dev, int64_t q, int k, int64_t self_of
   float* dbg = m->dbg_scores;
 
   cudaEventRecord(m->ev3, st);
-  tc::query_img_kernel<<<(unsigned)((qpad + 127) / 128), 128, 0, st>>>(z_dev, q, m->d, t.K, t.mu.as<double>(), t.scale,
+  tc::query_img_kernel<<<(unsigned)((qpad + 127) / 128), 128, 0, st>>>(z_dev, q, m->d, t.K, t.rg, t.mu.as<double>(), t.scale,
                                                                         t.ymax, m->zimg.as<__half>(), qpad, meta);
   B200_CUDA(cudaGetLastError());
   cudaEventRecord(m->ev0, st);
@@ -691,15 +818,21 @@ int knn_tc(b200_model* m, const double* z_dev, int64_t q, int k, int64_t self_of
   kp.ntiles = (int)t.tiles;
   kp.qblocks = qblocks;
   kp.slots = cfg.slots;
+  kp.sub = t.sub;
+  kp.flags = m->tc_flags;
   kp.keep = cfg.keep;
   kp.mode = m->tc_mode;
   kp.cand_idx = m->cand.as<int32_t>();
   kp.cand_cnt = cand_cnt;
   kp.cand_tau = cand_tau;
   kp.dbg = dbg;
+  kp.trace = m->dbg_trace;
+  kp.trace_start = m->tc_trace_start;
   int rc = 1;
   const bool dg = dbg != nullptr;
   if (cfg.cap == 32 && cfg.halves == 2) rc = launch_tc<32, 2>(m, kp, cfg, dg, st);
+  else if (cfg.cap == 48 && cfg.halves == 2) rc = launch_tc<48, 2>(m, kp, cfg, dg, st);
+  else if (cfg.cap == 48 && cfg.halves == 1) rc = launch_tc<48, 1>(m, kp, cfg, dg, st);
   else if (cfg.cap == 64 && cfg.halves == 2) rc = launch_tc<64, 2>(m, kp, cfg, dg, st);
   else if (cfg.cap == 128 && cfg.halves == 1) rc = launch_tc<128, 1>(m, kp, cfg, dg, st);
   else if (cfg.cap == 32 && cfg.halves == 1) rc = launch_tc<32, 1>(m, kp, cfg, dg, st);
@@ -707,14 +840,26 @@ int knn_tc(b200_model* m, const double* z_dev, int64_t q, int k, int64_t self_of
   else set_error("tensor kNN: no kernel for cap=%d halves=%d", cfg.cap, cfg.halves);
   B200_TRY(rc);
   cudaEventRecord(m->ev1, st);
+  m->st.last_cap = cfg.cap;
+  m->st.last_keep = cfg.keep;
+  m->st.last_slots = cfg.slots;
+  m->st.last_halves = cfg.halves;
+  if (m->tc_mode != 0) {  // debug ceilings: outputs are meaningless, only stage 1 is timed
+    B200_CUDA(cudaEventSynchronize(m->ev1));
+    float msd = 0;
+    cudaEventElapsedTime(&msd, m->ev0, m->ev1);
+    m->st.ms_stage1 += msd;
+    m->st.launches += 2;
+    return 0;
+  }
   B200_CUDA(cudaMemsetAsync(fail_cnt, 0, 4, st));
   const unsigned rb = (unsigned)((q + 7) / 8);
 #define RERANK(CAPV)                                                                                     \
-  tc::rerank_kernel<CAPV><<<rb, 256, 0, st>>>(m->x, m->n, m->d, z_dev, q, k, self_offset, kp.cand_idx,   \
+  tc::rerank_kernel<CAPV><<<rb, 256, 0, st>>>(m->x, m->n, m->d, z_dev, q, k, self_offset, kp.cand_idx, cfg.cap, \
                                               cand_cnt, cand_tau, meta, t.scale, t.cmax, idx_dev, d2_dev, \
                                               fail_list, fail_cnt)
   if (cfg.cap == 32) RERANK(32);
-  else if (cfg.cap == 64) RERANK(64);
+  else if (cfg.cap <= 64) RERANK(64);
   else RERANK(128);
 #undef RERANK
   B200_CUDA(cudaGetLastError());

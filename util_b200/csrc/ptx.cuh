@@ -10,6 +10,19 @@ __device__ __forceinline__ uint32_t smem_u32(const void* p) {
   return (uint32_t)__cvta_generic_to_shared(p);
 }
 
+// one elected lane of a converged warp (same lane every time while all 32 are active)
+__device__ __forceinline__ bool elect_one() {
+  uint32_t pred;
+  asm volatile(
+      "{\n"
+      ".reg .pred p;\n"
+      "elect.sync _|p, 0xffffffff;\n"
+      "selp.u32 %0, 1, 0, p;\n"
+      "}"
+      : "=r"(pred));
+  return pred != 0;
+}
+
 // ---- mbarrier
 __device__ __forceinline__ void mbar_init(uint32_t bar, uint32_t count) {
   asm volatile("mbarrier.init.shared::cta.b64 [%0], %1;" ::"r"(bar), "r"(count) : "memory");
@@ -27,9 +40,36 @@ __device__ __forceinline__ void mbar_arrive_expect_tx(uint32_t bar, uint32_t byt
   asm volatile("mbarrier.arrive.expect_tx.shared::cta.b64 _, [%0], %1;" ::"r"(bar), "r"(bytes)
                : "memory");
 }
-// try_wait with a suspend-time hint: the thread sleeps in hardware until the phase completes or
-// ~hint_ns elapse, instead of burning issue slots the epilogue warps of the same SM sub-partition need.
-__device__ __forceinline__ bool mbar_try_wait(uint32_t bar, uint32_t parity, uint32_t hint_ns = 100000) {
+__device__ __forceinline__ bool mbar_try_wait(uint32_t bar, uint32_t parity) {
+  uint32_t ok;
+  asm volatile(
+      "{\n"
+      ".reg .pred p;\n"
+      "mbarrier.try_wait.parity.shared::cta.b64 p, [%1], %2;\n"
+      "selp.u32 %0, 1, 0, p;\n"
+      "}"
+      : "=r"(ok)
+      : "r"(bar), "r"(parity)
+      : "memory");
+  return ok != 0;
+}
+// non-blocking probe of a phase
+__device__ __forceinline__ bool mbar_test_wait(uint32_t bar, uint32_t parity) {
+  uint32_t ok;
+  asm volatile(
+      "{\n"
+      ".reg .pred p;\n"
+      "mbarrier.test_wait.parity.shared::cta.b64 p, [%1], %2;\n"
+      "selp.u32 %0, 1, 0, p;\n"
+      "}"
+      : "=r"(ok)
+      : "r"(bar), "r"(parity)
+      : "memory");
+  return ok != 0;
+}
+// try_wait with a suspend-time hint: the thread may sleep in hardware until the phase completes
+// or ~hint_ns elapse instead of re-issuing the probe.
+__device__ __forceinline__ bool mbar_try_wait_hint(uint32_t bar, uint32_t parity, uint32_t hint_ns) {
   uint32_t ok;
   asm volatile(
       "{\n"
@@ -43,12 +83,15 @@ __device__ __forceinline__ bool mbar_try_wait(uint32_t bar, uint32_t parity, uin
   return ok != 0;
 }
 // Bounded wait: a protocol bug must not hang the GPU -- trap after ~5 s instead.
-__device__ __forceinline__ void mbar_wait(uint32_t bar, uint32_t parity) {
+// sleep_ns > 0: back off between probes (roles that wait long -- producer, MMA issuers -- must not
+// burn the issue slots of the epilogue warps sharing their SM sub-partition).
+__device__ __forceinline__ void mbar_wait(bool hint, uint32_t bar, uint32_t parity, uint32_t sleep_ns = 0) {
   if (mbar_try_wait(bar, parity)) return;
   const long long t0 = clock64();
   uint32_t spins = 0;
-  while (!mbar_try_wait(bar, parity)) {
-    if ((++spins & 0xff) == 0 && clock64() - t0 > 10000000000LL) {
+  while (!(hint ? mbar_try_wait_hint(bar, parity, 20000) : mbar_try_wait(bar, parity))) {
+    if (sleep_ns) __nanosleep(sleep_ns);
+    if ((++spins & 0xfff) == 0 && clock64() - t0 > 10000000000LL) {
       printf("b200: mbarrier wait timed out (block %d thread %d bar %u parity %u)\n", (int)blockIdx.x,
              (int)threadIdx.x, bar, parity);
       __trap();
