@@ -79,16 +79,22 @@ class ClockSampler(threading.Thread):
 
 
 def cpu_port(x, y, z, k, seconds=15.0, threads=None):
-    """The oracle (CPU restatement of the reference algorithm) on a bounded query sample."""
+    """The oracle (CPU restatement of the reference algorithm) on a bounded query sample sized to
+    take about `seconds` on all host cores."""
     from oracle import harness as H
     cores = threads or os.cpu_count() or 1
     H.set_threads(cores)
-    probe = z[:max(2, cores)]
-    t0 = time.perf_counter()
-    H.nn_predict(x, probe, k, "shepard")
-    per = (time.perf_counter() - t0) / len(probe)
+    s = max(2, cores)
+    per = None
+    for _ in range(3):  # grow the probe until the rate estimate is trustworthy
+        t0 = time.perf_counter()
+        H.nn_predict(x, z[:s], k, "shepard")
+        dt = time.perf_counter() - t0
+        per = dt / s
+        if dt > 1.0 or s >= len(z):
+            break
+        s = min(len(z), max(s * 4, int(1.5 / max(per, 1e-9))))
     s = int(max(cores, min(len(z), seconds / max(per, 1e-9))))
-    s = max(1, min(s, len(z)))
     t0 = time.perf_counter()
     ids, w, cnt, _ = H.nn_predict(x, z[:s], k, "shepard")
     out = H.weighted_sum(ids, w, cnt, y)
@@ -107,10 +113,16 @@ def run_reference(args, n, q, d, k):
     cores = os.cpu_count() or 1
     H.set_threads(cores)
     # size one step at ~ (120 s budget) / (steps + warmup)
-    probe = z[:max(2, cores)]
-    t0 = time.perf_counter()
-    H.nn_predict(x, probe, k, "shepard")
-    per = (time.perf_counter() - t0) / len(probe)
+    s0 = max(2, cores)
+    per = None
+    for _ in range(3):
+        t0 = time.perf_counter()
+        H.nn_predict(x, z[:s0], k, "shepard")
+        dt0 = time.perf_counter() - t0
+        per = dt0 / s0
+        if dt0 > 1.0 or s0 >= q:
+            break
+        s0 = min(q, max(s0 * 4, int(1.5 / max(per, 1e-9))))
     budget = 120.0 / (args.steps + args.warmup)
     s = int(max(cores, min(q, budget / max(per, 1e-9))))
     for _ in range(args.warmup):
@@ -175,14 +187,16 @@ def main():
     z = np.random.default_rng(1).random((q, d))
     y = fun(x)
 
-    # ---- data layout: rank r owns rows [lo, hi) of the fitted points (all of them when G == 1
-    # or when sharding queries); queries are padded to a multiple of G for the all-to-all.
-    if G > 1 and args.shard == "data":
-        per = (n + G - 1) // G
-        lo, hi = rank * per, min(n, (rank + 1) * per)
+    # ---- data layout: under data sharding rank r owns a contiguous block of the fitted points
+    # (util_b200.sharding); otherwise every rank holds all of them (and, with --shard query, a
+    # slice of the queries).
+    from util_b200 import sharding
+    data_sharded = G > 1 and args.shard == "data"
+    if data_sharded:
+        sh = sharding.DataShardedKNN(x, local)
+        model, lo, hi = sh.model, sh.lo, sh.hi
     else:
-        lo, hi = 0, n
-    model = _lib.Model(x[lo:hi], device=local)
+        model, lo, hi = _lib.Model(x, device=local), 0, n
     model.set_option("knn_path", args.path)
     model.set_option("margin", args.margin)
     model.set_option("tc_mode", args.tc_mode)
@@ -201,30 +215,17 @@ def main():
     y_dev = torch.from_numpy(y).to(dev)
     idx = torch.empty((ql, k), dtype=torch.int32, device=dev)
     d2 = torch.empty((ql, k), dtype=torch.float64, device=dev)
-    data_sharded = G > 1 and args.shard == "data"
-    if data_sharded:
-        assert q % G == 0, "query count must divide by the number of ranks"
-        qm = q // G
-        rd2 = torch.empty((G, qm, k), dtype=torch.float64, device=dev)
-        ridx = torch.empty((G, qm, k), dtype=torch.int32, device=dev)
-        md2 = torch.empty((qm, k), dtype=torch.float64, device=dev)
-        midx = torch.empty((qm, k), dtype=torch.int32, device=dev)
-        out = torch.empty((qm,), dtype=torch.float64, device=dev)
-    else:
-        out = torch.empty((ql,), dtype=torch.float64, device=dev)
+    qm = q // G if data_sharded else ql
+    out = torch.empty((qm,), dtype=torch.float64, device=dev)
+    res = {"out": out, "idx": idx}
     stream = torch.cuda.current_stream().cuda_stream
 
     def step_device():
-        _lib.check(lib.b200_knn_dev(h, z_dev.data_ptr(), ql, k, -1, idx.data_ptr(), d2.data_ptr(), stream))
         if data_sharded:
-            idx.add_(lo)  # local -> global row ids
-            dist.all_to_all_single(rd2.view(-1), d2.view(-1))
-            dist.all_to_all_single(ridx.view(-1), idx.view(-1))
-            _lib.check(lib.b200_merge_topk_dev(local, rd2.data_ptr(), ridx.data_ptr(), G, qm, k,
-                                               md2.data_ptr(), midx.data_ptr(), stream))
-            _lib.check(lib.b200_nn_weights_dev(h, None, qm, k, _lib.SHEPARD, midx.data_ptr(), md2.data_ptr(),
-                                               y_dev.data_ptr(), 1, None, None, None, out.data_ptr(), stream))
+            # local top-k -> NCCL all-to-all of the partial lists -> on-device merge -> weights
+            res["out"], res["idx"], _ = sh.predict(z_dev, k, _lib.SHEPARD, y_dev, stream)
         else:
+            _lib.check(lib.b200_knn_dev(h, z_dev.data_ptr(), ql, k, -1, idx.data_ptr(), d2.data_ptr(), stream))
             _lib.check(lib.b200_nn_weights_dev(h, None, ql, k, _lib.SHEPARD, idx.data_ptr(), d2.data_ptr(),
                                                y_dev.data_ptr(), 1, None, None, None, out.data_ptr(), stream))
 
@@ -280,7 +281,7 @@ def main():
         def step_e2e():
             z_dev.copy_(z_pin, non_blocking=True)
             step_device()
-            out_host.copy_(out, non_blocking=True)
+            out_host.copy_(res["out"], non_blocking=True)
             torch.cuda.synchronize()
         for _ in range(2):
             step_e2e()
@@ -335,8 +336,8 @@ def main():
             line["cpu_baseline"] = {"value": v, "unit": "queries/s", "cores": cores, "kind": "port",
                                     "sample": f"first {s} of {q} queries against all {n} points in {dtc:.1f} s, OpenMP over queries"}
             # the timed GPU outputs must agree with the CPU sample: indices bit-exact, values 1e-12
-            gi = idx[:s].cpu().numpy().astype(np.int64)
-            go = out[:s].cpu().numpy()
+            gi = res["idx"][:s].cpu().numpy().astype(np.int64)
+            go = res["out"][:s].cpu().numpy()
             line["parity_on_sample"] = {"indices_equal": bool(np.array_equal(gi, cids)),
                                         "max_rel_err": float(np.max(np.abs(go - cout) / np.maximum(np.abs(cout), 1e-3)))}
         print(json.dumps(line), flush=True)
