@@ -152,7 +152,9 @@ def main():
     ap.add_argument("--warmup", type=int, default=3)
     ap.add_argument("--impl", default="ours")
     ap.add_argument("--config", default="c5")
-    ap.add_argument("--shard", default="data", choices=["data", "query"])
+    ap.add_argument("--shard", default="auto", choices=["auto", "data", "query"],
+                    help="N>1: shard the fitted points (NCCL all-to-all + merge) or the queries; auto = "
+                         "queries when the data set fits one GPU's HBM (north_star), else data")
     ap.add_argument("--cpu-seconds", type=float, default=15.0)
     ap.add_argument("--no-cpu", action="store_true")
     ap.add_argument("--no-e2e", action="store_true", help="kernel experiments only: skip the host-buffer leg")
@@ -164,6 +166,8 @@ def main():
     ap.add_argument("--tc-mode", type=int, default=0, help="debug ceilings: 1 TMEM reads only, 2 no epilogue")
     args = ap.parse_args()
     n, q, d, k = CONFIGS[args.config]
+    if args.shard == "auto":
+        args.shard = "query" if n * d * 8 < 60e9 else "data"
     if args.warmup < 3:
         args.warmup = 3
 

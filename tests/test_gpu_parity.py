@@ -62,7 +62,8 @@ def test_nn_demo_latin(ub):
 
 
 @pytest.mark.parametrize("n,q,d,k", [(3000, 257, 3, 4), (1000, 1, 5, 1), (517, 300, 7, 17),
-                                     (200, 50, 2, 200), (5000, 64, 70, 9), (900, 33, 130, 5)])
+                                     (200, 50, 2, 200), (5000, 64, 70, 9), (900, 33, 130, 5),
+                                     (200000, 20, 16, 16), (150000, 50, 64, 33)])  # few queries: ~1000-way split + warp merge
 def test_knn_exact_vs_oracle(ub, oracle, n, q, d, k):
     from util_b200 import _lib
     x, z = synth(n, q, d)

@@ -156,6 +156,80 @@ __global__ void merge_topk_kernel(const double* __restrict__ pd2, const int32_t*
   }
 }
 
+// Same merge, one WARP per query, for many parts (the split scan of a few queries): lane l owns
+// lists l, l+32, ... and keeps their current heads in local arrays; each of the k rounds is a
+// lane-local minimum, a warp arg-min by (d2, idx), and one load by the winning lane.
+__global__ void __launch_bounds__(128)
+merge_topk_warp_kernel(const double* __restrict__ pd2, const int32_t* __restrict__ pidx, int parts,
+                       int64_t q, int k, const int32_t* __restrict__ qsel, double* __restrict__ od2,
+                       int32_t* __restrict__ oidx) {
+  const int lane = threadIdx.x & 31;
+  const int64_t slot = ((int64_t)blockIdx.x * blockDim.x + threadIdx.x) >> 5;
+  if (slot >= q) return;
+  const int64_t p = qsel ? (int64_t)qsel[slot] : slot;
+  constexpr int L = 32;  // parts <= 1024
+  double hd[L];
+  int hi[L], hp[L];
+#pragma unroll 1
+  for (int l = 0; l < L; ++l) {
+    const int s = lane + 32 * l;
+    hd[l] = CUDART_INF;
+    hi[l] = 0x7fffffff;
+    hp[l] = 0;
+    if (s < parts) {
+      const int64_t o = ((int64_t)s * q + slot) * k;
+      const int id = pidx[o];
+      if (id >= 0) {
+        hd[l] = pd2[o];
+        hi[l] = id;
+      }
+    }
+  }
+  const int nl = (parts + 31) / 32;
+  for (int j = 0; j < k; ++j) {
+    double bd = CUDART_INF;
+    int bi = 0x7fffffff, bl = 0;
+#pragma unroll 1
+    for (int l = 0; l < nl; ++l)
+      if (hd[l] < bd || (hd[l] == bd && hi[l] < bi)) {
+        bd = hd[l];
+        bi = hi[l];
+        bl = l;
+      }
+    double wd = bd;
+    int wi = bi, wl = lane;
+#pragma unroll
+    for (int o = 16; o > 0; o >>= 1) {
+      const double od = __shfl_xor_sync(0xffffffffu, wd, o);
+      const int oi = __shfl_xor_sync(0xffffffffu, wi, o);
+      const int ol = __shfl_xor_sync(0xffffffffu, wl, o);
+      if (od < wd || (od == wd && oi < wi)) {
+        wd = od;
+        wi = oi;
+        wl = ol;
+      }
+    }
+    if (lane == 0) {
+      oidx[p * k + j] = wi == 0x7fffffff ? -1 : wi;
+      if (od2) od2[p * k + j] = wd;
+    }
+    if (lane == wl && wi != 0x7fffffff) {  // advance the list that supplied the winner
+      const int s = lane + 32 * bl;
+      const int h = ++hp[bl];
+      hd[bl] = CUDART_INF;
+      hi[bl] = 0x7fffffff;
+      if (h < k) {
+        const int64_t o = ((int64_t)s * q + slot) * k + h;
+        const int id = pidx[o];
+        if (id >= 0) {
+          hd[bl] = pd2[o];
+          hi[bl] = id;
+        }
+      }
+    }
+  }
+}
+
 template <int KMAX>
 int launch_exact(b200_model* m, const double* z, int64_t q, int k, int64_t self_offset,
                  const int32_t* qsel, int32_t* idx, double* d2, cudaStream_t st) {
@@ -163,8 +237,13 @@ int launch_exact(b200_model* m, const double* z, int64_t q, int k, int64_t self_
   const int64_t n = m->n;
   // block size / tile size from the shared-memory budget
   int QB = d <= 96 ? 128 : (d <= 256 ? 64 : 32);
+  // few queries (the fallback for uncertified tensor-path queries): one warp of queries per block and
+  // small tiles, so that many blocks share an SM and the data range can be split ~1000 ways
+  const bool few = q <= 64;
+  if (few && q <= 32) QB = 32;
+  else if (few && QB > 64) QB = 64;
   size_t zbytes = (size_t)d * QB * 8;
-  int tile_pts = (int)((160 * 1024 - zbytes) / ((size_t)d * 8));
+  int tile_pts = (int)(((few ? 56 : 160) * 1024 - zbytes) / ((size_t)d * 8));
   if (tile_pts > 256) tile_pts = 256;
   tile_pts &= ~3;
   if (tile_pts < 4) {
@@ -175,11 +254,11 @@ int launch_exact(b200_model* m, const double* z, int64_t q, int k, int64_t self_
   const int64_t qblocks = (q + QB - 1) / QB;
   // split the data range so that the grid covers >= 2 waves of the SMs
   int64_t S = 1;
-  const int64_t want = 2 * (int64_t)m->sm_count;
+  const int64_t want = (few ? 8 : 2) * (int64_t)m->sm_count;
   if (qblocks < want) S = (want + qblocks - 1) / qblocks;
   const int64_t max_s = (n + (int64_t)4 * tile_pts - 1) / ((int64_t)4 * tile_pts);
   if (S > max_s) S = max_s;
-  if (S > 512) S = 512;
+  if (S > 1024) S = 1024;
   if (S < 1) S = 1;
   int64_t split_len = (n + S - 1) / S;
   split_len = (split_len + 3) & ~(int64_t)3;
@@ -210,7 +289,10 @@ int launch_exact(b200_model* m, const double* z, int64_t q, int k, int64_t self_
   B200_CUDA(cudaGetLastError());
   m->st.launches += 1;
   if (!direct) {
-    merge_topk_kernel<<<(unsigned)((q + 127) / 128), 128, 0, st>>>(od, oi, (int)S, q, k, qsel, d2, idx);
+    if (S > 32)
+      merge_topk_warp_kernel<<<(unsigned)((q * 32 + 127) / 128), 128, 0, st>>>(od, oi, (int)S, q, k, qsel, d2, idx);
+    else
+      merge_topk_kernel<<<(unsigned)((q + 127) / 128), 128, 0, st>>>(od, oi, (int)S, q, k, qsel, d2, idx);
     B200_CUDA(cudaGetLastError());
     m->st.launches += 1;
   }
