@@ -221,13 +221,13 @@ def main():
     d2 = torch.empty((ql, k), dtype=torch.float64, device=dev)
     qm = q // G if data_sharded else ql
     out = torch.empty((qm,), dtype=torch.float64, device=dev)
-    res = {"out": out, "idx": idx}
+    last = {"out": out, "idx": idx}
     stream = torch.cuda.current_stream().cuda_stream
 
     def step_device():
         if data_sharded:
             # local top-k -> NCCL all-to-all of the partial lists -> on-device merge -> weights
-            res["out"], res["idx"], _ = sh.predict(z_dev, k, _lib.SHEPARD, y_dev, stream)
+            last["out"], last["idx"], _ = sh.predict(z_dev, k, _lib.SHEPARD, y_dev, stream)
         else:
             _lib.check(lib.b200_knn_dev(h, z_dev.data_ptr(), ql, k, -1, idx.data_ptr(), d2.data_ptr(), stream))
             _lib.check(lib.b200_nn_weights_dev(h, None, ql, k, _lib.SHEPARD, idx.data_ptr(), d2.data_ptr(),
@@ -285,7 +285,7 @@ def main():
         def step_e2e():
             z_dev.copy_(z_pin, non_blocking=True)
             step_device()
-            out_host.copy_(res["out"], non_blocking=True)
+            out_host.copy_(last["out"], non_blocking=True)
             torch.cuda.synchronize()
         for _ in range(2):
             step_e2e()
@@ -340,8 +340,8 @@ def main():
             line["cpu_baseline"] = {"value": v, "unit": "queries/s", "cores": cores, "kind": "port",
                                     "sample": f"first {s} of {q} queries against all {n} points in {dtc:.1f} s, OpenMP over queries"}
             # the timed GPU outputs must agree with the CPU sample: indices bit-exact, values 1e-12
-            gi = res["idx"][:s].cpu().numpy().astype(np.int64)
-            go = res["out"][:s].cpu().numpy()
+            gi = last["idx"][:s].cpu().numpy().astype(np.int64)
+            go = last["out"][:s].cpu().numpy()
             line["parity_on_sample"] = {"indices_equal": bool(np.array_equal(gi, cids)),
                                         "max_rel_err": float(np.max(np.abs(go - cout) / np.maximum(np.abs(cout), 1e-3)))}
         print(json.dumps(line), flush=True)
