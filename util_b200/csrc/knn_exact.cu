@@ -243,7 +243,13 @@ int launch_exact(b200_model* m, const double* z, int64_t q, int k, int64_t self_
   if (few && q <= 32) QB = 32;
   else if (few && QB > 64) QB = 64;
   size_t zbytes = (size_t)d * QB * 8;
-  int tile_pts = (int)(((few ? 56 : 160) * 1024 - zbytes) / ((size_t)d * 8));
+  size_t budget = few ? 56 * 1024 : 160 * 1024;
+  if (budget < zbytes + (size_t)16 * d * 8) budget = std::min<size_t>(200 * 1024, zbytes + (size_t)16 * d * 8);
+  if (budget <= zbytes) {
+    set_error("knn_exact: dimension %d too large for the shared-memory tiling", d);
+    return 3;
+  }
+  int tile_pts = (int)((budget - zbytes) / ((size_t)d * 8));
   if (tile_pts > 256) tile_pts = 256;
   tile_pts &= ~3;
   if (tile_pts < 4) {
