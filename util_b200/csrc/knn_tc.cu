@@ -214,42 +214,49 @@ __device__ __forceinline__ float min3(float a, float b, float c) { return fminf(
 // Trim buffer column `col` (one query row) to its `keep` best entries; returns the new
 // threshold (the keep-th smallest score).  Warp-cooperative, all lanes must call.
 // bsc/bid are [CAP][RS] (slot-major, RS = rows + 1 keeps slot walks conflict-free).
+// Rank by counting: lane l ranks entries l and l+32 against broadcast reads of all n entries.
+// Equal scores would share a rank; they are detected by the rank checksum and re-ranked with
+// the slot number as tie-break.
 template <int CAP>
-__device__ __noinline__ float compact_row(float* bsc, int* bid, int RS, int col, int n_valid, int keep,
-                                          int lane) {
+__device__ __forceinline__ float compact_row(float* bsc, int* bid, int RS, int col, int n_valid, int keep,
+                                             int lane) {
   constexpr int U = (CAP + 31) / 32;
   float sc[U];
-  int id[U], rank[U], eq[U];
+  int id[U], rank[U];
 #pragma unroll
   for (int u = 0; u < U; ++u) {
     const int j = lane + 32 * u;
     sc[u] = j < n_valid ? bsc[j * RS + col] : CUDART_INF_F;
     id[u] = j < n_valid ? bid[j * RS + col] : 0;
     rank[u] = 0;
-    eq[u] = 0;
   }
   const float* ps = bsc + col;
   int i = 0;
-  for (; i + 4 <= n_valid; i += 4) {
-    const float s0 = ps[(i + 0) * RS], s1 = ps[(i + 1) * RS], s2 = ps[(i + 2) * RS], s3 = ps[(i + 3) * RS];
+  for (; i + 8 <= n_valid; i += 8) {
+    float s8[8];
+#pragma unroll
+    for (int e = 0; e < 8; ++e) s8[e] = ps[(i + e) * RS];
 #pragma unroll
     for (int u = 0; u < U; ++u) {
-      rank[u] += (s0 < sc[u]) + (s1 < sc[u]) + (s2 < sc[u]) + (s3 < sc[u]);
-      eq[u] += (s0 == sc[u]) + (s1 == sc[u]) + (s2 == sc[u]) + (s3 == sc[u]);
+      int r0 = 0, r1 = 0;
+#pragma unroll
+      for (int e = 0; e < 8; e += 2) {
+        r0 += s8[e] < sc[u] ? 1 : 0;
+        r1 += s8[e + 1] < sc[u] ? 1 : 0;
+      }
+      rank[u] += r0 + r1;
     }
   }
   for (; i < n_valid; ++i) {
     const float s0 = ps[i * RS];
 #pragma unroll
-    for (int u = 0; u < U; ++u) {
-      rank[u] += (s0 < sc[u]);
-      eq[u] += (s0 == sc[u]);
-    }
+    for (int u = 0; u < U; ++u) rank[u] += s0 < sc[u] ? 1 : 0;
   }
-  bool tie = false;
+  int sum = 0;
 #pragma unroll
-  for (int u = 0; u < U; ++u) tie |= (lane + 32 * u < n_valid) && eq[u] > 1;
-  if (__any_sync(0xffffffffu, tie)) {  // equal scores: redo with the slot number as tie-break
+  for (int u = 0; u < U; ++u) sum += (lane + 32 * u < n_valid) ? rank[u] : 0;
+  sum = __reduce_add_sync(0xffffffffu, sum);
+  if (sum != n_valid * (n_valid - 1) / 2) {  // equal scores: redo with the slot number as tie-break
 #pragma unroll
     for (int u = 0; u < U; ++u) rank[u] = 0;
     for (i = 0; i < n_valid; ++i) {
@@ -469,9 +476,13 @@ __global__ void __launch_bounds__((HALVES * 4 + 3) * 32, 1) knn_tc_kernel(const 
         ptx::mbar_wait(hint, ptx::smem_u32(&bar_accf[a * 2 + half]), aph);
         if (warp == 0 && lane == 0) B200_TRACE(2, (int)it, 0);
         ptx::tc_fence_after();
-        // compaction trigger: while hits are dense (first tiles) keep room for a whole 32-column chunk,
-        // later 8 free slots suffice (a rare overflow only lowers tau, see below)
-        const int high = t < 16 ? max(keep, CAP - 32) : CAP - 8;
+        // compaction trigger: 8 free slots suffice (an overflow only lowers tau, see below)
+        // Compaction trigger.  Normally 8 free slots suffice: a rare overflow only drops the survivor and
+        // lowers tau to it (see below).  In the first two tiles nearly every value beats tau, and a
+        // survivor dropped there is, with probability ~keep/n each, one of the final neighbours (that
+        // query then fails its certificate and is redone exactly), so there the buffer is trimmed
+        // whenever a whole 32-column chunk would no longer fit.
+        const int high = t < 2 ? max(keep, CAP - 32) : CAP - 8;
         const uint32_t t_acc = t_lane + a * ACC_COLS;
         if ((p.mode & 3) != 2) {
           float va[32], vb[32], mc[4];
