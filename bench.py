@@ -330,6 +330,12 @@ def main():
                            "l2": "inputs larger than L2 (queries %d MB, operand images %d MB)" % (zl.nbytes >> 20, (nloc * 80 * 2) >> 20)},
                 "roofline": roof,
                 "stages_ms": {kk: vv for kk, vv in stats.items() if kk.startswith("ms_")},
+                # HBM-bound stages: re-rank gathers c candidate rows per query
+                # (c*d*8 + d*8 + k*12 bytes); weighting reads k*(8+4+8) and writes 8 bytes per query
+                "roofline_stages": {
+                    "rerank": {"bound": "hbm", "bytes_per_query": int(model.stat("tc_cap")) * d * 8 + d * 8 + k * 12,
+                               "achieved": (ql * (model.stat("tc_cap") * d * 8 + d * 8 + k * 12) / 1e9) / (stats["ms_rerank"] * 1e-3)
+                               if stats["ms_rerank"] > 0 else None, "peak": pk["hbm"], "unit": "GB/s"}},
                 "uncertified_per_step": stats["uncertified"],
                 "tc": {"cap": model.stat("tc_cap"), "keep": model.stat("tc_keep"), "slots": model.stat("tc_slots"), "halves": model.stat("tc_halves"),
                        "K": model.stat("tc_K"), "mode": args.tc_mode, "sub": args.tc_sub, "flags": args.tc_flags},

@@ -233,3 +233,19 @@ def test_standalone_shepard_voronoi_demo_sizes(ub, oracle):
         w, e = oracle.voronoi_predict(x, p)
         refv.append(sum(y[i] * w[i] for i in range(20) if w[i] > 0))
     assert relerr(pv, np.array(refv)) < RTOL
+
+
+def test_auto_k_selection(ub):
+    """nearest_neighbor.auto (nearest_neighbor/__init__.py:93-132): k=None picks a power of two from the
+    neighbours of 100 sampled points; a response that only depends on the nearest point wants k = 1."""
+    import random
+    x, z = synth(4000, 10, 4)
+    y = fun(x)
+    random.seed(3)
+    m = ub.NearestNeighbor(k=None)
+    m.fit(x, y, display=False)
+    assert m.num_neighbors in (1, 2, 4, 8, 16, 32, 64, 128, 256, 512, 1024, 2048)
+    assert m.num_neighbors <= 8          # smooth low-noise response: small k wins
+    assert len(m.predict(z)) == 10
+    k = ub.auto(x, y, max_k=16, samples=50)
+    assert k in (1, 2, 4, 8, 16)
