@@ -740,7 +740,7 @@ bool tc_config(int d, int k, int margin, bool self, int subrows, int force_halve
   const int caps[4] = {32, 48, 64, 128};
   int cap = 128;
   for (int c0 : caps)
-    if (c0 >= keep + 16) {
+    if (c0 >= keep + 20) {
       cap = c0;
       break;
     }

@@ -229,6 +229,10 @@ lshep_eval_kernel(const double* __restrict__ x, const double* __restrict__ f, co
   double* as = xs + (size_t)tile_pts * d;   // [tile][d]   gradients, later unit normals [tile][d+1]
   double* fs = as + (size_t)tile_pts * (d + 1);
   double* rs = fs + tile_pts;
+  // squared-radius band: outside [lo, hi) the test sqrt(acc) < rk is decided without the square root
+  // (it is correctly rounded and monotone; the band is ~100 ulp wide), inside it falls back to sqrt
+  double* r2lo = rs + tile_pts;
+  double* r2hi = r2lo + tile_pts;
   const int t = threadIdx.x;
   const int64_t p = (int64_t)blockIdx.x * LS_QB + t;
   const bool live = p < q;
@@ -241,7 +245,7 @@ lshep_eval_kernel(const double* __restrict__ x, const double* __restrict__ f, co
   slope[DMAX] = 0.0;
   double D[DMAX + 1];
   int DI[DMAX + 1];
-#pragma unroll
+#pragma unroll 1
   for (int j = 0; j <= DMAX; ++j) { D[j] = 0.0; DI[j] = 0; }
   int J = 0, c = 0, hit = -1;
   double temp = 0.0, sw = 0.0, sv = 0.0;
@@ -251,7 +255,13 @@ lshep_eval_kernel(const double* __restrict__ x, const double* __restrict__ f, co
     const int tc = (int)imin64(tile_pts, n - base);
     __syncthreads();
     for (int e = t; e < tc * d; e += LS_QB) { xs[e] = x[base * d + e]; as[e] = a[base * d + e]; }
-    for (int e = t; e < tc; e += LS_QB) { fs[e] = f[base + e]; rs[e] = __dmul_rn(rw[base + e], radius); }
+    for (int e = t; e < tc; e += LS_QB) {
+      const double rk = __dmul_rn(rw[base + e], radius);
+      fs[e] = f[base + e];
+      rs[e] = rk;
+      r2lo[e] = rk * rk * (1.0 - 1e-14);
+      r2hi[e] = rk * rk * (1.0 + 1e-14);
+    }
     __syncthreads();
     if (!live || hit >= 0) continue;
     for (int i = 0; i < tc; ++i) {
@@ -264,9 +274,10 @@ lshep_eval_kernel(const double* __restrict__ x, const double* __restrict__ f, co
           df[j] = __dsub_rn(zq[j], xr[j]);
           acc = __dadd_rn(acc, __dmul_rn(df[j], df[j]));
         }
-      const double dist = sqrt(acc);  // :426
       const double rk = rs[i];
-      if (dist < rk) {
+      const bool inside = acc < r2lo[i] ? true : (acc >= r2hi[i] ? false : sqrt(acc) < rk);  // DIST < RW(K), :427
+      if (inside) {
+        const double dist = sqrt(acc);  // :426
         if (__dsub_rn(rk, dist) == rk) { hit = (int)(base + i); break; }  // :428-431
         const double u = __ddiv_rn(__dsub_rn(rk, dist), __dmul_rn(rk, dist));
         const double w = __dmul_rn(u, u);  // :433
@@ -284,16 +295,15 @@ lshep_eval_kernel(const double* __restrict__ x, const double* __restrict__ f, co
         sv = fma(w, nv, sv);
         ++c;
       } else if (c == 0) {
-        const double w = __ddiv_rn(1.0, dist);  // :439-445
+        const double w = __ddiv_rn(1.0, sqrt(acc));  // :439-445
         if (w > temp) {
-#pragma unroll
-          for (int u2 = 0; u2 <= DMAX; ++u2)
-            if (u2 == J) { D[u2] = w; DI[u2] = (int)(base + i); }
+          D[J] = w;  // rare bookkeeping (only until the first contributor): local memory is fine
+          DI[J] = (int)(base + i);
           int jm = 0;
           double dm = D[0];
-#pragma unroll
-          for (int u2 = 1; u2 <= DMAX; ++u2)
-            if (u2 < m1 && D[u2] < dm) { dm = D[u2]; jm = u2; }
+#pragma unroll 1
+          for (int u2 = 1; u2 < m1; ++u2)
+            if (D[u2] < dm) { dm = D[u2]; jm = u2; }
           J = jm;
           temp = dm;
         }
@@ -309,12 +319,10 @@ lshep_eval_kernel(const double* __restrict__ x, const double* __restrict__ f, co
     } else if (c == 0) {  // :450-454
       e = 1;
       double sd = 0.0;
-#pragma unroll
-      for (int u2 = 0; u2 <= DMAX; ++u2)
-        if (u2 < m1) { D[u2] = __dmul_rn(D[u2], D[u2]); sd = __dadd_rn(sd, D[u2]); }
-#pragma unroll
-      for (int u2 = 0; u2 <= DMAX; ++u2)
-        if (u2 < m1) val = __dadd_rn(val, __dmul_rn(__ddiv_rn(D[u2], sd), f[DI[u2]]));
+#pragma unroll 1
+      for (int u2 = 0; u2 < m1; ++u2) { D[u2] = __dmul_rn(D[u2], D[u2]); sd = __dadd_rn(sd, D[u2]); }
+#pragma unroll 1
+      for (int u2 = 0; u2 < m1; ++u2) val = __dadd_rn(val, __dmul_rn(__ddiv_rn(D[u2], sd), f[DI[u2]]));
     } else {
       val = sv / sw;  // :456-457 up to summation order
       need2 = true;
@@ -329,10 +337,15 @@ lshep_eval_kernel(const double* __restrict__ x, const double* __restrict__ f, co
   // second pass: IER = 2 iff some contributing normal has cosine < 0.9 with the mean (:460-469)
   for (int64_t base = 0; base < n; base += tile_pts) {
     const int tc = (int)imin64(tile_pts, n - base);
-    __syncthreads();
+    if (__syncthreads_and(!need2 || e == 2)) break;  // every query of the block is decided
     for (int e2 = t; e2 < tc * d; e2 += LS_QB) xs[e2] = x[base * d + e2];
     for (int e2 = t; e2 < tc * (d + 1); e2 += LS_QB) as[e2] = ah[base * (d + 1) + e2];
-    for (int e2 = t; e2 < tc; e2 += LS_QB) rs[e2] = __dmul_rn(rw[base + e2], radius);
+    for (int e2 = t; e2 < tc; e2 += LS_QB) {
+      const double rk = __dmul_rn(rw[base + e2], radius);
+      rs[e2] = rk;
+      r2lo[e2] = rk * rk * (1.0 - 1e-14);
+      r2hi[e2] = rk * rk * (1.0 + 1e-14);
+    }
     __syncthreads();
     if (!need2 || e == 2) continue;
     for (int i = 0; i < tc; ++i) {
@@ -344,7 +357,7 @@ lshep_eval_kernel(const double* __restrict__ x, const double* __restrict__ f, co
           const double dfj = __dsub_rn(zq[j], xr[j]);
           acc = __dadd_rn(acc, __dmul_rn(dfj, dfj));
         }
-      if (sqrt(acc) < rs[i]) {
+      if (acc < r2lo[i] ? true : (acc >= r2hi[i] ? false : sqrt(acc) < rs[i])) {
         const double* hr = as + (size_t)i * (d + 1);
         double dp = slope[DMAX] * hr[d];
 #pragma unroll
@@ -459,7 +472,7 @@ int lshep_predict(b200_model* m, double radius, const double* z_dev, int64_t q, 
   const int64_t n = m->n;
   const int d = m->d, r = m->lshep_r;
   int tile_pts = 256;
-  const size_t smem = ((size_t)tile_pts * (2 * d + 3)) * 8;
+  const size_t smem = ((size_t)tile_pts * (2 * d + 5)) * 8;
   const unsigned gb = (unsigned)((q + LS_QB - 1) / LS_QB);
   for (int c = 0; c < r; ++c) {
     const double* fc = m->lf.as<double>() + (size_t)c * n;
@@ -472,9 +485,14 @@ int lshep_predict(b200_model* m, double radius, const double* z_dev, int64_t q, 
     kern<<<gb, LS_QB, smem, st>>>(m->x, fc, ac, hc, m->rw.as<double>(), radius, n, d, z_dev, q,        \
                                   tile_pts, out_dev + c, ier_dev + c, r);                             \
   } while (0)
-    if (d <= 4) LS_LAUNCH(4);
+    if (d <= 2) LS_LAUNCH(2);
+    else if (d <= 4) LS_LAUNCH(4);
+    else if (d <= 6) LS_LAUNCH(6);
     else if (d <= 8) LS_LAUNCH(8);
+    else if (d <= 10) LS_LAUNCH(10);
+    else if (d <= 12) LS_LAUNCH(12);
     else if (d <= 16) LS_LAUNCH(16);
+    else if (d <= 24) LS_LAUNCH(24);
     else if (d <= 32) LS_LAUNCH(32);
     else LS_LAUNCH(64);
 #undef LS_LAUNCH

@@ -33,6 +33,7 @@ __global__ void rw_from_knn_kernel(const double* __restrict__ d2, int64_t n, int
 constexpr int SM_QB = 128;   // queries per block
 constexpr int SM_FB = 72;    // fallback slots kept per thread (M+1 <= SM_FB)
 
+template <int DMAX>  // query coordinates live in registers: DMAX >= d, loops fully unrolled
 __global__ void __launch_bounds__(SM_QB)
 shepmod_eval_kernel(const double* __restrict__ x, const double* __restrict__ rw, int64_t n, int d,
                     const double* __restrict__ z, int64_t q, int cap, int tile_pts,
@@ -40,17 +41,17 @@ shepmod_eval_kernel(const double* __restrict__ x, const double* __restrict__ rw,
                     int32_t* __restrict__ ier, const double* __restrict__ y, int r,
                     double* __restrict__ out) {
   extern __shared__ double sm[];
-  double* zs = sm;                        // [d][QB]
-  double* xs = zs + (size_t)d * SM_QB;    // [tile_pts][d]
+  double* xs = sm;                        // [tile_pts][d]
   double* rs = xs + (size_t)tile_pts * d; // [tile_pts]
+  // squared-radius band: outside [lo, hi) the test sqrt(a) < rk is decided without the square root
+  double* r2lo = rs + tile_pts;
+  double* r2hi = r2lo + tile_pts;
   const int t = threadIdx.x;
   const int64_t p = (int64_t)blockIdx.x * SM_QB + t;
   const bool live = p < q;
-  for (int e = t; e < d * SM_QB; e += SM_QB) {
-    const int qq = e / d, j = e - qq * d;
-    const int64_t pp = (int64_t)blockIdx.x * SM_QB + qq;
-    zs[(size_t)j * SM_QB + qq] = pp < q ? z[pp * d + j] : 0.0;
-  }
+  double zq[DMAX];
+#pragma unroll
+  for (int j = 0; j < DMAX; ++j) zq[j] = (live && j < d) ? z[p * d + j] : 0.0;
   const int m1 = d + 1;
   double D[SM_FB];
   int DI[SM_FB];
@@ -67,20 +68,27 @@ shepmod_eval_kernel(const double* __restrict__ x, const double* __restrict__ rw,
     const int tc = (int)imin64(tile_pts, n - base);
     __syncthreads();
     for (int e = t; e < tc * d; e += SM_QB) xs[e] = x[base * d + e];
-    for (int e = t; e < tc; e += SM_QB) rs[e] = rw[base + e];
+    for (int e = t; e < tc; e += SM_QB) {
+      const double rk = rw[base + e];
+      rs[e] = rk;
+      r2lo[e] = rk * rk * (1.0 - 1e-14);
+      r2hi[e] = rk * rk * (1.0 + 1e-14);
+    }
     __syncthreads();
     if (!live || hit >= 0) continue;
     for (int i = 0; i < tc; ++i) {
       const double* xr = xs + (size_t)i * d;
       double a = 0.0;
-#pragma unroll 4
-      for (int j = 0; j < d; ++j) {
-        const double df = __dsub_rn(zs[(size_t)j * SM_QB + t], xr[j]);
-        a = __dadd_rn(a, __dmul_rn(df, df));
-      }
-      const double dist = sqrt(a);  // :132
+#pragma unroll
+      for (int j = 0; j < DMAX; ++j)
+        if (j < d) {
+          const double df = __dsub_rn(zq[j], xr[j]);
+          a = __dadd_rn(a, __dmul_rn(df, df));
+        }
       const double rk = rs[i];
-      if (dist < rk) {
+      const bool inside = a < r2lo[i] ? true : (a >= r2hi[i] ? false : sqrt(a) < rk);  // DIST < RW(K), :134
+      if (inside) {
+        const double dist = sqrt(a);  // :132
         if (__dsub_rn(rk, dist) == rk) {  // :136-140
           hit = (int)(base + i);
           break;
@@ -94,7 +102,7 @@ shepmod_eval_kernel(const double* __restrict__ x, const double* __restrict__ rw,
         s = __dadd_rn(s, w);
         ++c;
       } else if (c == 0) {
-        const double w = __ddiv_rn(1.0, dist);  // :150
+        const double w = __ddiv_rn(1.0, sqrt(a));  // :150
         if (w > temp) {                          // :152-158
           D[J] = w;
           DI[J] = (int)(base + i);
@@ -200,14 +208,27 @@ int shepmod_predict(b200_model* m, const double* z_dev, int64_t q, int cap, int3
     set_error("shepmod_predict: cap=%d must be at least M+1=%d", cap, d + 1);
     return 1;
   }
-  const size_t zb = (size_t)d * SM_QB * 8;
-  int tile_pts = (int)((128 * 1024 - zb) / ((size_t)(d + 1) * 8));
+  int tile_pts = (int)((96 * 1024) / ((size_t)(d + 3) * 8));
   if (tile_pts > 512) tile_pts = 512;
-  const size_t smem = zb + (size_t)tile_pts * (d + 1) * 8;
-  B200_CUDA(cudaFuncSetAttribute(shepmod_eval_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
-  shepmod_eval_kernel<<<(unsigned)((q + SM_QB - 1) / SM_QB), SM_QB, smem, st>>>(
-      m->x, m->rw.as<double>(), m->n, d, z_dev, q, cap, tile_pts, ids_dev, wts_dev, cnt_dev, ier_dev,
-      y_dev, r, y_dev ? out_dev : nullptr);
+  const size_t smem = (size_t)tile_pts * (d + 3) * 8;
+  const unsigned gb = (unsigned)((q + SM_QB - 1) / SM_QB);
+#define SM_LAUNCH(DM)                                                                              \
+  do {                                                                                             \
+    auto kern = shepmod_eval_kernel<DM>;                                                           \
+    B200_CUDA(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem)); \
+    kern<<<gb, SM_QB, smem, st>>>(m->x, m->rw.as<double>(), m->n, d, z_dev, q, cap, tile_pts, ids_dev, \
+                                  wts_dev, cnt_dev, ier_dev, y_dev, r, y_dev ? out_dev : nullptr);  \
+  } while (0)
+  if (d <= 2) SM_LAUNCH(2);
+  else if (d <= 4) SM_LAUNCH(4);
+  else if (d <= 8) SM_LAUNCH(8);
+  else if (d <= 12) SM_LAUNCH(12);
+  else if (d <= 16) SM_LAUNCH(16);
+  else if (d <= 24) SM_LAUNCH(24);
+  else if (d <= 32) SM_LAUNCH(32);
+  else if (d <= 48) SM_LAUNCH(48);
+  else SM_LAUNCH(72);
+#undef SM_LAUNCH
   B200_CUDA(cudaGetLastError());
   m->st.launches += 1;
   return 0;
