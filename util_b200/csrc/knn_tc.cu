@@ -623,7 +623,7 @@ rerank_kernel(const double* __restrict__ x, int64_t n, int d, const double* __re
     const int j = lane + 32 * u;
     int c = j < cnt ? cand_idx[p * cstride + j] : -1;
     const bool ok = c >= 0 && c < n && c != self;
-    dd[u] = ok ? sqdist_seq(x + (int64_t)c * d, zp, d) : CUDART_INF;
+    dd[u] = ok ? sqdist_seq_wide(x + (int64_t)c * d, zp, d) : CUDART_INF;
     id[u] = ok ? c : 0x7fffffff;
     s_d2[w][j] = dd[u];
     s_id[w][j] = id[u];
