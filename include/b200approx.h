@@ -65,6 +65,13 @@ int b200_nn_predict(b200_model* m, const double* z, int64_t q, int32_t k, int32_
                     const double* y, int32_t r, int64_t* ids, double* wts, int32_t* cnt,
                     int32_t* err, double* out);
 
+/* Stand-alone Shepard(): WEIGHT (shepard/weight.f90:1-34) of every query against ALL fitted points,
+ * the batched form of Shepard._predict's loop (shepard/__init__.py:35-47).  wts (q,n) dense normalised
+ * weights in point order (may be NULL); y (n,r) -> out (q,r) weighted sums (y may be NULL when wts is
+ * given). */
+int b200_shepard_predict(b200_model* m, const double* z, int64_t q, const double* y, int32_t r, double* wts,
+                         double* out);
+
 /* SHEPMOD (modified_shepard.f95:10-60): radius of influence rw (n); *ier 0/1. */
 int b200_shepmod_fit(b200_model* m, double* rw, int32_t* ier);
 /* SHEPMODVAL over a batch + ShepMod._predict's `wts > 0` filter

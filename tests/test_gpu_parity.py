@@ -249,3 +249,24 @@ def test_auto_k_selection(ub):
     assert len(m.predict(z)) == 10
     k = ub.auto(x, y, max_k=16, samples=50)
     assert k in (1, 2, 4, 8, 16)
+
+
+def test_standalone_shepard_all_points(ub, oracle):
+    """Shepard() over every fitted point (shepard/__init__.py:35-47 + weight.f90) at a size where the
+    dense loop matters, incl. exact hits (weight.f90:25-28) and the dense weight matrix."""
+    x, z = synth(3000, 120, 5)
+    z[:7] = x[10:17]
+    y = fun(x)
+    m = ub.Shepard()
+    m.fit(x, y)
+    pred = np.array(m(z))
+    W = np.array([oracle.shepard_weight(x, p) for p in z])
+    ref = np.array([sum(y[i] * w for i, w in enumerate(row) if w != 0) for row in W])
+    assert relerr(pred, ref) < RTOL
+    assert np.array_equal(pred[:7], y[10:17])
+    m2 = ub.Shepard()
+    m2.fit(x)
+    pw = m2(z[:20])
+    ids, wts = pw[3]
+    assert np.array_equal(ids, np.arange(3000)) and np.max(np.abs(wts - W[3])) < 1e-15
+    assert all(abs(w.sum() - 1) < 1e-12 for _, w in pw)

@@ -32,6 +32,7 @@ _SIGNATURES = {
     "b200_knn": (C.c_int, [C.c_void_p, c_dp, C.c_int64, C.c_int32, C.c_int64, c_i64p, c_dp]),
     "b200_nn_predict": (C.c_int, [C.c_void_p, c_dp, C.c_int64, C.c_int32, C.c_int32, c_dp, C.c_int32,
                                   c_i64p, c_dp, c_i32p, c_i32p, c_dp]),
+    "b200_shepard_predict": (C.c_int, [C.c_void_p, c_dp, C.c_int64, c_dp, C.c_int32, c_dp, c_dp]),
     "b200_shepmod_fit": (C.c_int, [C.c_void_p, c_dp, c_i32p]),
     "b200_shepmod_predict": (C.c_int, [C.c_void_p, c_dp, C.c_int64, C.c_int32, c_i64p, c_dp, c_i32p,
                                        c_i32p, c_dp, C.c_int32, c_dp]),
@@ -167,6 +168,20 @@ class Model:
         out = np.zeros((3, 96, 4), dtype=np.int64)
         check(lib().b200_tc_debug_trace(self._h, ptr(z), z.shape[0], k, ptr(out, c_i64p), out.size))
         return out
+
+    def shepard_predict(self, z, y=None, want_weights=False):
+        """Stand-alone Shepard over all fitted points: (wts (q,n) or None, out (q,r) or None)."""
+        z = f64(z)
+        q = z.shape[0]
+        wts = np.empty((q, self.n)) if want_weights else None
+        out = None
+        r = 0
+        if y is not None:
+            y = f64(y).reshape(self.n, -1)
+            r = y.shape[1]
+            out = np.empty((q, r))
+        check(lib().b200_shepard_predict(self._h, ptr(z), q, ptr(y), r, ptr(wts), ptr(out)))
+        return wts, out
 
     def shepmod_fit(self):
         rw = np.empty(self.n)

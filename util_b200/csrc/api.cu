@@ -354,6 +354,29 @@ int b200_merge_topk_dev(int32_t device, const double* d2_parts, const int32_t* i
   return merge_topk(d2_parts, idx_parts, parts, q, k, d2_out, idx_out, (cudaStream_t)stream);
 }
 
+int b200_shepard_predict(b200_model* m, const double* z, int64_t q, const double* y, int32_t r, double* wts,
+                         double* out) {
+  B200_TRY(use(m));
+  if (q < 0 || (y && !out) || (!y && !wts)) {
+    set_error("b200_shepard_predict: bad arguments");
+    return 1;
+  }
+  if (q == 0) return 0;
+  B200_TRY(upload_queries(m, z, q));
+  B200_TRY(upload_y(m, y, r));
+  if (y) B200_TRY(m->out.reserve((size_t)q * r * 8));
+  if (wts) B200_TRY(m->wts.reserve((size_t)q * m->n * 8));
+  {
+    Timer t(m, 0, &m->st.ms_weights);
+    B200_TRY(shepard_all(m, m->zq.as<double>(), q, y ? m->y.as<double>() : nullptr, r,
+                         wts ? m->wts.as<double>() : nullptr, y ? m->out.as<double>() : nullptr, 0));
+  }
+  if (wts) B200_CUDA(cudaMemcpy(wts, m->wts.p, (size_t)q * m->n * 8, cudaMemcpyDeviceToHost));
+  if (y) B200_CUDA(cudaMemcpy(out, m->out.p, (size_t)q * r * 8, cudaMemcpyDeviceToHost));
+  B200_CUDA(cudaDeviceSynchronize());
+  return 0;
+}
+
 int b200_shepmod_fit(b200_model* m, double* rw, int32_t* ier) {
   B200_TRY(use(m));
   int e = 0;

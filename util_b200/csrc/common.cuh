@@ -129,6 +129,9 @@ int knn_tc(b200_model* m, const double* z_dev, int64_t q, int k, int64_t self_of
 int nn_weights(b200_model* m, const double* z_dev, int64_t q, int k, int method,
                const int32_t* idx_dev, const double* d2_dev, const double* y_dev, int r,
                double* wts_dev, int32_t* cnt_dev, int32_t* err_dev, double* out_dev, cudaStream_t st);
+// shepard_all.cu
+int shepard_all(b200_model* m, const double* z_dev, int64_t q, const double* y_dev, int r, double* wts_dev,
+                double* out_dev, cudaStream_t st);
 // shepmod.cu
 int shepmod_fit(b200_model* m, cudaStream_t st, int* ier);
 int shepmod_predict(b200_model* m, const double* z_dev, int64_t q, int cap, int32_t* ids_dev,

@@ -1,10 +1,10 @@
 """Shepard inverse-distance weighting, interface of util/approximate/shepard/__init__.py:20-47.
 
-As `NearestNeighbor(method=Shepard)` the weights over the k neighbours are
-computed by avg_shepard_kernel (WEIGHT, shepard/weight.f90:1-34).  Stand-alone
-`Shepard()` weights every fitted point; it is served by the same kernel with
-k = n, which the kernel supports up to n = 128 (the reference's demo uses 20
-points, shepard/__init__.py:53); larger stand-alone fits are not built yet.
+As `NearestNeighbor(method=Shepard)` the weights over the k neighbours are computed by
+avg_shepard_kernel; stand-alone `Shepard()` weights EVERY fitted point per query
+(WEIGHT, shepard/weight.f90:1-34) through shepard_all_kernel: the weighted sums are fused
+into the scan, and the dense (q, n) weight matrix the reference returns is only
+materialised when a caller asks for it (`_predict`).
 """
 import numpy as np
 
@@ -14,7 +14,6 @@ from .base import WeightedApproximator
 
 class Shepard(WeightedApproximator):
     _b200_method = _lib.SHEPARD
-    _MAX_N = 128
     points = None
     model = None
 
@@ -24,18 +23,14 @@ class Shepard(WeightedApproximator):
     def _fit(self, points):
         # the reference keeps points as (d, n) Fortran order (shepard/__init__.py:32)
         self.points = np.asarray(points.copy().T, order="F")
-        if points.shape[0] > self._MAX_N:
-            raise NotImplementedError(
-                f"stand-alone Shepard over n={points.shape[0]} > {self._MAX_N} points is not built; "
-                "use NearestNeighbor(k, method=Shepard)")
         if self.model is not None: self.model.close()
         self.model = _lib.Model(points, device=self.device)
 
     def _predict(self, points, display_wait_sec=3.):
         n = self.points.shape[1]
-        ids, wts, _, _, _ = self.model.nn_predict(points, n, _lib.SHEPARD)
-        # the reference returns indices 0..n-1 with weights in that order (:36-46)
-        indices = np.zeros((points.shape[0], n), dtype=int) + np.arange(n)
-        weights = np.zeros(indices.shape)
-        np.put_along_axis(weights, ids, wts, axis=1)
+        weights, _ = self.model.shepard_predict(points, want_weights=True)
+        indices = np.zeros((points.shape[0], n), dtype=int) + np.arange(n)  # :36-37
         return indices, weights
+
+    def _predict_values(self, points, display_wait_sec=3.):
+        return self.model.shepard_predict(points, y=self._y_numeric)[1][:, 0]
