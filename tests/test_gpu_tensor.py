@@ -40,7 +40,8 @@ def test_stage1_scores_match_fp64_within_bound(L):
 
 
 @pytest.mark.parametrize("n,q,d,k", [(20000, 1000, 64, 16), (30000, 700, 16, 17), (9000, 513, 8, 1),
-                                     (12000, 300, 32, 33), (5000, 260, 10, 15), (40000, 300, 3, 8)])
+                                     (12000, 300, 32, 33), (5000, 260, 10, 15), (40000, 300, 3, 8),
+                                     (8000, 300, 100, 5), (6000, 130, 125, 3)])  # K = 112 / 128: generic K loop, one half per CTA
 def test_tensor_knn_bit_exact(L, oracle, n, q, d, k):
     x, z = synth(n, q, d)
     m = L.Model(x)
