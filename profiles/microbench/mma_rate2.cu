@@ -15,14 +15,15 @@ __device__ __forceinline__ void umma_f16_ts(uint32_t d_tmem, uint32_t a_tmem, ui
 }
 
 // mode 0: idle other warps; 1: 8 warps poll an mbarrier (try_wait); 2: 8 warps stream LDS/STS
+__device__ int g_commit_every = 0;  // >0: a tcgen05.commit after every group of 5 MMAs (1: one barrier, 2: two)
 template <int ts, int vec>
 __global__ void __launch_bounds__(320, 1) k(long long* out, int N, int nmma, int mode) {
   extern __shared__ __align__(1024) uint8_t smem[];
-  __shared__ uint64_t bar, bar2;
+  __shared__ uint64_t bar, bar2, bar3;
   __shared__ uint32_t slot;
   __shared__ volatile int done;
   const int warp = __shfl_sync(0xffffffffu, (int)(threadIdx.x >> 5), 0);
-  if (threadIdx.x == 0) { ptx::mbar_init(ptx::smem_u32(&bar), 1); ptx::mbar_init(ptx::smem_u32(&bar2), 1); done = 0; ptx::fence_barrier_init(); }
+  if (threadIdx.x == 0) { ptx::mbar_init(ptx::smem_u32(&bar), 1); ptx::mbar_init(ptx::smem_u32(&bar2), 1); ptx::mbar_init(ptx::smem_u32(&bar3), 1); done = 0; ptx::fence_barrier_init(); }
   if (warp == 9) { ptx::tmem_alloc(ptx::smem_u32(&slot), 512); ptx::tmem_relinquish(); }
   for (int i = threadIdx.x; i < 131072 / 4; i += 320) reinterpret_cast<uint32_t*>(smem)[i] = 0;
   ptx::fence_proxy_async();
@@ -42,6 +43,8 @@ __global__ void __launch_bounds__(320, 1) k(long long* out, int N, int nmma, int
           if (ts) umma_f16_ts(off + ((i / 5) & 1) * 192, off + 384 + ks * 8, bd + (uint64_t)(ks * (N * 2)), idesc, ks > 0);
           else ptx::umma_f16(off + ((i / 5) & 1) * 256, ad + (uint64_t)(ks * 256), bd + (uint64_t)(ks * (N * 2)), idesc, ks > 0);
         }
+        if (g_commit_every >= 1) ptx::umma_commit(ptx::smem_u32(&bar2));
+        if (g_commit_every >= 2) ptx::umma_commit(ptx::smem_u32(&bar3));
       }
       long long t1 = clock64();
       ptx::umma_commit(ptx::smem_u32(&bar));
@@ -69,8 +72,8 @@ void run(long long* out) {
   auto kern = k<ts, vec>;
   cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, 131072);
   const char* names[] = {"others idle", "8 warps polling try_wait", "8 warps LDS/STS"};
-  for (int N : {96, 128, 256})
-    for (int mode = 0; mode < 3; ++mode) {
+  for (int N : {64, 96, 128, 256})
+    for (int mode = 0; mode < 3; mode += 2) {
       if (ts && N == 256) continue;
       long long a[2], b[2];
       kern<<<1, 320, 131072>>>(out, N, 20, mode); cudaDeviceSynchronize();
@@ -80,8 +83,16 @@ void run(long long* out) {
              cudaGetErrorString(e), (b[1] - a[1]) / 800.0, N / 2);
     }
 }
-int main() {
+int main(int argc, char** argv) {
   long long* out; cudaMalloc(&out, 64);
+  if (argc > 1) {  // commit study
+    for (int ce = 0; ce <= 2; ++ce) {
+      cudaMemcpyToSymbol(g_commit_every, &ce, 4);
+      printf("--- commits per group of 5 MMAs: %d\n", ce);
+      run<0, 0>(out); run<1, 0>(out);
+    }
+    return 0;
+  }
   run<0, 0>(out); run<0, 1>(out); run<1, 0>(out); run<1, 1>(out);
   return 0;
 }

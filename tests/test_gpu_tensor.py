@@ -59,6 +59,31 @@ def test_tensor_knn_bit_exact(L, oracle, n, q, d, k):
     print(f"uncertified {int(m.stat('uncertified'))}/{q} (n={n}, d={d}, k={k}, cap={int(m.stat('tc_cap'))})")
 
 
+@pytest.mark.parametrize("n,q,d,k", [(20000, 1000, 64, 16), (9000, 513, 8, 1), (12000, 300, 32, 33),
+                                     (8000, 300, 100, 5), (6000, 130, 125, 3), (5000, 260, 10, 40)])
+def test_tensor_knn_ts_kernel_bit_exact(L, oracle, n, q, d, k):
+    """The TS-form stage-1 kernel (queries resident in TMEM, 64-column accumulator stages), selected
+    with tc_flags bit 6: same exact result, and its raw scores obey the same bound."""
+    x, z = synth(n, q, d)
+    m = L.Model(x)
+    m.set_option("knn_path", L.PATH_TENSOR)
+    m.set_option("tc_flags", 64)
+    idx, d2 = m.knn(z, k)
+    oi, od = oracle.knn(x, z, k)
+    assert np.array_equal(idx, oi)
+    assert np.array_equal(d2, od)
+    assert m.stat("tc_queries") == q
+    if d >= 8:
+        assert m.stat("uncertified") <= 0.2 * q
+    s = m.tc_debug_scores(z[:128], k=1)
+    sc = m.stat("tc_scale")
+    D = ((z[:128, None, :] - x[None, :, :]) ** 2).sum(-1)
+    est = s[:, :n].astype(np.float64) / sc ** 2
+    off = np.median(D - est, axis=1, keepdims=True)
+    bound = 4 * 2.0 ** -11 * (2 * np.sqrt(d) * 1.0) * m.stat("tc_ymax") / sc ** 2 + 1e-4
+    assert np.abs(D - est - off).max() < bound
+
+
 def test_tensor_knn_self_excluding(L, oracle):
     x, _ = synth(15000, 1, 16)
     m = L.Model(x)

@@ -162,7 +162,7 @@ int b200_destroy(b200_model* m) {
   cudaSetDevice(m->device);
   cudaDeviceSynchronize();
   if (m->x) cudaFree(m->x);
-  DevBuf* bufs[] = {&m->tc.mu, &m->tc.img, &m->rw, &m->lf, &m->la, &m->y, &m->zq, &m->idx32, &m->d2,
+  DevBuf* bufs[] = {&m->tc.mu, &m->tc.img, &m->tc.perm, &m->rw, &m->lf, &m->la, &m->y, &m->zq, &m->idx32, &m->d2,
                     &m->wts, &m->cnt, &m->err, &m->out, &m->part_d2, &m->part_idx, &m->cand,
                     &m->cand_meta, &m->zimg, &m->flags, &m->misc, &m->ids64};
   for (DevBuf* b : bufs) b->release();
@@ -318,9 +318,22 @@ int b200_tc_debug_scores(b200_model* m, const double* z, int64_t q, int32_t k, f
   m->dbg_scores = dump.as<float>();
   int rc = knn_tc(m, m->zq.as<double>(), q, k, -1, m->idx32.as<int32_t>(), m->d2.as<double>(), 0);
   m->dbg_scores = nullptr;
-  if (rc == 0 && cudaMemcpy(scores, dump.p, (size_t)q * ncols * 4, cudaMemcpyDeviceToHost) != cudaSuccess) {
-    set_error("b200_tc_debug_scores: copy back failed");
-    rc = 2;
+  // the dump is in image-position order: hand it back in fitted-row order (padding columns stay last)
+  if (rc == 0) {
+    std::vector<float> raw((size_t)q * ncols);
+    std::vector<int32_t> perm((size_t)m->n);
+    if (cudaMemcpy(raw.data(), dump.p, raw.size() * 4, cudaMemcpyDeviceToHost) != cudaSuccess ||
+        cudaMemcpy(perm.data(), m->tc.perm.p, perm.size() * 4, cudaMemcpyDeviceToHost) != cudaSuccess) {
+      set_error("b200_tc_debug_scores: copy back failed");
+      rc = 2;
+    } else {
+      for (int64_t r = 0; r < q; ++r) {
+        const float* src = raw.data() + (size_t)r * ncols;
+        float* dst = scores + (size_t)r * ncols;
+        for (int64_t c = 0; c < m->n; ++c) dst[perm[c]] = src[c];
+        for (int64_t c = m->n; c < ncols; ++c) dst[c] = src[c];
+      }
+    }
   }
   dump.release();
   return rc;

@@ -64,12 +64,14 @@ struct TcData {
   int K = 0;            // padded contraction length (multiple of 16)
   int sub = 128;        // rows per data sub-tile image (64 or 128)
   int rg = 0;           // 1: row-group-major image layout
+  int order = 0;        // 0: positions ordered by centred norm, 1: fitted order
   int64_t tiles = 0;    // 128-point tiles
   double scale = 1.0;   // power of two applied after centring
   double ymax = 0.0;    // max over points of max(||yc||, ||fp16(yc)||) (scaled units)
   double cmax = 0.0;    // max |coordinate| of the raw data
   DevBuf mu;            // d doubles: per-dimension centre
   DevBuf img;           // tiles * 128 * K halfs, UMMA K-major no-swizzle tile images
+  DevBuf perm;          // n int32: image position -> fitted row (positions ordered by centred norm)
 };
 
 struct Stats {

@@ -27,6 +27,8 @@
 // [K/8][128][8 halfs] (K-major, no swizzle: 8x16-byte core matrices contiguous),
 // so one cp.async.bulk (TMA engine) brings a whole tile and the smem descriptor
 // is fixed: LBO = 2048 B (next K chunk), SBO = 128 B (next 8 rows).
+#include <cub/device/device_radix_sort.cuh>
+
 #include "common.cuh"
 #include "ptx.cuh"
 
@@ -75,15 +77,40 @@ __global__ void maxabs_kernel(const double* __restrict__ x, int64_t n, int d, co
   }
 }
 
+// ------------------------------------------------------------- data order
+// The fitted points are streamed past every query in order of increasing centred norm.  The score
+// ||y||^2 - 2 x.y of a low-norm point is systematically smaller, so the running thresholds tighten
+// early and far fewer later points survive the filter (about half as many after the first 1 % of the
+// stream on uniform data) -- any order gives the same exact result.  Key: fp32 bits of the squared
+// norm (non-negative, so unsigned order = numeric order).
+__global__ void norm_key_kernel(const double* __restrict__ x, int64_t n, int d, const double* __restrict__ mu,
+                                double scale, uint32_t* __restrict__ key, int32_t* __restrict__ val) {
+  const int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
+  if (i >= n) return;
+  double n2 = 0.0;
+  for (int j = 0; j < d; ++j) {
+    const double yc = (x[i * d + j] - mu[j]) * scale;
+    n2 = fma(yc, yc, n2);
+  }
+  key[i] = __float_as_uint((float)n2);
+  val[i] = (int32_t)i;
+}
+
+__global__ void iota_kernel(int32_t* __restrict__ v, int64_t n) {
+  const int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
+  if (i < n) v[i] = (int32_t)i;
+}
+
 // ------------------------------------------------------------- operand images
 // Data side: one thread per (padded) point; writes its row of the tile image and
 // folds max(||yc||, ||fp16(yc)||) into ymax.
 __global__ void data_img_kernel(const double* __restrict__ x, int64_t n, int d, int K, int SUBROWS, int rg,
-                                const double* __restrict__ mu, double scale, __half* __restrict__ img,
-                                int64_t npad, unsigned long long* __restrict__ ymax_bits) {
-  const int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
+                                const double* __restrict__ mu, double scale, const int32_t* __restrict__ perm,
+                                __half* __restrict__ img, int64_t npad, unsigned long long* __restrict__ ymax_bits) {
+  const int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;  // image position
   double nm = 0.0;
   if (i < npad) {
+    const int64_t src = i < n ? (int64_t)perm[i] : 0;  // fitted row that sits at this position
     const int64_t t = i / SUBROWS;
     const int r = (int)(i - t * SUBROWS);
     uint4* dst = reinterpret_cast<uint4*>(img + (size_t)t * SUBROWS * K);  // chunk c at dst[c*SUBROWS + r]
@@ -96,7 +123,7 @@ __global__ void data_img_kernel(const double* __restrict__ x, int64_t n, int d, 
         const int j = c * 8 + e;
         float hv = 0.0f;
         if (i < n && j < d) {
-          const double yc = (x[i * d + j] - mu[j]) * scale;
+          const double yc = (x[src * d + j] - mu[j]) * scale;
           const __half hh = __double2half(yc);
           n2 = fma(yc, yc, n2);
           const double yh = (double)__half2float(hh);
@@ -191,6 +218,7 @@ struct KParams {
   int sub;               // data rows per B sub-tile: 64 or 128 (one TMA copy, one UMMA N)
   int flags;             // bit 0: mbarrier waits pass a suspend-time hint
   int slots;             // depth of the B ring, in sub-tiles
+  int stages;            // TS kernel: 64-column accumulator stages per half
   int keep;              // C: candidates a compaction keeps (<= CAP - 8)
   int mode;              // 0 normal; debug ceilings: 1 = epilogue reads TMEM only, 2 = epilogue only releases
   int32_t* cand_idx;     // [qpad][CAP]
@@ -280,6 +308,72 @@ __device__ __forceinline__ float compact_row(float* bsc, int* bid, int RS, int c
   __syncwarp();
   return tau;
 }
+
+// Survivors of one 32-column chunk held in registers v[32] -> candidate buffer of my row.
+// mask: values below my threshold (32 independent compares, four short OR chains).  A row whose
+// buffer cannot take all its survivors is trimmed FIRST (warp-cooperative compact_row: keep best
+// entries, threshold lowered to the keep-th), the mask is taken again under the new threshold, and
+// only then are the survivors stored -- nothing is ever dropped, so the buffer holds every value
+// below the final threshold.  In the first tiles one chunk can hold more survivors than the
+// CAP - keep (>= 16) free slots a trim leaves: the chunk is then taken in two 16-column halves.
+// The usual case late in the stream is one survivor, the chunk minimum `mcc` already held.
+// Uses: tau, cnt, keep, lane, my_sc, my_id, bsc, bid, RS, row0, CAP (of the enclosing kernel).
+#define B200_MASK32(v, out)                                                                  \
+  do {                                                                                       \
+    unsigned m4_[4] = {0u, 0u, 0u, 0u};                                                      \
+    _Pragma("unroll") for (int i_ = 0; i_ < 32; ++i_) m4_[i_ & 3] |= v[i_] < tau ? (1u << i_) : 0u; \
+    out = (m4_[0] | m4_[1]) | (m4_[2] | m4_[3]);                                             \
+  } while (0)
+#define B200_APPEND_CHUNK(v, base, mcc)                                                      \
+  do {                                                                                       \
+    unsigned todo_ = 0xffffffffu;                                                            \
+    do {                                                                                     \
+      unsigned cur_ = todo_, mask_;                                                          \
+      B200_MASK32(v, mask_);                                                                 \
+      mask_ &= todo_;                                                                        \
+      unsigned need_ = __ballot_sync(0xffffffffu, cnt + __popc(mask_) > CAP);                \
+      if (need_) {                                                                           \
+        while (need_) {                                                                      \
+          const int r_ = __ffs(need_) - 1;                                                   \
+          need_ &= need_ - 1;                                                                \
+          const int nv_ = __shfl_sync(0xffffffffu, cnt, r_);                                 \
+          const float nt_ = compact_row<CAP>(bsc, bid, RS, row0 + r_, nv_, keep, lane);      \
+          if (lane == r_) {                                                                  \
+            tau = fminf(tau, nt_);                                                           \
+            cnt = keep;                                                                      \
+          }                                                                                  \
+        }                                                                                    \
+        B200_MASK32(v, mask_);                                                               \
+        mask_ &= todo_;                                                                      \
+        if (todo_ == 0xffffffffu && __any_sync(0xffffffffu, cnt + __popc(mask_) > CAP)) {    \
+          cur_ = 0x0000ffffu;                                                                \
+          mask_ &= cur_;                                                                     \
+        }                                                                                    \
+      }                                                                                      \
+      const int nh_ = __popc(mask_);                                                         \
+      if (nh_ == 1 && cur_ == 0xffffffffu) {                                                 \
+        if (cnt < CAP) {                                                                     \
+          my_sc[cnt * RS] = mcc;                                                             \
+          my_id[cnt * RS] = (base) + __ffs(mask_) - 1;                                       \
+          ++cnt;                                                                             \
+        } else {                                                                             \
+          tau = mcc; /* cannot happen (space was made above); kept so the filter stays valid */ \
+        }                                                                                    \
+      } else if (nh_ > 0) {                                                                  \
+        _Pragma("unroll") for (int i_ = 0; i_ < 32; ++i_) {                                  \
+          const bool lt_ = (mask_ >> i_) & 1u;                                               \
+          const bool put_ = lt_ && cnt < CAP;                                                \
+          if (put_) {                                                                        \
+            my_sc[cnt * RS] = v[i_];                                                         \
+            my_id[cnt * RS] = (base) + i_;                                                   \
+          }                                                                                  \
+          tau = (lt_ && !put_) ? v[i_] : tau;                                                \
+          cnt += put_ ? 1 : 0;                                                               \
+        }                                                                                    \
+      }                                                                                      \
+      todo_ &= ~cur_;                                                                        \
+    } while (todo_);                                                                         \
+  } while (0)
 
 template <int CAP, int HALVES, bool DBG>
 __global__ void __launch_bounds__((HALVES * 4 + 3) * 32, 1) knn_tc_kernel(const KParams p) {
@@ -395,41 +489,43 @@ __global__ void __launch_bounds__((HALVES * 4 + 3) * 32, 1) knn_tc_kernel(const 
       const uint32_t full0 = ptx::smem_u32(&bar_full[0]), empty0 = ptx::smem_u32(&bar_empty[0]);
       const uint32_t accf = ptx::smem_u32(&bar_accf[j * 2]), acce = ptx::smem_u32(&bar_acce[j * 2]);
       const uint32_t slot_mask = p.slots - 1, slot_shift = 31 - __clz(p.slots);  // slots is a power of two
-      uint32_t it0 = 0;   // global index of the current block's first tile
-      uint32_t mine = 0;  // tiles this issuer has done (phase of its accumulator stage)
-      for (int b = 0; b < nqb; ++b, it0 += p.ntiles) {
-        ptx::mbar_wait(hint, ptx::smem_u32(bar_afull), b & 1, bsleep);
-        for (uint32_t t = (j + it0) & 1; t < (uint32_t)p.ntiles; t += 2, ++mine) {
-          const uint32_t it = it0 + t;
-          for (int hs = 0; hs < per_tile; ++hs) {
-            const uint32_t jt = it * per_tile + hs, s = jt & slot_mask, ph = (jt >> slot_shift) & 1;
-            const uint64_t bd = b_desc0 + (uint64_t)(s * slot_step);
-            bool have_b = false;
+      // One thread per issuer warp, lean barrier probes, no per-tile parameter reloads: the per-tile
+      // serial path of the issuer is what bounds the pipeline once the epilogue keeps up.
+      if (lane == 0) {
+        uint32_t it0 = 0;   // global index of the current block's first tile
+        uint32_t mine = 0;  // tiles this issuer has done (phase of its accumulator stage)
+        const uint32_t afull = ptx::smem_u32(bar_afull), aempty = ptx::smem_u32(bar_aempty);
+        const uint32_t ntiles = (uint32_t)p.ntiles;
+        for (int b = 0; b < nqb; ++b, it0 += ntiles) {
+          while (!ptx::mbar_try_wait(afull, b & 1)) {}
+          for (uint32_t t = (j + it0) & 1; t < ntiles; t += 2, ++mine) {
+            const uint32_t it = it0 + t;
+            for (int hs = 0; hs < per_tile; ++hs) {
+              const uint32_t jt = it * per_tile + hs, s = jt & slot_mask, ph = (jt >> slot_shift) & 1;
+              const uint64_t bd = b_desc0 + (uint64_t)(s * slot_step);
 #pragma unroll
-            for (int h = 0; h < HALVES; ++h) {
-              // the accumulator half is free once its four epilogue warps have read the previous tile
-              if (hs == 0) ptx::mbar_wait(hint, acce + h * 8, (mine & 1) ^ 1, bsleep);
-              if (!have_b) {
-                ptx::mbar_wait(hint, full0 + s * 8, ph, bsleep);
-                have_b = true;
-              }
-              ptx::tc_fence_after();
-              // (the accumulator base is the literal 0: this CTA owns all 512 columns, checked at start)
-              const uint32_t d_tmem = j * ACC_COLS + h * TILE + hs * SUB;
-              if (ptx::elect_one()) {
-                if (h == 0) B200_TRACE(1, (int)it, 0);
-                if (!skip_mma) {
+              for (int h = 0; h < HALVES; ++h) {
+                // the accumulator half is free once its four epilogue warps have read the previous tile
+                if (hs == 0) {
+                  while (!ptx::mbar_try_wait(acce + h * 8, (mine & 1) ^ 1)) {}
+                }
+                if (h == 0) {
+                  while (!ptx::mbar_try_wait(full0 + s * 8, ph)) {}
+                }
+                ptx::tc_fence_after();
+                // (the accumulator base is the literal 0: this CTA owns all 512 columns, checked at start)
+                const uint32_t d_tmem = j * ACC_COLS + h * TILE + hs * SUB;
+                if (DBG && h == 0) B200_TRACE(1, (int)it, 0);
+                if (!(DBG && skip_mma)) {
 #define B200_ISSUE(KS)                                                                                   \
   _Pragma("unroll") for (int ks = 0; ks < KS; ++ks)                                                       \
     ptx::umma_f16(d_tmem, a_desc[h] + (uint64_t)(ks * a_step), bd + (uint64_t)(ks * b_step), idesc,        \
                   ks > 0 ? 1u : 0u);
                   switch (ksteps) {
-                    case 1: B200_ISSUE(1) break;
                     case 2: B200_ISSUE(2) break;
                     case 3: B200_ISSUE(3) break;
                     case 4: B200_ISSUE(4) break;
                     case 5: B200_ISSUE(5) break;
-                    case 6: B200_ISSUE(6) break;
                     default:
                       for (int ks = 0; ks < ksteps; ++ks)
                         ptx::umma_f16(d_tmem, a_desc[h] + (uint64_t)(ks * a_step), bd + (uint64_t)(ks * b_step),
@@ -439,17 +535,15 @@ __global__ void __launch_bounds__((HALVES * 4 + 3) * 32, 1) knn_tc_kernel(const 
                 }
                 if (hs == per_tile - 1) ptx::umma_commit(accf + h * 8);  // this half's 128 columns are ready
                 if (h == HALVES - 1) {
-                  B200_TRACE(1, (int)it, 1);
+                  if (DBG) B200_TRACE(1, (int)it, 1);
                   ptx::umma_commit(empty0 + s * 8);  // sub-tile slot free once these MMAs retire
-                  B200_TRACE(1, (int)it, 3);
+                  if (DBG) B200_TRACE(1, (int)it, 3);
                 }
               }
-              __syncwarp();
             }
           }
+          ptx::umma_commit(aempty);  // my MMAs on these A tiles are tracked
         }
-        if (ptx::elect_one()) ptx::umma_commit(ptx::smem_u32(bar_aempty));  // my MMAs on these A tiles are tracked
-        __syncwarp();
       }
     }
   } else {
@@ -476,13 +570,6 @@ __global__ void __launch_bounds__((HALVES * 4 + 3) * 32, 1) knn_tc_kernel(const 
         ptx::mbar_wait(hint, ptx::smem_u32(&bar_accf[a * 2 + half]), aph);
         if (warp == 0 && lane == 0) B200_TRACE(2, (int)it, 0);
         ptx::tc_fence_after();
-        // compaction trigger: 8 free slots suffice (an overflow only lowers tau, see below)
-        // Compaction trigger.  Normally 8 free slots suffice: a rare overflow only drops the survivor and
-        // lowers tau to it (see below).  In the first two tiles nearly every value beats tau, and a
-        // survivor dropped there is, with probability ~keep/n each, one of the final neighbours (that
-        // query then fails its certificate and is redone exactly), so there the buffer is trimmed
-        // whenever a whole 32-column chunk would no longer fit.
-        const int high = t < 2 ? max(keep, CAP - 32) : CAP - 8;
         const uint32_t t_acc = t_lane + a * ACC_COLS;
         if ((p.mode & 3) != 2) {
           float va[32], vb[32], mc[4];
@@ -528,49 +615,7 @@ __global__ void __launch_bounds__((HALVES * 4 + 3) * 32, 1) knn_tc_kernel(const 
             ptx::tmem_ld_wait();
             const int base = t * TILE + c * 32;
             const float mcc = c == 0 ? mc[0] : (c == 1 ? mc[1] : (c == 2 ? mc[2] : mc[3]));
-            // survivors of my row in this chunk as a bit mask: 32 independent compares, four short
-            // OR chains (a running threshold / counter here would serialise ~30 clk per value)
-            unsigned m4[4] = {0u, 0u, 0u, 0u};
-#pragma unroll
-            for (int i = 0; i < 32; ++i) m4[i & 3] |= va[i] < tau ? (1u << i) : 0u;
-            const unsigned mask = (m4[0] | m4[1]) | (m4[2] | m4[3]);
-            const int nh = __popc(mask);
-            if (nh == 1) {
-              // the usual case: one survivor, and it is the chunk minimum I already hold
-              if (cnt < CAP) {
-                my_sc[cnt * RS] = mcc;
-                my_id[cnt * RS] = base + __ffs(mask) - 1;
-                ++cnt;
-              } else {
-                tau = mcc;  // buffer full: drop it, but then nothing >= it may stay a candidate
-              }
-            } else if (nh > 1) {
-#pragma unroll
-              for (int i = 0; i < 32; ++i) {
-                const float s = va[i];
-                const bool lt = s < tau;
-                const bool put = lt && cnt < CAP;
-                if (put) {
-                  my_sc[cnt * RS] = s;
-                  my_id[cnt * RS] = base + i;
-                }
-                tau = (lt && !put) ? s : tau;
-                cnt += put ? 1 : 0;
-              }
-            }
-            unsigned need = __ballot_sync(0xffffffffu, cnt > high);
-            while (need) {
-              const int r = __ffs(need) - 1;
-              need &= need - 1;
-              const int nv = __shfl_sync(0xffffffffu, cnt, r);
-              if (warp == 0 && lane == 0) B200_TRACE(2, (int)it, 2);
-              const float nt = compact_row<CAP>(bsc, bid, RS, row0 + r, nv, keep, lane);
-              if (warp == 0 && lane == 0) B200_TRACE(2, (int)it, 3);
-              if (lane == r) {
-                tau = fminf(tau, nt);
-                cnt = keep;
-              }
-            }
+            B200_APPEND_CHUNK(va, base, mcc);
           }
         }
         ptx::tc_fence_before();
@@ -594,6 +639,8 @@ __global__ void __launch_bounds__((HALVES * 4 + 3) * 32, 1) knn_tc_kernel(const 
   if (warp == EPI_WARPS + 1) ptx::tmem_dealloc(tmem_base, 512);
 }
 
+#include "knn_tc_ts.cuh"
+
 // ------------------------------------------------------------------ fp64 re-rank
 // One warp per query: exact squared distances of its candidates (reference
 // arithmetic), rank by (d2, index), emit the k best, test the certificate.
@@ -602,7 +649,7 @@ __global__ void __launch_bounds__(256)
 rerank_kernel(const double* __restrict__ x, int64_t n, int d, const double* __restrict__ z, int64_t q,
               int k, int64_t self_offset, const int32_t* __restrict__ cand_idx, int cstride,
               const int32_t* __restrict__ cand_cnt, const float* __restrict__ cand_tau,
-              const QMeta* __restrict__ meta, double scale, double data_cmax,
+              const QMeta* __restrict__ meta, double scale, double data_cmax, const int32_t* __restrict__ perm,
               int32_t* __restrict__ out_idx, double* __restrict__ out_d2, int32_t* __restrict__ fail_list,
               int32_t* __restrict__ fail_cnt) {
   constexpr int U = CAP / 32;
@@ -622,7 +669,8 @@ rerank_kernel(const double* __restrict__ x, int64_t n, int d, const double* __re
   for (int u = 0; u < U; ++u) {
     const int j = lane + 32 * u;
     int c = j < cnt ? cand_idx[p * cstride + j] : -1;
-    const bool ok = c >= 0 && c < n && c != self;
+    c = (c >= 0 && c < n) ? perm[c] : -1;  // image position -> fitted row (padding positions drop out)
+    const bool ok = c >= 0 && c != self;
     dd[u] = ok ? sqdist_seq_wide(x + (int64_t)c * d, zp, d) : CUDART_INF;
     id[u] = ok ? c : 0x7fffffff;
     s_d2[w][j] = dd[u];
@@ -672,11 +720,21 @@ rerank_kernel(const double* __restrict__ x, int64_t n, int d, const double* __re
 // ------------------------------------------------------------------ host side
 namespace {
 
+// Two stage-1 kernels.  knn_tc_kernel (SS form, default) takes 128- or 64-row sub-tile images in
+// either layout.  knn_ts_kernel (TS form, tc_flags bit 6; 64-row chunk-major images) has the faster
+// pipeline -- its distance + min-tree path alone runs at 0.97 of the measured cuBLAS peak against
+// 0.86 -- but its epilogue warps are saturated, so survivor handling is not hidden and the whole
+// kernel is ~8 % slower at C5 (profiles/r01/README.md); kept selectable for the next round.
+inline bool use_ts(const b200_model* m) { return (m->tc_flags & 64) != 0; }
+
 int tc_prepare(b200_model* m, cudaStream_t st) {
   TcData& t = m->tc;
-  if (t.ready && t.sub == m->tc_sub && t.rg == ((m->tc_flags >> 1) & 1)) return 0;
-  t.sub = m->tc_sub;
-  t.rg = (m->tc_flags >> 1) & 1;
+  const int want_sub = use_ts(m) ? 64 : m->tc_sub, want_rg = use_ts(m) ? 0 : ((m->tc_flags >> 1) & 1);
+  const int want_order = (m->tc_flags >> 7) & 1;
+  if (t.ready && t.sub == want_sub && t.rg == want_rg && t.order == want_order) return 0;
+  t.sub = want_sub;
+  t.rg = want_rg;
+  t.order = want_order;
   const int64_t n = m->n;
   const int d = m->d;
   t.K = tc::padK(d);
@@ -713,9 +771,34 @@ int tc_prepare(b200_model* m, cudaStream_t st) {
     t.scale = ldexp(1.0, -ex);   // |centred value| * scale < 1
   }
   t.cmax = mr;
+  // image position -> fitted row, by increasing centred norm (tc_flags bit 7: fitted order, for A/B runs)
+  B200_TRY(t.perm.reserve((size_t)n * 4 + 64));
+  const unsigned nb = (unsigned)((n + 255) / 256);
+  if (m->tc_flags & 128) {
+    tc::iota_kernel<<<nb, 256, 0, st>>>(t.perm.as<int32_t>(), n);
+  } else {
+    DevBuf keys, vals, tmp;
+    B200_TRY(keys.reserve((size_t)n * 8 + 64));
+    B200_TRY(vals.reserve((size_t)n * 4 + 64));
+    uint32_t* k_in = keys.as<uint32_t>();
+    uint32_t* k_out = k_in + n;
+    tc::norm_key_kernel<<<nb, 256, 0, st>>>(m->x, n, d, t.mu.as<double>(), t.scale, k_in, vals.as<int32_t>());
+    size_t tmp_bytes = 0;
+    B200_CUDA(cub::DeviceRadixSort::SortPairs(nullptr, tmp_bytes, k_in, k_out, vals.as<int32_t>(), t.perm.as<int32_t>(),
+                                              (int)n, 0, 32, st));
+    B200_TRY(tmp.reserve(tmp_bytes + 64));
+    B200_CUDA(cub::DeviceRadixSort::SortPairs(tmp.p, tmp_bytes, k_in, k_out, vals.as<int32_t>(), t.perm.as<int32_t>(),
+                                              (int)n, 0, 32, st));
+    B200_CUDA(cudaStreamSynchronize(st));
+    keys.release();
+    vals.release();
+    tmp.release();
+    m->st.launches += 2;
+  }
+  B200_CUDA(cudaGetLastError());
   B200_CUDA(cudaMemsetAsync(bits, 0, 8, st));
   tc::data_img_kernel<<<(unsigned)((npad + 127) / 128), 128, 0, st>>>(m->x, n, d, t.K, t.sub, t.rg, t.mu.as<double>(), t.scale,
-                                                                       t.img.as<__half>(), npad, bits);
+                                                                       t.perm.as<int32_t>(), t.img.as<__half>(), npad, bits);
   B200_CUDA(cudaGetLastError());
   B200_CUDA(cudaMemcpyAsync(hb, bits, 8, cudaMemcpyDeviceToHost, st));
   B200_CUDA(cudaStreamSynchronize(st));
@@ -726,7 +809,7 @@ int tc_prepare(b200_model* m, cudaStream_t st) {
 }
 
 struct TcConfig {
-  int cap, halves, slots, keep;
+  int cap, halves, slots, keep, stages;
   size_t smem;
 };
 
@@ -764,6 +847,59 @@ bool tc_config(int d, int k, int margin, bool self, int subrows, int force_halve
   return false;
 }
 
+// TS kernel: A lives in TMEM, so shared memory holds only the B ring (64-row sub-tiles) and the
+// candidate buffers; TMEM holds `stages` 64-column accumulators per half next to A (K/2 columns).
+bool tc_config_ts(int d, int k, int margin, bool self, int force_halves, TcConfig* c) {
+  const int K = tc::padK(d);
+  const int base = k + (self ? 1 : 0);
+  int keep = base + (margin < 0 ? std::max(4, std::min(k / 2, 16)) : margin);
+  const int caps[4] = {32, 48, 64, 128};
+  int cap = 128;
+  for (int c0 : caps)
+    if (c0 >= keep + 20) {
+      cap = c0;
+      break;
+    }
+  if (keep > cap - 16) keep = cap - 16;
+  if (keep < base) return false;
+  const size_t sub = (size_t)64 * K * 2;
+  const size_t limit = 227 * 1024 - 512;
+  for (int halves = 2; halves >= 1; --halves) {
+    if (force_halves && halves != force_halves) continue;
+    const int stages = std::min(6, (512 / halves - K / 2) / 64);
+    if (stages < 2) continue;
+    const size_t fixed = (size_t)cap * (halves * tc::TILE + 1) * 8 + 1024;
+    if (fixed + 4 * sub > limit) continue;
+    int slots = (int)std::min<size_t>(16, (limit - fixed) / sub);
+    slots = slots >= 16 ? 16 : (slots >= 8 ? 8 : 4);
+    c->cap = cap;
+    c->halves = halves;
+    c->slots = slots;
+    c->keep = keep;
+    c->stages = stages;
+    c->smem = fixed + slots * sub;
+    return true;
+  }
+  return false;
+}
+
+template <int CAP, int HALVES>
+int launch_ts(b200_model* m, const tc::KParams& kp, const TcConfig& cfg, bool dbg, cudaStream_t st) {
+  const int threads = (HALVES * 6 + 1) * 32;  // 4 epilogue + 2 issuer warps per half, one producer
+  const int grid = std::min(kp.qblocks, m->sm_count);
+  if (dbg) {
+    auto kern = tc::knn_ts_kernel<CAP, HALVES, true>;
+    B200_CUDA(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)cfg.smem));
+    kern<<<grid, threads, cfg.smem, st>>>(kp);
+  } else {
+    auto kern = tc::knn_ts_kernel<CAP, HALVES, false>;
+    B200_CUDA(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)cfg.smem));
+    kern<<<grid, threads, cfg.smem, st>>>(kp);
+  }
+  B200_CUDA(cudaGetLastError());
+  return 0;
+}
+
 template <int CAP, int HALVES>
 int launch_tc(b200_model* m, const tc::KParams& kp, const TcConfig& cfg, bool dbg, cudaStream_t st) {
   const int threads = (HALVES * 4 + 3) * 32;
@@ -785,7 +921,8 @@ int launch_tc(b200_model* m, const tc::KParams& kp, const TcConfig& cfg, bool db
 
 bool tc_supported(const b200_model* m, int k) {
   TcConfig c;
-  return m->d + tc::NORM_SLOTS <= 256 && tc_config(m->d, k, 0, true, 128, 0, &c);
+  if (m->d + tc::NORM_SLOTS > 256) return false;
+  return use_ts(m) ? tc_config_ts(m->d, k, 0, true, 0, &c) : tc_config(m->d, k, 0, true, 128, 0, &c);
 }
 
 int knn_tc(b200_model* m, const double* z_dev, int64_t q, int k, int64_t self_offset,
@@ -797,7 +934,10 @@ int knn_tc(b200_model* m, const double* z_dev, int64_t q, int k, int64_t self_of
   }
   B200_TRY(tc_prepare(m, st));
   TcConfig cfg;
-  if (!tc_config(m->d, k, m->margin, self_offset >= 0, m->tc.sub, m->tc_halves, &cfg)) {
+  const bool ts = use_ts(m);
+  cfg.stages = 0;
+  if (!(ts ? tc_config_ts(m->d, k, m->margin, self_offset >= 0, m->tc_halves, &cfg)
+           : tc_config(m->d, k, m->margin, self_offset >= 0, m->tc.sub, m->tc_halves, &cfg))) {
     set_error("tensor kNN path unsupported for d=%d k=%d", m->d, k);
     return 1;
   }
@@ -829,6 +969,7 @@ int knn_tc(b200_model* m, const double* z_dev, int64_t q, int k, int64_t self_of
   kp.ntiles = (int)t.tiles;
   kp.qblocks = qblocks;
   kp.slots = cfg.slots;
+  kp.stages = cfg.stages;
   kp.sub = t.sub;
   kp.flags = m->tc_flags;
   kp.keep = cfg.keep;
@@ -840,8 +981,18 @@ int knn_tc(b200_model* m, const double* z_dev, int64_t q, int k, int64_t self_of
   kp.trace = m->dbg_trace;
   kp.trace_start = m->tc_trace_start;
   int rc = 1;
-  const bool dg = dbg != nullptr;
-  if (cfg.cap == 32 && cfg.halves == 2) rc = launch_tc<32, 2>(m, kp, cfg, dg, st);
+  const bool dg = dbg != nullptr || kp.trace != nullptr || (m->tc_mode & 12);  // trace and MMA/TMA knock-outs live in the debug build
+  if (ts) {
+    if (cfg.cap == 32 && cfg.halves == 2) rc = launch_ts<32, 2>(m, kp, cfg, dg, st);
+    else if (cfg.cap == 48 && cfg.halves == 2) rc = launch_ts<48, 2>(m, kp, cfg, dg, st);
+    else if (cfg.cap == 64 && cfg.halves == 2) rc = launch_ts<64, 2>(m, kp, cfg, dg, st);
+    else if (cfg.cap == 128 && cfg.halves == 2) rc = launch_ts<128, 2>(m, kp, cfg, dg, st);
+    else if (cfg.cap == 32 && cfg.halves == 1) rc = launch_ts<32, 1>(m, kp, cfg, dg, st);
+    else if (cfg.cap == 48 && cfg.halves == 1) rc = launch_ts<48, 1>(m, kp, cfg, dg, st);
+    else if (cfg.cap == 64 && cfg.halves == 1) rc = launch_ts<64, 1>(m, kp, cfg, dg, st);
+    else if (cfg.cap == 128 && cfg.halves == 1) rc = launch_ts<128, 1>(m, kp, cfg, dg, st);
+    else set_error("tensor kNN: no kernel for cap=%d halves=%d", cfg.cap, cfg.halves);
+  } else if (cfg.cap == 32 && cfg.halves == 2) rc = launch_tc<32, 2>(m, kp, cfg, dg, st);
   else if (cfg.cap == 48 && cfg.halves == 2) rc = launch_tc<48, 2>(m, kp, cfg, dg, st);
   else if (cfg.cap == 48 && cfg.halves == 1) rc = launch_tc<48, 1>(m, kp, cfg, dg, st);
   else if (cfg.cap == 64 && cfg.halves == 2) rc = launch_tc<64, 2>(m, kp, cfg, dg, st);
@@ -867,7 +1018,7 @@ int knn_tc(b200_model* m, const double* z_dev, int64_t q, int k, int64_t self_of
   const unsigned rb = (unsigned)((q + 7) / 8);
 #define RERANK(CAPV)                                                                                     \
   tc::rerank_kernel<CAPV><<<rb, 256, 0, st>>>(m->x, m->n, m->d, z_dev, q, k, self_offset, kp.cand_idx, cfg.cap, \
-                                              cand_cnt, cand_tau, meta, t.scale, t.cmax, idx_dev, d2_dev, \
+                                              cand_cnt, cand_tau, meta, t.scale, t.cmax, t.perm.as<int32_t>(), idx_dev, d2_dev, \
                                               fail_list, fail_cnt)
   if (cfg.cap == 32) RERANK(32);
   else if (cfg.cap <= 64) RERANK(64);
