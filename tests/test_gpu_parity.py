@@ -270,3 +270,19 @@ def test_standalone_shepard_all_points(ub, oracle):
     ids, wts = pw[3]
     assert np.array_equal(ids, np.arange(3000)) and np.max(np.abs(wts - W[3])) < 1e-15
     assert all(abs(w.sum() - 1) < 1e-12 for _, w in pw)
+
+
+def test_nn_predict_chunked_upload_matches_single_shot():
+    """Large batches from page-locked memory are uploaded in chunks under the previous chunk's kernels
+    (api.cu b200_nn_predict); the result must not depend on it."""
+    import torch
+    from util_b200 import _lib
+    n, q, d, k = 5000, 148 * 256 * 6 + 777, 4, 3
+    x, z = synth(n, q, d)
+    y = fun(x)
+    m = _lib.Model(x)
+    ref = m.nn_predict(z, k, _lib.SHEPARD, y=y, want_weights=True)          # pageable: one copy
+    zp = torch.from_numpy(z).pin_memory().numpy()
+    got = m.nn_predict(zp, k, _lib.SHEPARD, y=y, want_weights=True)         # pinned: chunked
+    for a, b in zip(ref, got):
+        assert np.array_equal(a, b)

@@ -153,6 +153,8 @@ int b200_create(const double* x, int64_t n, int32_t d, int32_t device, b200_mode
   B200_CUDA(cudaEventCreate(&m->ev1));
   B200_CUDA(cudaEventCreate(&m->ev2));
   B200_CUDA(cudaEventCreate(&m->ev3));
+  B200_CUDA(cudaStreamCreateWithFlags(&m->copy_stream, cudaStreamNonBlocking));
+  B200_CUDA(cudaEventCreateWithFlags(&m->ev_copy, cudaEventDisableTiming));
   *out = m;
   return 0;
 }
@@ -170,6 +172,8 @@ int b200_destroy(b200_model* m) {
   if (m->ev1) cudaEventDestroy(m->ev1);
   if (m->ev2) cudaEventDestroy(m->ev2);
   if (m->ev3) cudaEventDestroy(m->ev3);
+  if (m->ev_copy) cudaEventDestroy(m->ev_copy);
+  if (m->copy_stream) cudaStreamDestroy(m->copy_stream);
   delete m;
   return 0;
 }
@@ -253,20 +257,49 @@ int b200_nn_predict(b200_model* m, const double* z, int64_t q, int32_t k, int32_
     return 1;
   }
   if (q == 0) return 0;
-  B200_TRY(upload_queries(m, z, q));
   B200_TRY(upload_y(m, y, r));
+  B200_TRY(m->zq.reserve((size_t)q * m->d * 8 + 8));
   B200_TRY(m->idx32.reserve((size_t)q * k * 4));
   B200_TRY(m->d2.reserve((size_t)q * k * 8));
   B200_TRY(m->wts.reserve((size_t)q * k * 8));
   B200_TRY(m->cnt.reserve((size_t)q * 4));
   B200_TRY(m->err.reserve((size_t)q * 4));
   if (y) B200_TRY(m->out.reserve((size_t)q * r * 8));
-  B200_TRY(knn_dispatch(m, m->zq.as<double>(), q, k, -1, m->idx32.as<int32_t>(), m->d2.as<double>(), 0));
-  {
-    Timer t(m, 0, &m->st.ms_weights);
-    B200_TRY(nn_weights(m, m->zq.as<double>(), q, k, method, m->idx32.as<int32_t>(), m->d2.as<double>(),
-                        y ? m->y.as<double>() : nullptr, r, m->wts.as<double>(), m->cnt.as<int32_t>(),
-                        m->err.as<int32_t>(), y ? m->out.as<double>() : nullptr, 0));
+  // Large batches from page-locked host memory go up in chunks on a copy stream, each chunk's
+  // transfer under the previous chunk's kernels.  Chunks are whole waves of the tensor kernel's
+  // persistent grid (sm_count blocks of 256 queries), a short first one so the kernels start early.
+  const int64_t wave = (int64_t)m->sm_count * 256;
+  bool chunked = false;
+  if (q >= 6 * wave && method != B200_VORONOI) {
+    cudaPointerAttributes at;
+    chunked = cudaPointerGetAttributes(&at, z) == cudaSuccess && at.type == cudaMemoryTypeHost;
+    cudaGetLastError();
+  }
+  const size_t row_bytes = (size_t)m->d * 8;
+  int64_t done = 0, next = chunked ? 2 * wave : q;  // [done, next) is the chunk whose copy is in flight
+  B200_CUDA(cudaMemcpyAsync(m->zq.p, z, (size_t)next * row_bytes, cudaMemcpyHostToDevice, m->copy_stream));
+  while (done < q) {
+    B200_CUDA(cudaEventRecord(m->ev_copy, m->copy_stream));
+    B200_CUDA(cudaEventSynchronize(m->ev_copy));
+    const int64_t lo = done, hi = next;
+    if (hi < q) {  // start the next transfer before this chunk's kernels
+      next = std::min<int64_t>(q, hi + 6 * wave);
+      if (q - next < 2 * wave) next = q;
+      B200_CUDA(cudaMemcpyAsync(m->zq.as<char>() + (size_t)hi * row_bytes,
+                                reinterpret_cast<const char*>(z) + (size_t)hi * row_bytes,
+                                (size_t)(next - hi) * row_bytes, cudaMemcpyHostToDevice, m->copy_stream));
+    }
+    const double* zc = m->zq.as<double>() + (size_t)lo * m->d;
+    int32_t* ic = m->idx32.as<int32_t>() + (size_t)lo * k;
+    double* dc = m->d2.as<double>() + (size_t)lo * k;
+    B200_TRY(knn_dispatch(m, zc, hi - lo, k, -1, ic, dc, 0));
+    {
+      Timer t(m, 0, &m->st.ms_weights);
+      B200_TRY(nn_weights(m, zc, hi - lo, k, method, ic, dc, y ? m->y.as<double>() : nullptr, r,
+                          m->wts.as<double>() + (size_t)lo * k, m->cnt.as<int32_t>() + lo, m->err.as<int32_t>() + lo,
+                          y ? m->out.as<double>() + (size_t)lo * r : nullptr, 0));
+    }
+    done = hi;
   }
   if (ids) {
     const int32_t* src = method == B200_VORONOI ? m->misc.as<int32_t>() : m->idx32.as<int32_t>();

@@ -108,6 +108,8 @@ struct b200_model {
   int64_t rows_per_call = 1 << 20;
   b200::Stats st;
   cudaEvent_t ev0 = nullptr, ev1 = nullptr, ev2 = nullptr, ev3 = nullptr;
+  cudaStream_t copy_stream = nullptr;  // host->device query chunks overlap the previous chunk's kernels
+  cudaEvent_t ev_copy = nullptr;
   long long* dbg_trace = nullptr;  // tuning only: clock stamps of CTA 0
   float* dbg_scores = nullptr;  // tests only: raw tensor-path scores are dumped here
 };
