@@ -224,14 +224,20 @@ def main():
     last = {"out": out, "idx": idx}
     stream = torch.cuda.current_stream().cuda_stream
 
+    wev = []  # CUDA events around the weighting kernel of each step
+
     def step_device():
         if data_sharded:
             # local top-k -> NCCL all-to-all of the partial lists -> on-device merge -> weights
             last["out"], last["idx"], _ = sh.predict(z_dev, k, _lib.SHEPARD, y_dev, stream)
         else:
             _lib.check(lib.b200_knn_dev(h, z_dev.data_ptr(), ql, k, -1, idx.data_ptr(), d2.data_ptr(), stream))
+            w0, w1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+            w0.record()
             _lib.check(lib.b200_nn_weights_dev(h, None, ql, k, _lib.SHEPARD, idx.data_ptr(), d2.data_ptr(),
                                                y_dev.data_ptr(), 1, None, None, None, out.data_ptr(), stream))
+            w1.record()
+            wev.append((w0, w1))
 
     def sync_all():
         torch.cuda.synchronize()
@@ -243,6 +249,7 @@ def main():
         step_device()
     sync_all()
     model.set_option("reset_stats", 1)
+    wev.clear()
     sampler = ClockSampler(local)
     if rank == 0:
         sampler.start()
@@ -255,6 +262,7 @@ def main():
     ms = e0.elapsed_time(e1) / args.steps
     stats = {s: model.stat(s) / args.steps for s in
              ("ms_prep", "ms_stage1", "ms_rerank", "ms_exact", "launches", "uncertified")}
+    stats["ms_weights"] = sum(a.elapsed_time(b) for a, b in wev) / max(len(wev), 1)
     if G > 1:
         t = torch.tensor([ms], device=dev)
         dist.all_reduce(t, op=dist.ReduceOp.MAX)
@@ -338,10 +346,15 @@ def main():
                 "stages_ms": {kk: vv for kk, vv in stats.items() if kk.startswith("ms_")},
                 # HBM-bound stages: re-rank gathers c candidate rows per query
                 # (c*d*8 + d*8 + k*12 bytes); weighting reads k*(8+4+8) and writes 8 bytes per query
+                # (a row's buffer ends with keep..CAP candidates: keep is the lower bound used here)
                 "roofline_stages": {
-                    "rerank": {"bound": "hbm", "bytes_per_query": int(model.stat("tc_cap")) * d * 8 + d * 8 + k * 12,
-                               "achieved": (ql * (model.stat("tc_cap") * d * 8 + d * 8 + k * 12) / 1e9) / (stats["ms_rerank"] * 1e-3)
-                               if stats["ms_rerank"] > 0 else None, "peak": pk["hbm"], "unit": "GB/s"}},
+                    "rerank": {"bound": "hbm", "bytes_per_query": int(model.stat("tc_keep")) * d * 8 + d * 8 + k * 12,
+                               "ms": stats["ms_rerank"],
+                               "achieved": (ql * (model.stat("tc_keep") * d * 8 + d * 8 + k * 12) / 1e9) / (stats["ms_rerank"] * 1e-3)
+                               if stats["ms_rerank"] > 0 else None, "peak": pk["hbm"], "unit": "GB/s"},
+                    "weights": {"bound": "hbm", "bytes_per_query": k * 20 + 8, "ms": stats["ms_weights"],
+                                "achieved": (ql * (k * 20 + 8) / 1e9) / (stats["ms_weights"] * 1e-3)
+                                if stats["ms_weights"] > 0 else None, "peak": pk["hbm"], "unit": "GB/s"}},
                 "uncertified_per_step": stats["uncertified"],
                 "tc": {"cap": model.stat("tc_cap"), "keep": model.stat("tc_keep"), "slots": model.stat("tc_slots"), "halves": model.stat("tc_halves"),
                        "K": model.stat("tc_K"), "mode": args.tc_mode, "sub": args.tc_sub, "flags": args.tc_flags},

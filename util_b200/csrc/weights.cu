@@ -105,6 +105,69 @@ avg_shepard_kernel(const double* __restrict__ d2, int64_t q,
   }
 }
 
+// Same arithmetic, one THREAD per query, for k <= KMAX <= 32: the k distances and weights of a query
+// live in registers, so the index-order sums are plain loops instead of 2k shuffles by a half-empty
+// warp (k = 16: 1.0 ms -> see profiles/r01 for 10^6 queries).  A warp reads 32 consecutive rows of
+// d2 / idx, i.e. contiguous memory; only the y gather is scattered.
+template <int KMAX>
+__global__ void __launch_bounds__(128)
+avg_shepard_thread_kernel(const double* __restrict__ d2, int64_t q, int k, int method,
+                          const int32_t* __restrict__ idx, const double* __restrict__ y, int r,
+                          double* __restrict__ wts, int32_t* __restrict__ cnt, int32_t* __restrict__ err,
+                          double* __restrict__ out) {
+  const int64_t p = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
+  if (p >= q) return;
+  double w[KMAX];
+  if (method == B200_AVERAGE) {
+    const double a = 1.0 / (double)k;  // nearest_neighbor/__init__.py:12
+#pragma unroll
+    for (int i = 0; i < KMAX; ++i) w[i] = a;
+  } else {
+    double mn = CUDART_INF, mx = 0.0;
+#pragma unroll
+    for (int i = 0; i < KMAX; ++i) {
+      w[i] = 0.0;
+      if (i < k) {
+        w[i] = sqrt(d2[p * k + i]);  // weight.f90:13-15 (the kNN stage's exact d2, same arithmetic)
+        mn = fmin(mn, w[i]);
+        mx = fmax(mx, w[i]);
+      }
+    }
+    const double eps = 1.4901161193847656e-08;  // SQRT(EPSILON(1d0)), weight.f90:17
+    double s = 0.0;
+#pragma unroll
+    for (int i = 0; i < KMAX; ++i) {
+      if (i < k) {
+        if (mx < eps) w[i] = 1.0;                               // :22-24
+        else if (mn < eps) w[i] = w[i] < eps ? 1.0 : 0.0;        // :25-28
+        else w[i] = __ddiv_rn(1.0, __dmul_rn(w[i], w[i]));      // :29-31
+        s = __dadd_rn(s, w[i]);                                 // SUM(WTS) in index order (:34)
+      }
+    }
+#pragma unroll
+    for (int i = 0; i < KMAX; ++i) w[i] = __ddiv_rn(w[i], s);
+  }
+  if (wts) {
+#pragma unroll
+    for (int i = 0; i < KMAX; ++i)
+      if (i < k) wts[p * k + i] = w[i];
+  }
+  if (cnt) cnt[p] = k;
+  if (err) err[p] = 0;
+  if (out) {
+    int nb[KMAX];
+#pragma unroll
+    for (int i = 0; i < KMAX; ++i) nb[i] = i < k ? idx[p * k + i] : 0;
+    for (int c = 0; c < r; ++c) {
+      double s = 0.0;  // base.py:169: left to right from 0
+#pragma unroll
+      for (int i = 0; i < KMAX; ++i)
+        if (i < k) s = __dadd_rn(s, __dmul_rn(y[(int64_t)nb[i] * r + c], w[i]));
+      out[p * r + c] = s;
+    }
+  }
+}
+
 // Voronoi weights on the k neighbours: one block per query.  Shared memory holds
 // the k rows, their Gram matrix G (the reference's DOTS cache, voronoi.f90:105-129),
 // p.x_i and the per-centre maximum ratio.  Evaluated in the closed form the
@@ -244,9 +307,17 @@ int nn_weights(b200_model* m, const double* z_dev, int64_t q, int k, int method,
       set_error("nn_weights: Shepard weighting needs the kNN squared distances");
       return 1;
     }
-    avg_shepard_kernel<<<(unsigned)((threads + 255) / 256), 256, 0, st>>>(
-        d2_dev, q, k, method, idx_dev, y_dev, r, wts_dev, cnt_dev, err_dev,
-        y_dev ? out_dev : nullptr);
+    double* outp = y_dev ? out_dev : nullptr;
+    const unsigned tb = (unsigned)((q + 127) / 128);
+    if (k <= 8 && q >= 4096)
+      avg_shepard_thread_kernel<8><<<tb, 128, 0, st>>>(d2_dev, q, k, method, idx_dev, y_dev, r, wts_dev, cnt_dev, err_dev, outp);
+    else if (k <= 16 && q >= 4096)
+      avg_shepard_thread_kernel<16><<<tb, 128, 0, st>>>(d2_dev, q, k, method, idx_dev, y_dev, r, wts_dev, cnt_dev, err_dev, outp);
+    else if (k <= 32 && q >= 4096)
+      avg_shepard_thread_kernel<32><<<tb, 128, 0, st>>>(d2_dev, q, k, method, idx_dev, y_dev, r, wts_dev, cnt_dev, err_dev, outp);
+    else
+      avg_shepard_kernel<<<(unsigned)((threads + 255) / 256), 256, 0, st>>>(d2_dev, q, k, method, idx_dev, y_dev, r, wts_dev,
+                                                                             cnt_dev, err_dev, outp);
     B200_CUDA(cudaGetLastError());
     m->st.launches += 1;
     return 0;
