@@ -159,7 +159,7 @@ __device__ __forceinline__ double sqdist_seq(const double* __restrict__ a,
   return s;
 }
 
-// Same arithmetic (dimension order, separate roundings), 16-byte loads and eight loads in flight:
+// Same arithmetic (dimension order, separate roundings), 16-byte loads, sixteen (then eight) loads in flight:
 // for gather-bound callers whose lanes each walk a different row.
 __device__ __forceinline__ double sqdist_seq_wide(const double* __restrict__ a, const double* __restrict__ b, int d) {
   double s = 0.0;
@@ -169,6 +169,20 @@ __device__ __forceinline__ double sqdist_seq_wide(const double* __restrict__ a, 
     const double2* b2 = reinterpret_cast<const double2*>(b);
     const int h = d >> 1;
     int i = 0;
+    for (; i + 16 <= h; i += 16) {  // sixteen 16-byte loads of the gathered row in flight
+      double2 va[16], vb[16];
+#pragma unroll
+      for (int e = 0; e < 16; ++e) va[e] = __ldg(a2 + i + e);
+#pragma unroll
+      for (int e = 0; e < 16; ++e) vb[e] = __ldg(b2 + i + e);
+#pragma unroll
+      for (int e = 0; e < 16; ++e) {
+        const double t0 = __dsub_rn(va[e].x, vb[e].x);
+        s = __dadd_rn(s, __dmul_rn(t0, t0));
+        const double t1 = __dsub_rn(va[e].y, vb[e].y);
+        s = __dadd_rn(s, __dmul_rn(t1, t1));
+      }
+    }
     for (; i + 8 <= h; i += 8) {
       double2 va[8], vb[8];
 #pragma unroll

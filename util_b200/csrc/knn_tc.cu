@@ -623,6 +623,22 @@ __global__ void __launch_bounds__((HALVES * 4 + 3) * 32, 1) knn_tc_kernel(const 
         if (lane == 0) ptx::mbar_arrive(ptx::smem_u32(&bar_acce[a * 2 + half]));
         if (warp == 0 && lane == 0) B200_TRACE(2, (int)it, 1);
       }
+      // ---- final trim: a row left with more than 32 entries is cut to its keep best, so the re-rank
+      // takes every query's candidates in one pass of its warp (one candidate row per lane)
+      if (p.keep <= 32 && !(p.flags & 1024)) {
+        const int keep = p.keep;
+        unsigned need = __ballot_sync(0xffffffffu, cnt > 32);
+        while (need) {
+          const int r = __ffs(need) - 1;
+          need &= need - 1;
+          const int nv = __shfl_sync(0xffffffffu, cnt, r);
+          const float nt = compact_row<CAP>(bsc, bid, RS, row0 + r, nv, keep, lane);
+          if (lane == r) {
+            tau = fminf(tau, nt);
+            cnt = keep;
+          }
+        }
+      }
       // ---- flush this block's candidate lists (coalesced, one row at a time)
       const int64_t q0 = (int64_t)qb * ROWS + row0;
       p.cand_cnt[q0 + lane] = cnt;
@@ -659,7 +675,7 @@ rerank_kernel(const double* __restrict__ x, int64_t n, int d, const double* __re
   const int w = threadIdx.x >> 5, lane = threadIdx.x & 31;
   const int64_t p = (int64_t)blockIdx.x * 8 + w;
   if (p >= q) return;
-  const int cnt = min(cand_cnt[p], cstride);
+  const int cnt = min(cand_cnt[p], min(cstride, CAP));
   const int self = self_offset >= 0 ? (int)(self_offset + p) : -1;
   const double* zp = z + p * d;
   double dd[U];
@@ -1020,7 +1036,9 @@ int knn_tc(b200_model* m, const double* z_dev, int64_t q, int k, int64_t self_of
   tc::rerank_kernel<CAPV><<<rb, 256, 0, st>>>(m->x, m->n, m->d, z_dev, q, k, self_offset, kp.cand_idx, cfg.cap, \
                                               cand_cnt, cand_tau, meta, t.scale, t.cmax, t.perm.as<int32_t>(), idx_dev, d2_dev, \
                                               fail_list, fail_cnt)
-  if (cfg.cap == 32) RERANK(32);
+  // the SS kernel's final trim leaves at most 32 candidates per query when keep <= 32
+  const bool one_pass = !ts && cfg.keep <= 32 && !(m->tc_flags & (1024 | 2048));
+  if (cfg.cap == 32 || one_pass) RERANK(32);
   else if (cfg.cap <= 64) RERANK(64);
   else RERANK(128);
 #undef RERANK
