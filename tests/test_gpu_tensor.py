@@ -84,6 +84,20 @@ def test_tensor_knn_ts_kernel_bit_exact(L, oracle, n, q, d, k):
     assert np.abs(D - est - off).max() < bound
 
 
+def test_tensor_knn_uncertified_fallbacks_agree(L, oracle):
+    """A few uncertified queries are resolved by the rescan (every point within the candidates' k-th
+    distance, ranked exactly); many, or tc_flags bit 12, by the split brute-force scan.  Same answer."""
+    x, z = synth(40000, 300, 3)  # 3-D: the error bound is loose against the tiny gaps
+    oi, od = oracle.knn(x, z, 8)
+    for nq, flags in [(300, 0), (300, 4096), (40, 0), (40, 4096)]:
+        m = L.Model(x)
+        m.set_option("knn_path", L.PATH_TENSOR)
+        m.set_option("tc_flags", flags)
+        idx, d2 = m.knn(z[:nq], 8)
+        assert m.stat("uncertified") > 0
+        assert np.array_equal(idx, oi[:nq]) and np.array_equal(d2, od[:nq])
+
+
 def test_tensor_knn_self_excluding(L, oracle):
     x, _ = synth(15000, 1, 16)
     m = L.Model(x)

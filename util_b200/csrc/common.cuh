@@ -123,6 +123,8 @@ int knn_dispatch(b200_model* m, const double* z_dev, int64_t q, int k, int64_t s
 int knn_exact(b200_model* m, const double* z_dev, int64_t q, int k, int64_t self_offset,
               int32_t* idx_dev, double* d2_dev, const int32_t* qsel, int64_t nsel,
               cudaStream_t st);
+int knn_rescan(b200_model* m, const double* z_dev, int64_t q, int k, int64_t self_offset, int32_t* idx_dev,
+               double* d2_dev, const int32_t* fail_list, int nf, cudaStream_t st);
 int merge_topk(const double* d2_parts, const int32_t* idx_parts, int parts, int64_t q, int k,
                double* d2_out, int32_t* idx_out, cudaStream_t st);
 // knn_tc.cu

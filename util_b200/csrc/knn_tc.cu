@@ -1063,7 +1063,8 @@ int knn_tc(b200_model* m, const double* z_dev, int64_t q, int k, int64_t self_of
   m->st.last_slots = cfg.slots;
   if (h_fail > 0) {
     cudaEventRecord(m->ev0, st);
-    B200_TRY(knn_exact(m, z_dev, q, k, self_offset, idx_dev, d2_dev, fail_list, h_fail, st));
+    if (m->tc_flags & 4096) B200_TRY(knn_exact(m, z_dev, q, k, self_offset, idx_dev, d2_dev, fail_list, h_fail, st));
+    else B200_TRY(knn_rescan(m, z_dev, q, k, self_offset, idx_dev, d2_dev, fail_list, h_fail, st));
     cudaEventRecord(m->ev1, st);
     B200_CUDA(cudaEventSynchronize(m->ev1));
     cudaEventElapsedTime(&ms1, m->ev0, m->ev1);
