@@ -277,12 +277,13 @@ def test_nn_predict_chunked_upload_matches_single_shot():
     (api.cu b200_nn_predict); the result must not depend on it."""
     import torch
     from util_b200 import _lib
-    n, q, d, k = 5000, 148 * 256 * 6 + 777, 4, 3
-    x, z = synth(n, q, d)
-    y = fun(x)
-    m = _lib.Model(x)
-    ref = m.nn_predict(z, k, _lib.SHEPARD, y=y, want_weights=True)          # pageable: one copy
-    zp = torch.from_numpy(z).pin_memory().numpy()
-    got = m.nn_predict(zp, k, _lib.SHEPARD, y=y, want_weights=True)         # pinned: chunked
-    for a, b in zip(ref, got):
-        assert np.array_equal(a, b)
+    n, d, k = 5000, 4, 3
+    for q in (148 * 256 * 6 + 777, 148 * 256 * 2 + 500):  # several chunks / one short chunk and the rest
+        x, z = synth(n, q, d)
+        y = fun(x)
+        m = _lib.Model(x)
+        ref = m.nn_predict(z, k, _lib.SHEPARD, y=y, want_weights=True)          # pageable: one copy
+        zp = torch.from_numpy(z).pin_memory().numpy()
+        got = m.nn_predict(zp, k, _lib.SHEPARD, y=y, want_weights=True)         # pinned: chunked
+        for a, b in zip(ref, got):
+            assert np.array_equal(a, b)

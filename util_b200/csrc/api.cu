@@ -270,13 +270,13 @@ int b200_nn_predict(b200_model* m, const double* z, int64_t q, int32_t k, int32_
   // persistent grid (sm_count blocks of 256 queries), a short first one so the kernels start early.
   const int64_t wave = (int64_t)m->sm_count * 256;
   bool chunked = false;
-  if (q >= 6 * wave && method != B200_VORONOI) {
+  if (q >= 2 * wave && method != B200_VORONOI) {
     cudaPointerAttributes at;
     chunked = cudaPointerGetAttributes(&at, z) == cudaSuccess && at.type == cudaMemoryTypeHost;
     cudaGetLastError();
   }
   const size_t row_bytes = (size_t)m->d * 8;
-  int64_t done = 0, next = chunked ? 2 * wave : q;  // [done, next) is the chunk whose copy is in flight
+  int64_t done = 0, next = chunked ? (q >= 6 * wave ? 2 * wave : wave) : q;  // [done, next): chunk whose copy is in flight
   B200_CUDA(cudaMemcpyAsync(m->zq.p, z, (size_t)next * row_bytes, cudaMemcpyHostToDevice, m->copy_stream));
   while (done < q) {
     B200_CUDA(cudaEventRecord(m->ev_copy, m->copy_stream));
