@@ -159,3 +159,25 @@ def test_tensor_knn_round_trip_at_size(L):
         t = x[sel[:50], None, c] - x[j, c]
         ref += t * t
     assert np.array_equal(ref, d2[:50])
+
+
+def test_tensor_knn_full_size_against_exact_kernel(L):
+    """BASELINE C5 data size (1M x 64): the tensor path (norm-ordered images, trims, final trim, tail round
+    of 128-query blocks, rescan fallback) must give, bit for bit, what the fp64 brute-force kernel gives
+    (itself checked against the oracle at smaller sizes), and every fitted row must find itself first."""
+    n, d, k = 1000000, 64, 16
+    x = np.random.default_rng(0).random((n, d))
+    q = 148 * 256 + 3000  # one full round of the persistent grid + a short tail round
+    z = np.random.default_rng(1).random((q, d))
+    sel = np.random.default_rng(2).choice(n, 512, replace=False)
+    z[:512] = x[sel]
+    m = L.Model(x)
+    m.set_option("knn_path", L.PATH_TENSOR)
+    idx, d2 = m.knn(z, k)
+    assert m.stat("tc_queries") == q
+    assert np.array_equal(idx[:512, 0], sel) and np.all(d2[:512, 0] == 0)
+    assert np.all(np.diff(d2, axis=1) >= 0) and idx.min() >= 0 and idx.max() < n
+    pick = np.concatenate([np.arange(0, 700), np.arange(q - 700, q)])  # both launches
+    m.set_option("knn_path", L.PATH_EXACT)
+    ei, ed = m.knn(z[pick], k)
+    assert np.array_equal(idx[pick], ei) and np.array_equal(d2[pick], ed)
