@@ -74,6 +74,17 @@ int b200_shepard_predict(b200_model* m, const double* z, int64_t q, const double
 
 /* SHEPMOD (modified_shepard.f95:10-60): radius of influence rw (n); *ier 0/1. */
 int b200_shepmod_fit(b200_model* m, double* rw, int32_t* ier);
+/* Stand-alone Voronoi() over ALL fitted points (Voronoi._predict,
+ * voronoi/__init__.py:41-62: PREDICT, voronoi/voronoi.f90:57-155, once per query
+ * against the n x n inner-product cache of _fit, :32-38).  The cache is built on
+ * the first call (n <= 4096).  Per query the points with positive weight in
+ * ascending index order: ids/wts (q,cap), cnt (q) = their number (> cap: the
+ * row was truncated, call again with a larger cap), err (q) 0 / 1 overflow /
+ * 2 duplicated fit points; optional y (n,r) -> out (q,r). */
+int b200_voronoi_predict(b200_model* m, const double* z, int64_t q, int32_t cap, int64_t* ids,
+                         double* wts, int32_t* cnt, int32_t* err, const double* y, int32_t r,
+                         double* out);
+
 /* SHEPMODVAL over a batch + ShepMod._predict's `wts > 0` filter
  * (modified_shepard.f95:83-176, modified_shepard/__init__.py:39-58).
  * ids/wts (q,cap) ascending index, cnt (q) true counts (rows with cnt > cap are

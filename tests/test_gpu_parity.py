@@ -235,6 +235,35 @@ def test_standalone_shepard_voronoi_demo_sizes(ub, oracle):
     assert relerr(pv, np.array(refv)) < RTOL
 
 
+def test_standalone_voronoi_all_points(ub, oracle):
+    """Voronoi() over all fitted points beyond what one block's shared memory holds (voronoi_all_kernel against
+    the device-resident n x n inner-product cache): supporting points, weights and predictions against the
+    oracle's PREDICT; interpolation at nodes; duplicated fit points raise as voronoi/__init__.py:56-57."""
+    for (n, q, d) in [(300, 40, 5), (700, 16, 2)]:
+        x, z = synth(n, q, d)
+        y = fun(x)
+        m = ub.Voronoi()
+        m.fit(x)
+        got = m(z)
+        for p, (ids, wts) in zip(z, got):
+            w, e = oracle.voronoi_predict(x, p)
+            assert e == 0
+            assert np.array_equal(ids, np.nonzero(w > 0)[0])
+            assert relerr(wts, w[w > 0]) < RTOL
+        m2 = ub.Voronoi()
+        m2.fit(x, y)
+        pv = np.array(m2(z))
+        ref = np.array([sum(y[i] * w for i, w in zip(ids, wts)) for ids, wts in got])
+        assert relerr(pv, ref) < RTOL
+        at_nodes = np.array(m2(x[:10]))
+        assert relerr(at_nodes, y[:10]) < RTOL
+    xd = np.vstack([x, x[:1]])
+    md = ub.Voronoi()
+    md.fit(xd)
+    with pytest.raises(ub.DuplicateInterpolationPoints):
+        md(z[:2])
+
+
 def test_auto_k_selection(ub):
     """nearest_neighbor.auto (nearest_neighbor/__init__.py:93-132): k=None picks a power of two from the
     neighbours of 100 sampled points; a response that only depends on the nearest point wants k = 1."""

@@ -34,6 +34,8 @@ _SIGNATURES = {
                                   c_i64p, c_dp, c_i32p, c_i32p, c_dp]),
     "b200_shepard_predict": (C.c_int, [C.c_void_p, c_dp, C.c_int64, c_dp, C.c_int32, c_dp, c_dp]),
     "b200_shepmod_fit": (C.c_int, [C.c_void_p, c_dp, c_i32p]),
+    "b200_voronoi_predict": (C.c_int, [C.c_void_p, c_dp, C.c_int64, C.c_int32, c_i64p, c_dp, c_i32p,
+                                       c_i32p, c_dp, C.c_int32, c_dp]),
     "b200_shepmod_predict": (C.c_int, [C.c_void_p, c_dp, C.c_int64, C.c_int32, c_i64p, c_dp, c_i32p,
                                        c_i32p, c_dp, C.c_int32, c_dp]),
     "b200_lshep_fit": (C.c_int, [C.c_void_p, c_dp, C.c_int32, c_dp, c_dp, c_i32p]),
@@ -209,6 +211,30 @@ class Model:
             if mx <= cap:
                 return ids, wts, cnt, ier, out
             cap = max(2 * cap, mx)  # a hit list overflowed: repeat with room for the longest
+
+    def voronoi_predict(self, z, cap=32, y=None):
+        """Stand-alone Voronoi over all fitted points: per query the supporting points (ascending
+        index) and weights; the list capacity grows until the longest fits."""
+        z = f64(z)
+        q = z.shape[0]
+        r = 0
+        out = None
+        if y is not None:
+            y = f64(y).reshape(self.n, -1)
+            r = y.shape[1]
+            out = np.empty((q, r))
+        cap = max(1, min(cap, self.n))
+        while True:
+            ids = np.empty((q, cap), dtype=np.int64)
+            wts = np.empty((q, cap))
+            cnt = np.empty(q, dtype=np.int32)
+            err = np.empty(q, dtype=np.int32)
+            check(lib().b200_voronoi_predict(self._h, ptr(z), q, cap, ptr(ids, c_i64p), ptr(wts),
+                                             ptr(cnt, c_i32p), ptr(err, c_i32p), ptr(y), r, ptr(out)))
+            mx = int(cnt.max()) if q else 0
+            if mx <= cap:
+                return ids, wts, cnt, err, out
+            cap = min(self.n, max(2 * cap, mx))
 
     def lshep_fit(self, f):
         f = f64(f).reshape(self.n, -1)

@@ -164,7 +164,7 @@ int b200_destroy(b200_model* m) {
   cudaSetDevice(m->device);
   cudaDeviceSynchronize();
   if (m->x) cudaFree(m->x);
-  DevBuf* bufs[] = {&m->tc.mu, &m->tc.img, &m->tc.perm, &m->rw, &m->lf, &m->la, &m->y, &m->zq, &m->idx32, &m->d2,
+  DevBuf* bufs[] = {&m->tc.mu, &m->tc.img, &m->tc.perm, &m->vor_g, &m->rw, &m->lf, &m->la, &m->y, &m->zq, &m->idx32, &m->d2,
                     &m->wts, &m->cnt, &m->err, &m->out, &m->part_d2, &m->part_idx, &m->cand,
                     &m->cand_meta, &m->zimg, &m->flags, &m->misc, &m->ids64};
   for (DevBuf* b : bufs) b->release();
@@ -429,6 +429,37 @@ int b200_shepmod_fit(b200_model* m, double* rw, int32_t* ier) {
   B200_TRY(shepmod_fit(m, 0, &e));
   if (ier) *ier = e;
   if (e == 0 && rw) B200_CUDA(cudaMemcpy(rw, m->rw.p, (size_t)m->n * 8, cudaMemcpyDeviceToHost));
+  B200_CUDA(cudaDeviceSynchronize());
+  return 0;
+}
+
+int b200_voronoi_predict(b200_model* m, const double* z, int64_t q, int32_t cap, int64_t* ids,
+                         double* wts, int32_t* cnt, int32_t* err, const double* y, int32_t r,
+                         double* out) {
+  B200_TRY(use(m));
+  if (q < 0 || cap < 1 || (y && !out)) {
+    set_error("b200_voronoi_predict: bad arguments");
+    return 1;
+  }
+  if (q == 0) return 0;
+  B200_TRY(upload_queries(m, z, q));
+  B200_TRY(upload_y(m, y, r));
+  B200_TRY(m->idx32.reserve((size_t)q * cap * 4));
+  B200_TRY(m->wts.reserve((size_t)q * cap * 8));
+  B200_TRY(m->cnt.reserve((size_t)q * 4));
+  B200_TRY(m->err.reserve((size_t)q * 4));
+  if (y) B200_TRY(m->out.reserve((size_t)q * r * 8));
+  {
+    Timer t(m, 0, &m->st.ms_weights);
+    B200_TRY(voronoi_all(m, m->zq.as<double>(), q, cap, y ? m->y.as<double>() : nullptr, r, m->idx32.as<int32_t>(),
+                         m->wts.as<double>(), m->cnt.as<int32_t>(), m->err.as<int32_t>(),
+                         y ? m->out.as<double>() : nullptr, 0));
+  }
+  if (ids) B200_TRY(fetch_idx64(m, m->idx32.as<int32_t>(), q * cap, ids));
+  if (wts) B200_CUDA(cudaMemcpy(wts, m->wts.p, (size_t)q * cap * 8, cudaMemcpyDeviceToHost));
+  if (cnt) B200_CUDA(cudaMemcpy(cnt, m->cnt.p, (size_t)q * 4, cudaMemcpyDeviceToHost));
+  if (err) B200_CUDA(cudaMemcpy(err, m->err.p, (size_t)q * 4, cudaMemcpyDeviceToHost));
+  if (y) B200_CUDA(cudaMemcpy(out, m->out.p, (size_t)q * r * 8, cudaMemcpyDeviceToHost));
   B200_CUDA(cudaDeviceSynchronize());
   return 0;
 }

@@ -91,6 +91,8 @@ struct b200_model {
   // ShepMod / LSHEP fitted state
   b200::DevBuf rw, lf, la;  // rw (n); lshep f (r,n), a (r,n,d)
   int lshep_r = 0;
+  b200::DevBuf vor_g;       // stand-alone Voronoi: n x n inner products of the fitted rows (+ overflow flag)
+  bool vor_ready = false;
   bool shepmod_ready = false, lshep_ready = false;
   // cached response values for fused weighted sums
   b200::DevBuf y;
@@ -138,6 +140,10 @@ int nn_weights(b200_model* m, const double* z_dev, int64_t q, int k, int method,
 // shepard_all.cu
 int shepard_all(b200_model* m, const double* z_dev, int64_t q, const double* y_dev, int r, double* wts_dev,
                 double* out_dev, cudaStream_t st);
+// voronoi_all.cu
+int voronoi_all(b200_model* m, const double* z_dev, int64_t q, int cap, const double* y_dev, int r,
+                int32_t* ids_dev, double* wts_dev, int32_t* cnt_dev, int32_t* err_dev, double* out_dev,
+                cudaStream_t st);
 // shepmod.cu
 int shepmod_fit(b200_model* m, cudaStream_t st, int* ier);
 int shepmod_predict(b200_model* m, const double* z_dev, int64_t q, int cap, int32_t* ids_dev,

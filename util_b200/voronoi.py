@@ -2,9 +2,10 @@
 
 As `NearestNeighbor(k, method=Voronoi)` (BASELINE.json config 4, "candidate-pruned
 by kNN") the weights on the k neighbours come from voronoi_kernel (PREDICT,
-voronoi/voronoi.f90:57-155).  Stand-alone `Voronoi()` over all n fitted points is
-served by the same kernel with k = n while its Gram matrix fits in shared
-memory (n <= 96 or so); the un-pruned large-n mesh is not built yet.
+voronoi/voronoi.f90:57-155).  Stand-alone `Voronoi()` over all n fitted points uses
+voronoi_all_kernel against the n x n inner-product matrix (the reference's `dots`
+cache, :32-38), built once on the device: n <= 4096 (128 MiB; the reference's cache
+is 20 GB at n = 50 000 -- beyond that use the kNN-pruned form, as BASELINE does).
 """
 import numpy as np
 
@@ -17,7 +18,7 @@ class DuplicateInterpolationPoints(Exception): pass
 
 class Voronoi(WeightedApproximator):
     _b200_method = _lib.VORONOI
-    _MAX_N = 96
+    _MAX_N = 4096
     points = None
     dots = None  # the reference's lazily filled n x n cache; results never depended on it
     model = None
@@ -35,15 +36,18 @@ class Voronoi(WeightedApproximator):
         self.model = _lib.Model(points, device=self.device)
 
     def _predict(self, points, display_wait_sec=3.):
-        n = self.points.shape[1]
-        ids, wts, cnt, err, _ = self.model.nn_predict(points, n, _lib.VORONOI)
+        ids, wts, cnt, err, _ = self.model.voronoi_predict(points)
         if (err == 1).any():
             raise OverflowError("The scale of the data caused a squared float to overflow, consider normalizing data.")
         if (err == 2).any():
             raise DuplicateInterpolationPoints("Some fit points were duplicated.")
-        indices, weights = [], []
-        for i in range(len(ids)):
-            o = np.argsort(ids[i, :cnt[i]])  # idx[support > 0]: ascending point index (:58-61)
-            indices.append(ids[i, :cnt[i]][o])
-            weights.append(wts[i, :cnt[i]][o])
-        return indices, weights
+        # idx[support > 0]: ascending point index (:58-61)
+        return ([ids[i, :cnt[i]] for i in range(len(ids))], [wts[i, :cnt[i]] for i in range(len(ids))])
+
+    def _predict_values(self, points, **kw):
+        _, _, _, err, out = self.model.voronoi_predict(points, y=self._y_numeric)
+        if (err == 1).any():
+            raise OverflowError("The scale of the data caused a squared float to overflow, consider normalizing data.")
+        if (err == 2).any():
+            raise DuplicateInterpolationPoints("Some fit points were duplicated.")
+        return out[:, 0]
