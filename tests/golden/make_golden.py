@@ -97,5 +97,27 @@ def main():
     print("pairwise", d.shape)
 
 
+def gen_wrappers():
+    """Split / unique of the reference (wrappers.py:13-116) around pure-Python stand-in models."""
+    from util.approximate.wrappers import Split, unique
+    from util.approximate.base import Approximator, WeightedApproximator
+    sys.path.insert(0, HERE)
+    import standins
+    xu, yu, zu, xs, ys, zs = standins.wrapper_inputs()
+    a = unique(standins.nearest_two(WeightedApproximator))()
+    a.fit(xu, yu)
+    with_values = np.array(a(zu))
+    b = unique(standins.nearest_two(WeightedApproximator))()
+    b.fit(xu)
+    rows = b(zu)
+    s = Split(standins.linear(Approximator), k=4, seed=5)
+    s.fit(xs, ys)
+    np.savez(os.path.join(HERE, "wrappers.npz"), unique_values=with_values,
+             unique_ids=np.array([list(r[0]) + [-1] * (40 - len(r[0])) for r in rows]),
+             unique_wts=np.array([list(r[1]) + [0.0] * (40 - len(r[1])) for r in rows]),
+             unique_indices=b.unique_indices, split=s(zs))
+
+
 if __name__ == "__main__":
     main()
+    gen_wrappers()

@@ -316,3 +316,36 @@ def test_nn_predict_chunked_upload_matches_single_shot():
         got = m.nn_predict(zp, k, _lib.SHEPARD, y=y, want_weights=True)         # pinned: chunked
         for a, b in zip(ref, got):
             assert np.array_equal(a, b)
+
+
+def test_wrappers_around_gpu_models(ub, oracle):
+    """Split / unique / condition (util/approximate/wrappers.py) around the CUDA-backed models."""
+    x, z = synth(3000, 50, 4)
+    y = fun(x)
+    # Split: mean of k models, each on every k-th row of the seeded shuffle (:21-36)
+    s = ub.Split(ub.NearestNeighbor, k=3, seed=1)
+    s.fit(x, y)
+    np.random.seed(1)
+    order = np.arange(len(x))
+    np.random.shuffle(order)
+    parts = []
+    for i in range(3):
+        rows = order[i::3]
+        ids, w, cnt, _ = oracle.nn_predict(x[rows], z, 1, "average")
+        parts.append(oracle.weighted_sum(ids, w, cnt, y[rows]))
+    assert relerr(s(z), np.mean(parts, axis=0)) < RTOL
+    # unique: duplicated rows collapse to their first occurrence, responses averaged (:52-80)
+    xd = np.vstack([x[:500], x[:100]])
+    yd = np.concatenate([y[:500], y[:100] + 2.0])
+    U = ub.unique(ub.NearestNeighbor)
+    m = U(k=1)
+    m.fit(xd, yd)
+    assert len(m.unique_indices) == 500
+    assert relerr(np.array(m(x[:100])), y[:100] + 1.0) < RTOL
+    # condition with an explicit map: neighbours are found in the mapped space (:172,183)
+    A = np.diag([2.0, 1.0, 0.5, 0.0])
+    C = ub.condition(ub.NearestNeighbor, A)
+    c = C(k=5)
+    c.fit(x, y)
+    ids, w, cnt, _ = oracle.nn_predict(x @ A, z @ A, 5, "average")
+    assert relerr(np.array(c(z)), oracle.weighted_sum(ids, w, cnt, y)) < RTOL

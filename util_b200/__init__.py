@@ -13,7 +13,8 @@ from .shepard import Shepard
 from .voronoi import Voronoi, DuplicateInterpolationPoints
 from .modified_shepard import ShepMod, TooFewDataPoints
 from .linear_shepard import LSHEP
+from .wrappers import Split, unique, condition
 
 __all__ = ["Approximator", "WeightedApproximator", "NearestNeighbor", "Average", "auto", "Shepard",
-           "Voronoi", "ShepMod", "LSHEP", "TooFewDataPoints", "DuplicateInterpolationPoints",
+           "Voronoi", "ShepMod", "LSHEP", "Split", "unique", "condition", "TooFewDataPoints", "DuplicateInterpolationPoints",
            "ImproperUsage", "UnexpectedType", "UnexpectedShape", "MissingOperator", "UnderdefinedModel"]
