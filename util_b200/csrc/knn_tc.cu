@@ -20,8 +20,12 @@
 //     is CERTIFIED: every non-candidate has approximate score >= tau, so with a
 //     rigorous bound E on |approximate - exact| score, exact d2_k < (tau - E +
 //     ||x_q||^2)/s^2 proves no non-candidate can enter the top k.
-//  3. Queries that fail the certificate are re-run by the exact kernel
-//     (knn_exact.cu) -- so the result is always the exact answer.
+//  3. Queries that fail the certificate are resolved exactly (knn_exact.cu: a rescan
+//     listing every point within the candidates' k-th distance when they are few, the
+//     split brute-force scan otherwise) -- so the result is always the exact answer.
+//
+// The images hold the fitted points in order of increasing centred norm (position ->
+// row map `perm`, applied by the re-rank): thresholds tighten early, fewer survivors.
 //
 // Operand layout in HBM: per 128-row tile a ready-to-use UMMA image
 // [K/8][128][8 halfs] (K-major, no swizzle: 8x16-byte core matrices contiguous),

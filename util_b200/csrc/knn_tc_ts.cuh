@@ -13,7 +13,8 @@
 //     stage loop has S-1 units of slack instead of one;
 //   * an epilogue warp copies its 64 values to registers and hands the stage back at once; the
 //     min trees, the vote, appends and compactions all run after the release;
-//   * one issuer warp per half; the B ring holds 64-row sub-tile images (one bulk copy each).
+//   * two issuer threads per half on alternate units; the B ring holds 64-row sub-tile images
+//     (one bulk copy each).
 #pragma once
 
 // One thread issues every MMA of one half.  KS: compile-time K/16 (0: run-time loop).
