@@ -74,6 +74,13 @@ int b200_shepard_predict(b200_model* m, const double* z, int64_t q, const double
 
 /* SHEPMOD (modified_shepard.f95:10-60): radius of influence rw (n); *ier 0/1. */
 int b200_shepmod_fit(b200_model* m, double* rw, int32_t* ier);
+/* EVAL_MESH (voronoi/voronoi.f90:5-44, fmodpy symbol c_eval_mesh): naive full
+ * Voronoi mesh from precomputed inner products.  Arrays column-major as the
+ * Fortran takes them: int_prods (n,n), app_int_prods (q,n) -> mesh (q,n), rows
+ * normalised to sum 1.  Host pointers; no model handle. */
+int b200_eval_mesh(int32_t device, const double* int_prods, int32_t n, const double* app_int_prods, int64_t q,
+                   double* mesh);
+
 /* Stand-alone Voronoi() over ALL fitted points (Voronoi._predict,
  * voronoi/__init__.py:41-62: PREDICT, voronoi/voronoi.f90:57-155, once per query
  * against the n x n inner-product cache of _fit, :32-38).  The cache is built on

@@ -145,6 +145,17 @@ def voronoi_predict(pts, pt):
     return w, err
 
 
+def eval_mesh(int_prods, app_int_prods):
+    """EVAL_MESH (voronoi.f90:5-44): (n,n) and (q,n) inner products -> (q,n) mesh."""
+    ip = np.asfortranarray(int_prods, dtype=np.float64)
+    ap = np.asfortranarray(app_int_prods, dtype=np.float64)
+    mesh = np.empty(ap.shape, order="F")
+    lib().orc_eval_mesh(ip.ctypes.data_as(C.POINTER(C.c_double)), C.c_int64(ip.shape[0]),
+                        ap.ctypes.data_as(C.POINTER(C.c_double)), C.c_int64(ap.shape[0]),
+                        mesh.ctypes.data_as(C.POINTER(C.c_double)))
+    return mesh
+
+
 def nn_predict(x, z, k, method="average"):
     """NearestNeighbor._predict with a sub-model: (ids (q,k), wts (q,k), cnt (q), err (q))."""
     x, z = _f64(x), _f64(z)

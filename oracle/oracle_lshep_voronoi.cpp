@@ -278,6 +278,33 @@ int orc_nn_predict(const double* x, int64_t n, int d, const double* z, int64_t q
   return 0;
 }
 
+// ---------------------------------------------------------------------------
+// EVAL_MESH (voronoi/voronoi.f90:5-44): the naive full evaluation from precomputed
+// inner products.  Arrays are column-major as the Fortran sees them: int_prods (n,n),
+// app_int_prods (q,n), mesh (q,n).  Operand order of :26-29; ratios with
+// |denominator| <= EPSILON are skipped (:30); SUM over the row in index order (:42).
+// ---------------------------------------------------------------------------
+void orc_eval_mesh(const double* ip, int64_t n, const double* ap, int64_t q, double* mesh) {
+  for (int64_t y = 0; y < q; ++y) {
+    for (int64_t xi = 0; xi < n; ++xi) {
+      double max_ratio = 0.0;
+      for (int64_t c = 0; c < n; ++c) {
+        if (c == xi) continue;
+        const double num = ap[y + c * q] - ap[y + xi * q] - ip[xi + c * n] + ip[xi + xi * n];
+        const double den = ip[c + c * n] - ip[c + xi * n] - ip[xi + c * n] + ip[xi + xi * n];
+        if (std::fabs(den) > DBL_EPSILON) {
+          const double ratio = num / den;
+          if (ratio > max_ratio) max_ratio = ratio;
+        }
+      }
+      mesh[y + xi * q] = std::max(1.0 - max_ratio, 0.0);
+    }
+    double s = 0.0;
+    for (int64_t xi = 0; xi < n; ++xi) s += mesh[y + xi * q];
+    for (int64_t xi = 0; xi < n; ++xi) mesh[y + xi * q] /= s;
+  }
+}
+
 // WeightedApproximator.predict's sum(self.y[i]*w ...) (base.py:169): left to
 // right from integer 0, one multiply and one add rounding per term.
 void orc_weighted_sum(const int64_t* ids, const double* wts, const int32_t* cnt, int64_t q,

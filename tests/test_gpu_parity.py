@@ -349,3 +349,13 @@ def test_wrappers_around_gpu_models(ub, oracle):
     c.fit(x, y)
     ids, w, cnt, _ = oracle.nn_predict(x @ A, z @ A, 5, "average")
     assert relerr(np.array(c(z)), oracle.weighted_sum(ids, w, cnt, y)) < RTOL
+
+
+def test_eval_mesh_bit_exact(oracle):
+    """b200_eval_mesh against the oracle's EVAL_MESH: same operand order, so the same bits."""
+    from util_b200.voronoi import eval_mesh
+    for (n, q, d) in [(40, 12, 3), (333, 70, 6)]:
+        x, z = synth(n, q, d)
+        ip, ap = x @ x.T, z @ x.T
+        got = eval_mesh(ip, ap)
+        assert np.array_equal(got, oracle.eval_mesh(ip, ap))

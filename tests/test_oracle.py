@@ -128,3 +128,15 @@ def test_nn_submodels(oracle):
             assert abs(w[p, :cnt[p]].sum() - 1) < 1e-13 and np.all(w[p, :cnt[p]] > 0)
         if m == "shepard":
             assert np.all(cnt == 10)
+
+
+def test_oracle_eval_mesh_agrees_with_predict(oracle):
+    """EVAL_MESH (voronoi.f90:5-44) from inner products and PREDICT (:57-155) from coordinates are the same
+    mesh up to rounding (different operand grouping); rows are convex combinations."""
+    x, z = synth(40, 12, 3)
+    mesh = oracle.eval_mesh(x @ x.T, z @ x.T)
+    assert mesh.shape == (12, 40) and np.all(mesh >= 0)
+    assert np.allclose(mesh.sum(1), 1.0, rtol=0, atol=1e-14)
+    for p, row in zip(z, mesh):
+        w, e = oracle.voronoi_predict(x, p)
+        assert e == 0 and np.allclose(row, w, rtol=1e-10, atol=1e-13)

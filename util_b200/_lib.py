@@ -34,6 +34,7 @@ _SIGNATURES = {
                                   c_i64p, c_dp, c_i32p, c_i32p, c_dp]),
     "b200_shepard_predict": (C.c_int, [C.c_void_p, c_dp, C.c_int64, c_dp, C.c_int32, c_dp, c_dp]),
     "b200_shepmod_fit": (C.c_int, [C.c_void_p, c_dp, c_i32p]),
+    "b200_eval_mesh": (C.c_int, [C.c_int32, c_dp, C.c_int32, c_dp, C.c_int64, c_dp]),
     "b200_voronoi_predict": (C.c_int, [C.c_void_p, c_dp, C.c_int64, C.c_int32, c_i64p, c_dp, c_i32p,
                                        c_i32p, c_dp, C.c_int32, c_dp]),
     "b200_shepmod_predict": (C.c_int, [C.c_void_p, c_dp, C.c_int64, C.c_int32, c_i64p, c_dp, c_i32p,

@@ -433,6 +433,34 @@ int b200_shepmod_fit(b200_model* m, double* rw, int32_t* ier) {
   return 0;
 }
 
+int b200_eval_mesh(int32_t device, const double* int_prods, int32_t n, const double* app_int_prods, int64_t q,
+                   double* mesh) {
+  B200_CUDA(cudaSetDevice(device));
+  if (n < 1 || q < 0 || !int_prods || (q > 0 && (!app_int_prods || !mesh))) {
+    set_error("b200_eval_mesh: bad arguments");
+    return 1;
+  }
+  if (q == 0) return 0;
+  DevBuf ip, ap, out;
+  int rc = ip.reserve((size_t)n * n * 8);
+  if (!rc) rc = ap.reserve((size_t)q * n * 8);
+  if (!rc) rc = out.reserve((size_t)q * n * 8);
+  if (!rc && (cudaMemcpy(ip.p, int_prods, (size_t)n * n * 8, cudaMemcpyHostToDevice) != cudaSuccess ||
+              cudaMemcpy(ap.p, app_int_prods, (size_t)q * n * 8, cudaMemcpyHostToDevice) != cudaSuccess)) {
+    set_error("b200_eval_mesh: upload failed");
+    rc = 2;
+  }
+  if (!rc) rc = eval_mesh(ip.as<double>(), n, ap.as<double>(), q, out.as<double>(), 0);
+  if (!rc && cudaMemcpy(mesh, out.p, (size_t)q * n * 8, cudaMemcpyDeviceToHost) != cudaSuccess) {
+    set_error("b200_eval_mesh: copy back failed");
+    rc = 2;
+  }
+  ip.release();
+  ap.release();
+  out.release();
+  return rc;
+}
+
 int b200_voronoi_predict(b200_model* m, const double* z, int64_t q, int32_t cap, int64_t* ids,
                          double* wts, int32_t* cnt, int32_t* err, const double* y, int32_t r,
                          double* out) {

@@ -144,6 +144,7 @@ int shepard_all(b200_model* m, const double* z_dev, int64_t q, const double* y_d
 int voronoi_all(b200_model* m, const double* z_dev, int64_t q, int cap, const double* y_dev, int r,
                 int32_t* ids_dev, double* wts_dev, int32_t* cnt_dev, int32_t* err_dev, double* out_dev,
                 cudaStream_t st);
+int eval_mesh(const double* ip_dev, int n, const double* ap_dev, int64_t q, double* mesh_dev, cudaStream_t st);
 // shepmod.cu
 int shepmod_fit(b200_model* m, cudaStream_t st, int* ier);
 int shepmod_predict(b200_model* m, const double* z_dev, int64_t q, int cap, int32_t* ids_dev,

@@ -126,7 +126,63 @@ voronoi_all_kernel(const double* __restrict__ x, int n, int d, const double* __r
   }
 }
 
+// EVAL_MESH (voronoi/voronoi.f90:5-44): the naive full evaluation from precomputed inner products,
+// column-major as the Fortran sees them: ip (n,n), ap (q,n), mesh (q,n).  Block per approximation
+// point, warp per interpolation point xi, lanes over the cell centres c; operand order of :26-29,
+// |denominator| <= EPSILON skipped (:30), row sum in index order (:42).
+__global__ void __launch_bounds__(256)
+eval_mesh_kernel(const double* __restrict__ ip, int n, const double* __restrict__ ap, int64_t q,
+                 double* __restrict__ mesh) {
+  extern __shared__ double sm[];
+  double* a = sm;        // [n] app_int_prods(y, :)
+  double* w = a + n;     // [n]
+  __shared__ double s_sum;
+  const int64_t y = blockIdx.x;
+  const int t = threadIdx.x, nt = blockDim.x;
+  for (int c = t; c < n; c += nt) a[c] = ap[y + (int64_t)c * q];
+  __syncthreads();
+  const int lane = t & 31, wid = t >> 5, nw = nt >> 5;
+  for (int xi = wid; xi < n; xi += nw) {
+    const double gxx = ip[xi + (int64_t)xi * n], axi = a[xi];
+    double mr = 0.0;
+    for (int c = lane; c < n; c += 32) {
+      if (c == xi) continue;
+      const double gxc = ip[xi + (int64_t)c * n];
+      const double num = __dadd_rn(__dsub_rn(__dsub_rn(a[c], axi), gxc), gxx);
+      const double den = __dadd_rn(__dsub_rn(__dsub_rn(ip[c + (int64_t)c * n], ip[c + (int64_t)xi * n]), gxc), gxx);
+      if (fabs(den) > 2.220446049250313e-16) {
+        const double ratio = __ddiv_rn(num, den);
+        if (ratio > mr) mr = ratio;
+      }
+    }
+    for (int s = 16; s > 0; s >>= 1) mr = fmax(mr, __shfl_xor_sync(0xffffffffu, mr, s));
+    if (lane == 0) w[xi] = fmax(__dsub_rn(1.0, mr), 0.0);
+  }
+  __syncthreads();
+  if (t == 0) {
+    double s = 0.0;
+    for (int i = 0; i < n; ++i) s = __dadd_rn(s, w[i]);
+    s_sum = s;
+  }
+  __syncthreads();
+  const double s = s_sum;
+  for (int xi = t; xi < n; xi += nt) mesh[y + (int64_t)xi * q] = __ddiv_rn(w[xi], s);
+}
+
 }  // namespace
+
+int eval_mesh(const double* ip_dev, int n, const double* ap_dev, int64_t q, double* mesh_dev, cudaStream_t st) {
+  if (q == 0 || n == 0) return 0;
+  const size_t smem = (size_t)2 * n * 8;
+  if (smem > 200 * 1024) {
+    set_error("eval_mesh: n=%d interpolation points exceed the shared-memory row buffers", n);
+    return 1;
+  }
+  B200_CUDA(cudaFuncSetAttribute(eval_mesh_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+  eval_mesh_kernel<<<(unsigned)q, 256, smem, st>>>(ip_dev, n, ap_dev, q, mesh_dev);
+  B200_CUDA(cudaGetLastError());
+  return 0;
+}
 
 int voronoi_all(b200_model* m, const double* z_dev, int64_t q, int cap, const double* y_dev, int r,
                 int32_t* ids_dev, double* wts_dev, int32_t* cnt_dev, int32_t* err_dev, double* out_dev,

@@ -51,3 +51,15 @@ class Voronoi(WeightedApproximator):
         if (err == 2).any():
             raise DuplicateInterpolationPoints("Some fit points were duplicated.")
         return out[:, 0]
+
+
+def eval_mesh(int_prods, app_int_prods, device=0):
+    """EVAL_MESH (voronoi/voronoi.f90:5-44; the reference's `voronoi_mod.eval_mesh`): inner products of
+    the interpolation points (n,n) and of the approximation points with them (q,n) -> mesh (q,n)."""
+    ip = np.asfortranarray(int_prods, dtype=np.float64)
+    ap = np.asfortranarray(app_int_prods, dtype=np.float64)
+    if ip.ndim != 2 or ip.shape[0] != ip.shape[1] or ap.ndim != 2 or ap.shape[1] != ip.shape[0]:
+        raise ValueError("eval_mesh: int_prods must be (n,n) and app_int_prods (q,n)")
+    mesh = np.empty(ap.shape, order="F")
+    _lib.check(_lib.lib().b200_eval_mesh(device, _lib.ptr(ip), ip.shape[0], _lib.ptr(ap), ap.shape[0], _lib.ptr(mesh)))
+    return mesh
