@@ -192,7 +192,9 @@ class Model:
         check(lib().b200_shepmod_fit(self._h, ptr(rw), C.byref(ier)))
         return rw, ier.value
 
-    def shepmod_predict(self, z, cap=64, y=None):
+    def shepmod_predict(self, z, cap=64, y=None, want_weights=True):
+        """want_weights=False (with y): only the fused sums, counts and codes come back; the hit lists stay
+        on the device (returned ids/wts are then None, `cap` still grows until the longest list fits)."""
         z = f64(z)
         q = z.shape[0]
         r = 0
@@ -202,14 +204,16 @@ class Model:
             r = y.shape[1]
             out = np.empty((q, r))
         while True:
-            ids = np.empty((q, cap), dtype=np.int64)
-            wts = np.empty((q, cap))
+            keep = want_weights or y is None
+            ids = np.empty((q, cap), dtype=np.int64) if keep else None
+            wts = np.empty((q, cap)) if keep else None
             cnt = np.empty(q, dtype=np.int32)
             ier = np.empty(q, dtype=np.int32)
             check(lib().b200_shepmod_predict(self._h, ptr(z), q, cap, ptr(ids, c_i64p), ptr(wts),
                                              ptr(cnt, c_i32p), ptr(ier, c_i32p), ptr(y), r, ptr(out)))
             mx = int(cnt.max()) if q else 0
             if mx <= cap:
+                self.last_cap = cap
                 return ids, wts, cnt, ier, out
             cap = max(2 * cap, mx)  # a hit list overflowed: repeat with room for the longest
 

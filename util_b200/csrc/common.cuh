@@ -91,6 +91,7 @@ struct b200_model {
   // ShepMod / LSHEP fitted state
   b200::DevBuf rw, lf, la;  // rw (n); lshep f (r,n), a (r,n,d)
   int lshep_r = 0;
+  double x_absmax = -1.0;   // max |coordinate| of the fitted rows (lazy; bound for the fp32 prefilters)
   b200::DevBuf vor_g;       // stand-alone Voronoi: n x n inner products of the fitted rows (+ overflow flag)
   bool vor_ready = false;
   bool shepmod_ready = false, lshep_ready = false;
@@ -146,6 +147,7 @@ int voronoi_all(b200_model* m, const double* z_dev, int64_t q, int cap, const do
                 cudaStream_t st);
 int eval_mesh(const double* ip_dev, int n, const double* ap_dev, int64_t q, double* mesh_dev, cudaStream_t st);
 // shepmod.cu
+int data_absmax(b200_model* m, cudaStream_t st, double* out);  // max |x_ij|, cached in the model
 int shepmod_fit(b200_model* m, cudaStream_t st, int* ier);
 int shepmod_predict(b200_model* m, const double* z_dev, int64_t q, int cap, int32_t* ids_dev,
                     double* wts_dev, int32_t* cnt_dev, int32_t* ier_dev, const double* y_dev, int r,
@@ -156,6 +158,46 @@ int lshep_predict(b200_model* m, double radius, const double* z_dev, int64_t q, 
                   int32_t* ier_dev, cudaStream_t st);
 
 __host__ __device__ inline int64_t imin64(int64_t a, int64_t b) { return a < b ? a : b; }
+
+// fp32 prefilter of the dense fp64 scans (ShepMod / LSHEP evaluation): a node certainly lies at
+// distance >= L from the query when the fp32 squared distance `af` of the fp32-rounded coordinates
+// satisfies af >= pre_thr(L).  With u = 2^-24, cm >= every |coordinate| involved, the fp32 difference
+// vector t obeys ||t|| <= dist (1+u) + g0, g0 = 2.0001 u sqrt(d) cm, and the fma chain gives
+// af <= ||t||^2 (1 + d u); so dist >= L follows from af >= (L (1+u) + g0)^2 (1 + d u).  The float
+// evaluation below rounds every step upwards with room to spare.
+__device__ __forceinline__ float pre_gap(int d, double cm) {  // g0, rounded up
+  return (float)(2.0001 * 5.9604644775390625e-08 * sqrt((double)d) * cm) * 1.000001f;
+}
+__device__ __forceinline__ float pre_thr(float L_up, float g0, float eps1) {  // L_up >= L (1+u)
+  const float lim = (L_up + g0) * 1.0000005f;
+  return lim * lim * eps1;
+}
+__device__ __forceinline__ float pre_eps1(int d) { return 1.0f + (float)(d + 16) * 2.384185791015625e-07f; }
+// Tile of `tc` fitted rows -> shared memory, as doubles [tc][d] and as floats [tc][dsf] (rows padded
+// with zeros to dsf = 4*ceil(d/4)); (row, column) advance without divisions.
+__device__ __forceinline__ void load_tile_f64_f32(const double* __restrict__ src, int tc, int d, int dsf,
+                                                  double* __restrict__ xs, float* __restrict__ xf, int t, int nt) {
+  const int step_r = nt / dsf, step_c = nt % dsf;
+  int r = t / dsf, c = t % dsf;
+  for (int e = t; e < tc * dsf; e += nt) {
+    if (c < d) {
+      const double v = src[(size_t)r * d + c];
+      xs[(size_t)r * d + c] = v;
+      xf[e] = (float)v;
+    } else {
+      xf[e] = 0.0f;
+    }
+    r += step_r;
+    c += step_c;
+    if (c >= dsf) {
+      c -= dsf;
+      ++r;
+    }
+  }
+}
+__device__ __forceinline__ float pre_up(double L) {  // float >= L (1 + 2^-24), finite or +inf
+  return (float)L * 1.0000005f;
+}
 
 // Exact fp64 arithmetic with the reference's roundings: no FMA contraction.
 __device__ __forceinline__ double sqdist_seq(const double* __restrict__ a,

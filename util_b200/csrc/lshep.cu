@@ -223,7 +223,7 @@ __global__ void __launch_bounds__(LS_QB)
 lshep_eval_kernel(const double* __restrict__ x, const double* __restrict__ f, const double* __restrict__ a,
                   const double* __restrict__ ah, const double* __restrict__ rw, double radius, int64_t n,
                   int d, const double* __restrict__ z, int64_t q, int tile_pts, double* __restrict__ out,
-                  int32_t* __restrict__ ier, int ostride) {
+                  int32_t* __restrict__ ier, int ostride, double x_absmax) {
   extern __shared__ double sm[];
   double* xs = sm;                          // [tile][d]
   double* as = xs + (size_t)tile_pts * d;   // [tile][d]   gradients, later unit normals [tile][d+1]
@@ -233,15 +233,27 @@ lshep_eval_kernel(const double* __restrict__ x, const double* __restrict__ f, co
   // (it is correctly rounded and monotone; the band is ~100 ulp wide), inside it falls back to sqrt
   double* r2lo = rs + tile_pts;
   double* r2hi = r2lo + tile_pts;
+  // fp32 prefilter (common.cuh): float copies of the tile, rows padded to a multiple of 4
+  constexpr int D4 = (DMAX + 3) / 4;
+  const int dsf = ((d + 3) / 4) * 4;
+  float* xf = reinterpret_cast<float*>(r2hi + tile_pts);  // [tile_pts][dsf]
+  float* rkf = xf + (size_t)tile_pts * dsf;               // [tile_pts] radius, rounded up
   const int t = threadIdx.x;
   const int64_t p = (int64_t)blockIdx.x * LS_QB + t;
   const bool live = p < q;
   double zq[DMAX], slope[DMAX + 1];
+  float zf[D4 * 4];
+  double cm = x_absmax;
 #pragma unroll
   for (int j = 0; j < DMAX; ++j) {
     zq[j] = (live && j < d) ? z[p * d + j] : 0.0;
+    cm = fmax(cm, fabs(zq[j]));
     slope[j] = 0.0;
   }
+#pragma unroll
+  for (int j = 0; j < D4 * 4; ++j) zf[j] = j < DMAX ? (float)zq[j] : 0.0f;
+  const float g0 = pre_gap(d, cm), eps1 = pre_eps1(d);
+  float thr_fb = CUDART_INF_F;  // while no contributor is known: nodes nearer than 1/temp still matter
   slope[DMAX] = 0.0;
   double D[DMAX + 1];
   int DI[DMAX + 1];
@@ -254,17 +266,46 @@ lshep_eval_kernel(const double* __restrict__ x, const double* __restrict__ f, co
   for (int64_t base = 0; base < n; base += tile_pts) {
     const int tc = (int)imin64(tile_pts, n - base);
     __syncthreads();
-    for (int e = t; e < tc * d; e += LS_QB) { xs[e] = x[base * d + e]; as[e] = a[base * d + e]; }
+    load_tile_f64_f32(x + base * d, tc, d, dsf, xs, xf, t, LS_QB);
+    for (int e = t; e < tc * d; e += LS_QB) as[e] = a[base * d + e];
     for (int e = t; e < tc; e += LS_QB) {
       const double rk = __dmul_rn(rw[base + e], radius);
       fs[e] = f[base + e];
       rs[e] = rk;
       r2lo[e] = rk * rk * (1.0 - 1e-14);
       r2hi[e] = rk * rk * (1.0 + 1e-14);
+      rkf[e] = pre_up(rk);
     }
     __syncthreads();
     if (!live || hit >= 0) continue;
-    for (int i = 0; i < tc; ++i) {
+    // nodes four at a time through the fp32 prefilter, the rest in index order on the exact path
+    // (see shepmod_eval_kernel)
+    for (int i0 = 0; i0 < tc && hit < 0; i0 += 4) {
+      float af[4] = {0.0f, 0.0f, 0.0f, 0.0f};
+#pragma unroll
+      for (int j4 = 0; j4 < D4; ++j4)
+        if (j4 * 4 < d) {
+#pragma unroll
+          for (int u = 0; u < 4; ++u) {
+            const float4 v = reinterpret_cast<const float4*>(xf + (size_t)(i0 + u) * dsf)[j4];
+            const float t0 = zf[j4 * 4] - v.x, t1 = zf[j4 * 4 + 1] - v.y, t2 = zf[j4 * 4 + 2] - v.z,
+                        t3 = zf[j4 * 4 + 3] - v.w;
+            af[u] = fmaf(t0, t0, af[u]);
+            af[u] = fmaf(t1, t1, af[u]);
+            af[u] = fmaf(t2, t2, af[u]);
+            af[u] = fmaf(t3, t3, af[u]);
+          }
+        }
+      unsigned need = 0;
+#pragma unroll
+      for (int u = 0; u < 4; ++u) {
+        float thr = pre_thr(rkf[i0 + u], g0, eps1);
+        if (c == 0) thr = fmaxf(thr, thr_fb);
+        if (i0 + u < tc && !(af[u] >= thr)) need |= 1u << u;
+      }
+      while (need) {
+      const int i = i0 + __ffs(need) - 1;
+      need &= need - 1;
       const double* xr = xs + (size_t)i * d;
       double df[DMAX];
       double acc = 0.0;
@@ -306,7 +347,9 @@ lshep_eval_kernel(const double* __restrict__ x, const double* __restrict__ f, co
             if (D[u2] < dm) { dm = D[u2]; jm = u2; }
           J = jm;
           temp = dm;
+          thr_fb = temp > 0.0 ? pre_thr(pre_up(1.0 / temp), g0, eps1) : CUDART_INF_F;
         }
+      }
       }
     }
   }
@@ -338,17 +381,40 @@ lshep_eval_kernel(const double* __restrict__ x, const double* __restrict__ f, co
   for (int64_t base = 0; base < n; base += tile_pts) {
     const int tc = (int)imin64(tile_pts, n - base);
     if (__syncthreads_and(!need2 || e == 2)) break;  // every query of the block is decided
-    for (int e2 = t; e2 < tc * d; e2 += LS_QB) xs[e2] = x[base * d + e2];
+    load_tile_f64_f32(x + base * d, tc, d, dsf, xs, xf, t, LS_QB);
     for (int e2 = t; e2 < tc * (d + 1); e2 += LS_QB) as[e2] = ah[base * (d + 1) + e2];
     for (int e2 = t; e2 < tc; e2 += LS_QB) {
       const double rk = __dmul_rn(rw[base + e2], radius);
       rs[e2] = rk;
       r2lo[e2] = rk * rk * (1.0 - 1e-14);
       r2hi[e2] = rk * rk * (1.0 + 1e-14);
+      rkf[e2] = pre_up(rk);
     }
     __syncthreads();
     if (!need2 || e == 2) continue;
-    for (int i = 0; i < tc; ++i) {
+    for (int i0 = 0; i0 < tc && e != 2; i0 += 4) {
+      float af[4] = {0.0f, 0.0f, 0.0f, 0.0f};
+#pragma unroll
+      for (int j4 = 0; j4 < D4; ++j4)
+        if (j4 * 4 < d) {
+#pragma unroll
+          for (int u = 0; u < 4; ++u) {
+            const float4 v = reinterpret_cast<const float4*>(xf + (size_t)(i0 + u) * dsf)[j4];
+            const float t0 = zf[j4 * 4] - v.x, t1 = zf[j4 * 4 + 1] - v.y, t2 = zf[j4 * 4 + 2] - v.z,
+                        t3 = zf[j4 * 4 + 3] - v.w;
+            af[u] = fmaf(t0, t0, af[u]);
+            af[u] = fmaf(t1, t1, af[u]);
+            af[u] = fmaf(t2, t2, af[u]);
+            af[u] = fmaf(t3, t3, af[u]);
+          }
+        }
+      unsigned need = 0;
+#pragma unroll
+      for (int u = 0; u < 4; ++u)
+        if (i0 + u < tc && !(af[u] >= pre_thr(rkf[i0 + u], g0, eps1))) need |= 1u << u;
+      while (need) {
+      const int i = i0 + __ffs(need) - 1;
+      need &= need - 1;
       const double* xr = xs + (size_t)i * d;
       double acc = 0.0;
 #pragma unroll
@@ -364,6 +430,7 @@ lshep_eval_kernel(const double* __restrict__ x, const double* __restrict__ f, co
         for (int j = 0; j < DMAX; ++j)
           if (j < d) dp = fma(slope[j], hr[j], dp);
         if (dp < 0.9) { e = 2; break; }
+      }
       }
     }
   }
@@ -471,8 +538,15 @@ int lshep_predict(b200_model* m, double radius, const double* z_dev, int64_t q, 
   if (q == 0) return 0;
   const int64_t n = m->n;
   const int d = m->d, r = m->lshep_r;
-  int tile_pts = 256;
-  const size_t smem = ((size_t)tile_pts * (2 * d + 5)) * 8;
+  const int dsf = ((d + 3) / 4) * 4;
+  const size_t per_pt = (size_t)(2 * d + 5) * 8 + (size_t)(dsf + 1) * 4;
+  int tile_pts = (int)((40 * 1024) / per_pt);  // small tiles: several blocks per SM hide the scan's latencies
+  if (tile_pts > 256) tile_pts = 256;
+  tile_pts &= ~3;
+  if (tile_pts < 4) tile_pts = 4;
+  const size_t smem = (size_t)tile_pts * per_pt;
+  double absmax = 0.0;
+  B200_TRY(data_absmax(m, st, &absmax));
   const unsigned gb = (unsigned)((q + LS_QB - 1) / LS_QB);
   for (int c = 0; c < r; ++c) {
     const double* fc = m->lf.as<double>() + (size_t)c * n;
@@ -483,7 +557,7 @@ int lshep_predict(b200_model* m, double radius, const double* z_dev, int64_t q, 
     auto kern = lshep_eval_kernel<DM>;                                                                \
     B200_CUDA(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));    \
     kern<<<gb, LS_QB, smem, st>>>(m->x, fc, ac, hc, m->rw.as<double>(), radius, n, d, z_dev, q,        \
-                                  tile_pts, out_dev + c, ier_dev + c, r);                             \
+                                  tile_pts, out_dev + c, ier_dev + c, r, absmax);                     \
   } while (0)
     if (d <= 2) LS_LAUNCH(2);
     else if (d <= 4) LS_LAUNCH(4);

@@ -24,6 +24,14 @@ int knn_dispatch(b200_model* m, const double* z_dev, int64_t q, int k, int64_t s
 
 namespace {
 
+__global__ void absmax_kernel(const double* __restrict__ x, int64_t tot, unsigned long long* __restrict__ out) {
+  double m = 0.0;
+  for (int64_t e = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; e < tot; e += (int64_t)gridDim.x * blockDim.x)
+    m = fmax(m, fabs(x[e]));  // NaN coordinates are ignored here; the exact path sees them
+  for (int o = 16; o > 0; o >>= 1) m = fmax(m, __shfl_xor_sync(0xffffffffu, m, o));
+  if ((threadIdx.x & 31) == 0) atomicMax(out, (unsigned long long)__double_as_longlong(m));
+}
+
 __global__ void rw_from_knn_kernel(const double* __restrict__ d2, int64_t n, int k,
                                    double* __restrict__ rw) {
   const int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
@@ -39,19 +47,33 @@ shepmod_eval_kernel(const double* __restrict__ x, const double* __restrict__ rw,
                     const double* __restrict__ z, int64_t q, int cap, int tile_pts,
                     int32_t* __restrict__ ids, double* __restrict__ wts, int32_t* __restrict__ cnt,
                     int32_t* __restrict__ ier, const double* __restrict__ y, int r,
-                    double* __restrict__ out) {
+                    double* __restrict__ out, double x_absmax) {
   extern __shared__ double sm[];
   double* xs = sm;                        // [tile_pts][d]
   double* rs = xs + (size_t)tile_pts * d; // [tile_pts]
   // squared-radius band: outside [lo, hi) the test sqrt(a) < rk is decided without the square root
   double* r2lo = rs + tile_pts;
   double* r2hi = r2lo + tile_pts;
+  // fp32 prefilter (common.cuh): float copies of the tile, rows padded to a multiple of 4
+  constexpr int D4 = (DMAX + 3) / 4;
+  const int dsf = ((d + 3) / 4) * 4;
+  float* xf = reinterpret_cast<float*>(r2hi + tile_pts);  // [tile_pts][dsf]
+  float* rkf = xf + (size_t)tile_pts * dsf;               // [tile_pts] radius, rounded up
   const int t = threadIdx.x;
   const int64_t p = (int64_t)blockIdx.x * SM_QB + t;
   const bool live = p < q;
   double zq[DMAX];
+  float zf[D4 * 4];
+  double cm = x_absmax;
 #pragma unroll
-  for (int j = 0; j < DMAX; ++j) zq[j] = (live && j < d) ? z[p * d + j] : 0.0;
+  for (int j = 0; j < DMAX; ++j) {
+    zq[j] = (live && j < d) ? z[p * d + j] : 0.0;
+    cm = fmax(cm, fabs(zq[j]));
+  }
+#pragma unroll
+  for (int j = 0; j < D4 * 4; ++j) zf[j] = j < DMAX ? (float)zq[j] : 0.0f;
+  const float g0 = pre_gap(d, cm), eps1 = pre_eps1(d);
+  float thr_fb = CUDART_INF_F;  // while no contributor is known: nodes nearer than 1/temp still matter
   const int m1 = d + 1;
   double D[SM_FB];
   int DI[SM_FB];
@@ -67,16 +89,47 @@ shepmod_eval_kernel(const double* __restrict__ x, const double* __restrict__ rw,
   for (int64_t base = 0; base < n; base += tile_pts) {
     const int tc = (int)imin64(tile_pts, n - base);
     __syncthreads();
-    for (int e = t; e < tc * d; e += SM_QB) xs[e] = x[base * d + e];
+    load_tile_f64_f32(x + base * d, tc, d, dsf, xs, xf, t, SM_QB);
     for (int e = t; e < tc; e += SM_QB) {
       const double rk = rw[base + e];
       rs[e] = rk;
       r2lo[e] = rk * rk * (1.0 - 1e-14);
       r2hi[e] = rk * rk * (1.0 + 1e-14);
+      rkf[e] = pre_up(rk);
     }
     __syncthreads();
     if (!live || hit >= 0) continue;
-    for (int i = 0; i < tc; ++i) {
+    // Nodes four at a time: four independent fp32 distance chains (the loop is latency bound), then
+    // the few nodes the prefilter cannot rule out take the exact path in index order.  A node is
+    // ruled out when it is certainly outside its radius and, before the first contributor, certainly
+    // not among the M+1 nearest kept for the fallback; thresholds taken at the start of a group are
+    // only ever looser than the current ones.
+    for (int i0 = 0; i0 < tc && hit < 0; i0 += 4) {
+      float af[4] = {0.0f, 0.0f, 0.0f, 0.0f};
+#pragma unroll
+      for (int j4 = 0; j4 < D4; ++j4)
+        if (j4 * 4 < d) {
+#pragma unroll
+          for (int u = 0; u < 4; ++u) {
+            const float4 v = reinterpret_cast<const float4*>(xf + (size_t)(i0 + u) * dsf)[j4];
+            const float t0 = zf[j4 * 4] - v.x, t1 = zf[j4 * 4 + 1] - v.y, t2 = zf[j4 * 4 + 2] - v.z,
+                        t3 = zf[j4 * 4 + 3] - v.w;
+            af[u] = fmaf(t0, t0, af[u]);
+            af[u] = fmaf(t1, t1, af[u]);
+            af[u] = fmaf(t2, t2, af[u]);
+            af[u] = fmaf(t3, t3, af[u]);
+          }
+        }
+      unsigned need = 0;
+#pragma unroll
+      for (int u = 0; u < 4; ++u) {
+        float thr = pre_thr(rkf[i0 + u], g0, eps1);
+        if (c == 0) thr = fmaxf(thr, thr_fb);
+        if (i0 + u < tc && !(af[u] >= thr)) need |= 1u << u;
+      }
+      while (need) {
+      const int i = i0 + __ffs(need) - 1;
+      need &= need - 1;
       const double* xr = xs + (size_t)i * d;
       double a = 0.0;
 #pragma unroll
@@ -91,7 +144,7 @@ shepmod_eval_kernel(const double* __restrict__ x, const double* __restrict__ rw,
         const double dist = sqrt(a);  // :132
         if (__dsub_rn(rk, dist) == rk) {  // :136-140
           hit = (int)(base + i);
-          break;
+          break;  // leaves the group; the outer loops test hit
         }
         const double u = __ddiv_rn(__dsub_rn(rk, dist), __dmul_rn(rk, dist));  // :143
         const double w = __dmul_rn(u, u);
@@ -112,7 +165,10 @@ shepmod_eval_kernel(const double* __restrict__ x, const double* __restrict__ rw,
             if (D[u2] < dm) { dm = D[u2]; jm = u2; }  // MINLOC: first minimum
           J = jm;
           temp = dm;
+          // a node can still enter the fallback set only with 1/dist > temp, i.e. dist < 1/temp
+          thr_fb = temp > 0.0 ? pre_thr(pre_up(1.0 / temp), g0, eps1) : CUDART_INF_F;
         }
+      }
       }
     }
   }
@@ -171,6 +227,25 @@ shepmod_eval_kernel(const double* __restrict__ x, const double* __restrict__ rw,
 
 }  // namespace
 
+int data_absmax(b200_model* m, cudaStream_t st, double* out) {
+  if (m->x_absmax < 0.0) {
+    B200_TRY(m->flags.reserve(256));
+    unsigned long long* bits = reinterpret_cast<unsigned long long*>(m->flags.as<char>() + 128);
+    B200_CUDA(cudaMemsetAsync(bits, 0, 8, st));
+    absmax_kernel<<<1024, 256, 0, st>>>(m->x, m->n * m->d, bits);
+    B200_CUDA(cudaGetLastError());
+    unsigned long long h = 0;
+    B200_CUDA(cudaMemcpyAsync(&h, bits, 8, cudaMemcpyDeviceToHost, st));
+    B200_CUDA(cudaStreamSynchronize(st));
+    double v;
+    memcpy(&v, &h, 8);
+    m->x_absmax = (v == v && v < 1e300) ? v : 1e300;  // inf -> the prefilter switches itself off
+    m->st.launches += 1;
+  }
+  *out = m->x_absmax;
+  return 0;
+}
+
 int shepmod_fit(b200_model* m, cudaStream_t st, int* ier) {
   const int64_t n = m->n;
   const int d = m->d;
@@ -208,16 +283,22 @@ int shepmod_predict(b200_model* m, const double* z_dev, int64_t q, int cap, int3
     set_error("shepmod_predict: cap=%d must be at least M+1=%d", cap, d + 1);
     return 1;
   }
-  int tile_pts = (int)((96 * 1024) / ((size_t)(d + 3) * 8));
+  const int dsf = ((d + 3) / 4) * 4;
+  const size_t per_pt = (size_t)(d + 3) * 8 + (size_t)(dsf + 1) * 4;
+  int tile_pts = (int)((40 * 1024) / per_pt);  // small tiles: five blocks per SM hide the scan's latencies
   if (tile_pts > 512) tile_pts = 512;
-  const size_t smem = (size_t)tile_pts * (d + 3) * 8;
+  tile_pts &= ~3;  // whole groups of four; keeps the float rows 16-byte aligned behind the double arrays
+  if (tile_pts < 4) tile_pts = 4;
+  const size_t smem = (size_t)tile_pts * per_pt;
   const unsigned gb = (unsigned)((q + SM_QB - 1) / SM_QB);
+  double absmax = 0.0;
+  B200_TRY(data_absmax(m, st, &absmax));
 #define SM_LAUNCH(DM)                                                                              \
   do {                                                                                             \
     auto kern = shepmod_eval_kernel<DM>;                                                           \
     B200_CUDA(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem)); \
     kern<<<gb, SM_QB, smem, st>>>(m->x, m->rw.as<double>(), m->n, d, z_dev, q, cap, tile_pts, ids_dev, \
-                                  wts_dev, cnt_dev, ier_dev, y_dev, r, y_dev ? out_dev : nullptr);  \
+                                  wts_dev, cnt_dev, ier_dev, y_dev, r, y_dev ? out_dev : nullptr, absmax); \
   } while (0)
   if (d <= 2) SM_LAUNCH(2);
   else if (d <= 4) SM_LAUNCH(4);

@@ -32,8 +32,8 @@ class ShepMod(WeightedApproximator):
 
     def _run(self, x, y=None):
         cap = max(self.capacity, self.x.shape[0] + 1)
-        ids, wts, cnt, ier, out = self.model.shepmod_predict(x, cap=cap, y=y)
-        self.capacity = max(self.capacity, ids.shape[1])
+        ids, wts, cnt, ier, out = self.model.shepmod_predict(x, cap=cap, y=y, want_weights=y is None)
+        self.capacity = max(self.capacity, self.model.last_cap)
         for code, num in zip(*np.unique(ier, return_counts=True)):
             self.ierrors[int(code)] = self.ierrors.get(int(code), 0) + int(num)  # :50
         return ids, wts, cnt, out
