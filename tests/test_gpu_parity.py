@@ -359,3 +359,40 @@ def test_eval_mesh_bit_exact(oracle):
         ip, ap = x @ x.T, z @ x.T
         got = eval_mesh(ip, ap)
         assert np.array_equal(got, oracle.eval_mesh(ip, ap))
+
+
+@pytest.mark.parametrize("shift,scale", [(1e6, 1.0), (0.0, 1e-6), (-3e3, 50.0)])
+def test_shepmod_lshep_prefilter_on_shifted_scaled_data(ub, oracle, shift, scale):
+    """The fp32 prefilter of the ShepMod / LSHEP scans must never change a result: far-offset data
+    (coordinates huge against the distances: its rounding bound swallows the radii and everything goes to
+    the exact path), tiny scales, exact hits, queries outside every radius, clustered nodes."""
+    rng = np.random.default_rng(7)
+    n, q, d = 2500, 160, 5
+    x = rng.random((n, d))
+    x[:400] = x[0] + 1e-3 * rng.random((400, d))   # a tight cluster: very small radii next to large ones
+    z = rng.random((q, d))
+    z[:15] = x[500:515]                              # exact hits
+    z[15:20] = 5.0                                   # outside every radius
+    z[20:60] = x[0] + 1e-3 * rng.random((40, d))    # inside the cluster
+    x = x * scale + shift
+    z = z * scale + shift
+    y = fun((x - shift) / scale)
+    rw_o, _ = oracle.shepmod_fit(x)
+    m = ub.ShepMod()
+    m.fit(x)
+    assert np.array_equal(m.rw, rw_o)
+    oi, ow, oc, oe = oracle.shepmod_predict(x, rw_o, z, cap=n)
+    pw = m(z)
+    for p in range(q):
+        assert np.array_equal(pw[p][0], oi[p, :oc[p]])
+        assert np.max(np.abs(pw[p][1] - ow[p, :oc[p]])) < 1e-13
+    assert m.ierrors.get(1, 0) == int((oe == 1).sum())
+    ml = ub.LSHEP()
+    ml.fit(x, y)
+    a_o, rwl, _, _ = oracle.lshep_fit(x, y)
+    g_out, g_ier = oracle.lshep_predict(x, y, ml.a[0].T, rwl * 2, z)
+    assert relerr(np.asarray(ml(z)), g_out) < RTOL
+    hist = {}
+    for e in g_ier:
+        hist[int(e)] = hist.get(int(e), 0) + 1
+    assert ml.ierrors == hist
