@@ -91,6 +91,7 @@ struct b200_model {
   // ShepMod / LSHEP fitted state
   b200::DevBuf rw, lf, la;  // rw (n); lshep f (r,n), a (r,n,d)
   int lshep_r = 0;
+  b200::DevBuf x32;         // fitted rows as floats, rows padded with zeros to 4*ceil(d/4) (fp32 prefilters; lazy)
   double x_absmax = -1.0;   // max |coordinate| of the fitted rows (lazy; bound for the fp32 prefilters)
   b200::DevBuf vor_g;       // stand-alone Voronoi: n x n inner products of the fitted rows (+ overflow flag)
   bool vor_ready = false;
@@ -148,6 +149,7 @@ int voronoi_all(b200_model* m, const double* z_dev, int64_t q, int cap, const do
 int eval_mesh(const double* ip_dev, int n, const double* ap_dev, int64_t q, double* mesh_dev, cudaStream_t st);
 // shepmod.cu
 int data_absmax(b200_model* m, cudaStream_t st, double* out);  // max |x_ij|, cached in the model
+int data_f32(b200_model* m, cudaStream_t st, const float** out);  // padded float copy of the fitted rows, cached
 int shepmod_fit(b200_model* m, cudaStream_t st, int* ier);
 int shepmod_predict(b200_model* m, const double* z_dev, int64_t q, int cap, int32_t* ids_dev,
                     double* wts_dev, int32_t* cnt_dev, int32_t* ier_dev, const double* y_dev, int r,
@@ -173,27 +175,15 @@ __device__ __forceinline__ float pre_thr(float L_up, float g0, float eps1) {  //
   return lim * lim * eps1;
 }
 __device__ __forceinline__ float pre_eps1(int d) { return 1.0f + (float)(d + 16) * 2.384185791015625e-07f; }
-// Tile of `tc` fitted rows -> shared memory, as doubles [tc][d] and as floats [tc][dsf] (rows padded
-// with zeros to dsf = 4*ceil(d/4)); (row, column) advance without divisions.
-__device__ __forceinline__ void load_tile_f64_f32(const double* __restrict__ src, int tc, int d, int dsf,
-                                                  double* __restrict__ xs, float* __restrict__ xf, int t, int nt) {
-  const int step_r = nt / dsf, step_c = nt % dsf;
-  int r = t / dsf, c = t % dsf;
-  for (int e = t; e < tc * dsf; e += nt) {
-    if (c < d) {
-      const double v = src[(size_t)r * d + c];
-      xs[(size_t)r * d + c] = v;
-      xf[e] = (float)v;
-    } else {
-      xf[e] = 0.0f;
-    }
-    r += step_r;
-    c += step_c;
-    if (c >= dsf) {
-      c -= dsf;
-      ++r;
-    }
-  }
+// Tile of `tc` fitted rows -> shared memory: doubles [tc][d] from x, floats [tc][dsf] from the padded
+// float image (dsf = 4*ceil(d/4)); both are contiguous ranges, so plain linear copies.
+__device__ __forceinline__ void load_tile_f64_f32(const double* __restrict__ src, const float* __restrict__ src32,
+                                                  int tc, int d, int dsf, double* __restrict__ xs,
+                                                  float* __restrict__ xf, int t, int nt) {
+  for (int e = t; e < tc * d; e += nt) xs[e] = src[e];
+  const float4* s4 = reinterpret_cast<const float4*>(src32);
+  float4* d4 = reinterpret_cast<float4*>(xf);
+  for (int e = t; e < tc * (dsf >> 2); e += nt) d4[e] = s4[e];
 }
 __device__ __forceinline__ float pre_up(double L) {  // float >= L (1 + 2^-24), finite or +inf
   return (float)L * 1.0000005f;

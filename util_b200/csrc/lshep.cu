@@ -220,7 +220,8 @@ constexpr int LS_QB = 128;
 
 template <int DMAX>
 __global__ void __launch_bounds__(LS_QB)
-lshep_eval_kernel(const double* __restrict__ x, const double* __restrict__ f, const double* __restrict__ a,
+lshep_eval_kernel(const double* __restrict__ x, const float* __restrict__ x32, const double* __restrict__ f,
+                  const double* __restrict__ a,
                   const double* __restrict__ ah, const double* __restrict__ rw, double radius, int64_t n,
                   int d, const double* __restrict__ z, int64_t q, int tile_pts, double* __restrict__ out,
                   int32_t* __restrict__ ier, int ostride, double x_absmax) {
@@ -266,7 +267,7 @@ lshep_eval_kernel(const double* __restrict__ x, const double* __restrict__ f, co
   for (int64_t base = 0; base < n; base += tile_pts) {
     const int tc = (int)imin64(tile_pts, n - base);
     __syncthreads();
-    load_tile_f64_f32(x + base * d, tc, d, dsf, xs, xf, t, LS_QB);
+    load_tile_f64_f32(x + base * d, x32 + base * dsf, tc, d, dsf, xs, xf, t, LS_QB);
     for (int e = t; e < tc * d; e += LS_QB) as[e] = a[base * d + e];
     for (int e = t; e < tc; e += LS_QB) {
       const double rk = __dmul_rn(rw[base + e], radius);
@@ -381,7 +382,7 @@ lshep_eval_kernel(const double* __restrict__ x, const double* __restrict__ f, co
   for (int64_t base = 0; base < n; base += tile_pts) {
     const int tc = (int)imin64(tile_pts, n - base);
     if (__syncthreads_and(!need2 || e == 2)) break;  // every query of the block is decided
-    load_tile_f64_f32(x + base * d, tc, d, dsf, xs, xf, t, LS_QB);
+    load_tile_f64_f32(x + base * d, x32 + base * dsf, tc, d, dsf, xs, xf, t, LS_QB);
     for (int e2 = t; e2 < tc * (d + 1); e2 += LS_QB) as[e2] = ah[base * (d + 1) + e2];
     for (int e2 = t; e2 < tc; e2 += LS_QB) {
       const double rk = __dmul_rn(rw[base + e2], radius);
@@ -547,6 +548,8 @@ int lshep_predict(b200_model* m, double radius, const double* z_dev, int64_t q, 
   const size_t smem = (size_t)tile_pts * per_pt;
   double absmax = 0.0;
   B200_TRY(data_absmax(m, st, &absmax));
+  const float* x32 = nullptr;
+  B200_TRY(data_f32(m, st, &x32));
   const unsigned gb = (unsigned)((q + LS_QB - 1) / LS_QB);
   for (int c = 0; c < r; ++c) {
     const double* fc = m->lf.as<double>() + (size_t)c * n;
@@ -556,7 +559,7 @@ int lshep_predict(b200_model* m, double radius, const double* z_dev, int64_t q, 
   do {                                                                                                \
     auto kern = lshep_eval_kernel<DM>;                                                                \
     B200_CUDA(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));    \
-    kern<<<gb, LS_QB, smem, st>>>(m->x, fc, ac, hc, m->rw.as<double>(), radius, n, d, z_dev, q,        \
+    kern<<<gb, LS_QB, smem, st>>>(m->x, x32, fc, ac, hc, m->rw.as<double>(), radius, n, d, z_dev, q,   \
                                   tile_pts, out_dev + c, ier_dev + c, r, absmax);                     \
   } while (0)
     if (d <= 2) LS_LAUNCH(2);

@@ -32,6 +32,14 @@ __global__ void absmax_kernel(const double* __restrict__ x, int64_t tot, unsigne
   if ((threadIdx.x & 31) == 0) atomicMax(out, (unsigned long long)__double_as_longlong(m));
 }
 
+__global__ void f32_image_kernel(const double* __restrict__ x, int64_t n, int d, int dsf, float* __restrict__ out) {
+  const int64_t e = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
+  if (e >= n * dsf) return;
+  const int64_t i = e / dsf;
+  const int j = (int)(e - i * dsf);
+  out[e] = j < d ? (float)x[i * d + j] : 0.0f;
+}
+
 __global__ void rw_from_knn_kernel(const double* __restrict__ d2, int64_t n, int k,
                                    double* __restrict__ rw) {
   const int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
@@ -43,7 +51,8 @@ constexpr int SM_FB = 72;    // fallback slots kept per thread (M+1 <= SM_FB)
 
 template <int DMAX>  // query coordinates live in registers: DMAX >= d, loops fully unrolled
 __global__ void __launch_bounds__(SM_QB)
-shepmod_eval_kernel(const double* __restrict__ x, const double* __restrict__ rw, int64_t n, int d,
+shepmod_eval_kernel(const double* __restrict__ x, const float* __restrict__ x32, const double* __restrict__ rw,
+                    int64_t n, int d,
                     const double* __restrict__ z, int64_t q, int cap, int tile_pts,
                     int32_t* __restrict__ ids, double* __restrict__ wts, int32_t* __restrict__ cnt,
                     int32_t* __restrict__ ier, const double* __restrict__ y, int r,
@@ -89,7 +98,7 @@ shepmod_eval_kernel(const double* __restrict__ x, const double* __restrict__ rw,
   for (int64_t base = 0; base < n; base += tile_pts) {
     const int tc = (int)imin64(tile_pts, n - base);
     __syncthreads();
-    load_tile_f64_f32(x + base * d, tc, d, dsf, xs, xf, t, SM_QB);
+    load_tile_f64_f32(x + base * d, x32 + base * dsf, tc, d, dsf, xs, xf, t, SM_QB);
     for (int e = t; e < tc; e += SM_QB) {
       const double rk = rw[base + e];
       rs[e] = rk;
@@ -246,6 +255,20 @@ int data_absmax(b200_model* m, cudaStream_t st, double* out) {
   return 0;
 }
 
+int data_f32(b200_model* m, cudaStream_t st, const float** out) {
+  const int dsf = ((m->d + 3) / 4) * 4;
+  const size_t bytes = (size_t)m->n * dsf * 4;
+  if (!m->x32.p) {
+    B200_TRY(m->x32.reserve(bytes));
+    const int64_t tot = m->n * dsf;
+    f32_image_kernel<<<(unsigned)((tot + 255) / 256), 256, 0, st>>>(m->x, m->n, m->d, dsf, m->x32.as<float>());
+    B200_CUDA(cudaGetLastError());
+    m->st.launches += 1;
+  }
+  *out = m->x32.as<float>();
+  return 0;
+}
+
 int shepmod_fit(b200_model* m, cudaStream_t st, int* ier) {
   const int64_t n = m->n;
   const int d = m->d;
@@ -293,11 +316,13 @@ int shepmod_predict(b200_model* m, const double* z_dev, int64_t q, int cap, int3
   const unsigned gb = (unsigned)((q + SM_QB - 1) / SM_QB);
   double absmax = 0.0;
   B200_TRY(data_absmax(m, st, &absmax));
+  const float* x32 = nullptr;
+  B200_TRY(data_f32(m, st, &x32));
 #define SM_LAUNCH(DM)                                                                              \
   do {                                                                                             \
     auto kern = shepmod_eval_kernel<DM>;                                                           \
     B200_CUDA(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem)); \
-    kern<<<gb, SM_QB, smem, st>>>(m->x, m->rw.as<double>(), m->n, d, z_dev, q, cap, tile_pts, ids_dev, \
+    kern<<<gb, SM_QB, smem, st>>>(m->x, x32, m->rw.as<double>(), m->n, d, z_dev, q, cap, tile_pts, ids_dev, \
                                   wts_dev, cnt_dev, ier_dev, y_dev, r, y_dev ? out_dev : nullptr, absmax); \
   } while (0)
   if (d <= 2) SM_LAUNCH(2);
