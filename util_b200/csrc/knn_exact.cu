@@ -32,15 +32,23 @@ __device__ __forceinline__ void topk_insert(double* bd, int* bi, int k, double d
   bi[j] = gi;
 }
 
-template <int KMAX, int QB>
+// PRE: an fp32 prefilter (common.cuh) in front of the fp64 arithmetic.  Four points at a time get
+// fp32 squared distances from float copies of the tile and of the queries; the group is skipped when
+// all four are certainly no nearer than the current k-th best (rigorous rounding bound, so the result
+// is unchanged bit for bit); otherwise it takes the fp64 path below.  Needs the model's padded float
+// image x32 ([n][dsf], dsf = 4*ceil(d/4)) and max |coordinate|.
+template <int KMAX, int QB, bool PRE = false>
 __global__ void __launch_bounds__(QB)
 knn_exact_kernel(const double* __restrict__ x, int64_t n, int d, const double* __restrict__ z,
                  int64_t q, int k, int64_t self_offset, const int32_t* __restrict__ qsel,
                  int64_t split_len, int tile_pts, int32_t* __restrict__ out_idx,
-                 double* __restrict__ out_d2, int direct) {
+                 double* __restrict__ out_d2, int direct, const float* __restrict__ x32 = nullptr, int dsf = 0,
+                 double x_absmax = 0.0) {
   extern __shared__ double sm[];
   double* zs = sm;                    // [d][QB] transposed queries
   double* xs = sm + (size_t)d * QB;   // [tile_pts][d] data tile
+  float* xsf = reinterpret_cast<float*>(xs + (size_t)tile_pts * d);  // PRE: [tile_pts][dsf]
+  float* zsf = xsf + (size_t)tile_pts * dsf;                         // PRE: [dsf][QB]
   const int t = threadIdx.x;
   const int64_t slot = (int64_t)blockIdx.x * QB + t;  // position in the (selected) query list
   const bool live = slot < q;
@@ -55,6 +63,16 @@ knn_exact_kernel(const double* __restrict__ x, int64_t n, int d, const double* _
       v = z[pp * d + j];
     }
     zs[(size_t)j * QB + qq] = v;
+    if (PRE) zsf[(size_t)j * QB + qq] = (float)v;
+  }
+  float g0 = 0.0f, eps1 = 1.0f, thrw = CUDART_INF_F;
+  if (PRE) {
+    for (int e = d * QB + t; e < dsf * QB; e += QB) zsf[e] = 0.0f;  // padding dimensions
+    __syncthreads();
+    double cm = x_absmax;
+    for (int j = 0; j < d; ++j) cm = fmax(cm, fabs(zs[(size_t)j * QB + t]));
+    g0 = pre_gap(d, cm);
+    eps1 = pre_eps1(d);
   }
 
   double bd[KMAX];
@@ -76,11 +94,38 @@ knn_exact_kernel(const double* __restrict__ x, int64_t n, int d, const double* _
       const double* src = x + base * d;
       const int tot = cnt * d;
       for (int e = t; e < tot; e += QB) xs[e] = src[e];
+      if (PRE) {
+        const float4* s4 = reinterpret_cast<const float4*>(x32 + base * dsf);
+        float4* d4 = reinterpret_cast<float4*>(xsf);
+        for (int e = t; e < cnt * (dsf >> 2); e += QB) d4[e] = s4[e];
+      }
     }
     __syncthreads();
     if (live) {
       int i = 0;
       for (; i + 4 <= cnt; i += 4) {
+        if (PRE) {
+          const int n4 = dsf >> 2;
+          const float4* q0 = reinterpret_cast<const float4*>(xsf + (size_t)i * dsf);
+          const float4 *q1 = q0 + n4, *q2 = q1 + n4, *q3 = q2 + n4;
+          float f0 = 0.0f, f1 = 0.0f, f2 = 0.0f, f3 = 0.0f;
+#pragma unroll 2
+          for (int j4 = 0; j4 < n4; ++j4) {
+            const float* zc = zsf + (size_t)(j4 * 4) * QB + t;
+            const float za = zc[0], zb = zc[QB], zcc = zc[2 * QB], zd = zc[3 * QB];
+            const float4 v0 = q0[j4], v1 = q1[j4], v2 = q2[j4], v3 = q3[j4];
+            float u;
+            u = za - v0.x; f0 = fmaf(u, u, f0); u = zb - v0.y; f0 = fmaf(u, u, f0);
+            u = zcc - v0.z; f0 = fmaf(u, u, f0); u = zd - v0.w; f0 = fmaf(u, u, f0);
+            u = za - v1.x; f1 = fmaf(u, u, f1); u = zb - v1.y; f1 = fmaf(u, u, f1);
+            u = zcc - v1.z; f1 = fmaf(u, u, f1); u = zd - v1.w; f1 = fmaf(u, u, f1);
+            u = za - v2.x; f2 = fmaf(u, u, f2); u = zb - v2.y; f2 = fmaf(u, u, f2);
+            u = zcc - v2.z; f2 = fmaf(u, u, f2); u = zd - v2.w; f2 = fmaf(u, u, f2);
+            u = za - v3.x; f3 = fmaf(u, u, f3); u = zb - v3.y; f3 = fmaf(u, u, f3);
+            u = zcc - v3.z; f3 = fmaf(u, u, f3); u = zd - v3.w; f3 = fmaf(u, u, f3);
+          }
+          if (f0 >= thrw && f1 >= thrw && f2 >= thrw && f3 >= thrw) continue;  // none can beat the k-th best
+        }
         double a0 = 0, a1 = 0, a2 = 0, a3 = 0;
         const double* r0 = xs + (size_t)i * d;
         const double* r1 = r0 + d;
@@ -101,6 +146,7 @@ knn_exact_kernel(const double* __restrict__ x, int64_t n, int d, const double* _
         if (a1 < worst && g + 1 != self) { topk_insert<KMAX>(bd, bi, k, a1, g + 1); worst = bd[k - 1]; }
         if (a2 < worst && g + 2 != self) { topk_insert<KMAX>(bd, bi, k, a2, g + 2); worst = bd[k - 1]; }
         if (a3 < worst && g + 3 != self) { topk_insert<KMAX>(bd, bi, k, a3, g + 3); worst = bd[k - 1]; }
+        if (PRE && worst < CUDART_INF) thrw = pre_thr(pre_up(sqrt(worst)), g0, eps1);
       }
       for (; i < cnt; ++i) {
         double a0 = 0;
@@ -242,21 +288,27 @@ int launch_exact(b200_model* m, const double* z, int64_t q, int k, int64_t self_
   const bool few = q <= 64;
   if (few && q <= 32) QB = 32;
   else if (few && QB > 64) QB = 64;
-  size_t zbytes = (size_t)d * QB * 8;
+  const int dsf = ((d + 3) / 4) * 4;
+  double absmax = 0.0;
+  const float* x32 = nullptr;
+  B200_TRY(data_absmax(m, st, &absmax));
+  B200_TRY(data_f32(m, st, &x32));
+  size_t zbytes = (size_t)d * QB * 8 + (size_t)dsf * QB * 4;
+  const size_t per_pt = (size_t)d * 8 + (size_t)dsf * 4;
   size_t budget = few ? 56 * 1024 : 160 * 1024;
-  if (budget < zbytes + (size_t)16 * d * 8) budget = std::min<size_t>(200 * 1024, zbytes + (size_t)16 * d * 8);
+  if (budget < zbytes + 16 * per_pt) budget = std::min<size_t>(200 * 1024, zbytes + 16 * per_pt);
   if (budget <= zbytes) {
     set_error("knn_exact: dimension %d too large for the shared-memory tiling", d);
     return 3;
   }
-  int tile_pts = (int)((budget - zbytes) / ((size_t)d * 8));
+  int tile_pts = (int)((budget - zbytes) / per_pt);
   if (tile_pts > 256) tile_pts = 256;
   tile_pts &= ~3;
   if (tile_pts < 4) {
     set_error("knn_exact: dimension %d too large for the shared-memory tiling", d);
     return 3;
   }
-  const size_t smem = zbytes + (size_t)tile_pts * d * 8;
+  const size_t smem = zbytes + (size_t)tile_pts * per_pt;
   const int64_t qblocks = (q + QB - 1) / QB;
   // split the data range so that the grid covers >= 2 waves of the SMs
   int64_t S = 1;
@@ -283,10 +335,10 @@ int launch_exact(b200_model* m, const double* z, int64_t q, int k, int64_t self_
   dim3 grid((unsigned)qblocks, (unsigned)S);
 #define LAUNCH_QB(QBV)                                                                          \
   do {                                                                                          \
-    auto kern = knn_exact_kernel<KMAX, QBV>;                                                    \
+    auto kern = knn_exact_kernel<KMAX, QBV, true>;                                              \
     B200_CUDA(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem)); \
     kern<<<grid, QBV, smem, st>>>(m->x, n, d, z, q, k, self_offset, qsel, split_len, tile_pts, oi, \
-                                  od, direct);                                                  \
+                                  od, direct, x32, dsf, absmax);                                \
   } while (0)
   if (QB == 128) LAUNCH_QB(128);
   else if (QB == 64) LAUNCH_QB(64);
@@ -583,10 +635,10 @@ int launch_noalloc(const double* x, int64_t n, int d, const double* z, int64_t q
   dim3 grid((unsigned)qblocks, (unsigned)S);
 #define NA_LAUNCH(QBV)                                                                             \
   do {                                                                                             \
-    auto kern = knn_exact_kernel<KMAX, QBV>;                                                       \
+    auto kern = knn_exact_kernel<KMAX, QBV, false>; /* no model here: no float image, no prefilter */ \
     B200_CUDA(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem)); \
     kern<<<grid, QBV, smem, st>>>(x, n, d, z, q, k, -1, nullptr, split_len, tile_pts,             \
-                                  direct ? idx : pidx, direct ? d2 : pd2, direct);                 \
+                                  direct ? idx : pidx, direct ? d2 : pd2, direct, nullptr, 0, 0.0); \
   } while (0)
   if (QB == 128) NA_LAUNCH(128);
   else if (QB == 64) NA_LAUNCH(64);
