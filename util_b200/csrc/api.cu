@@ -91,8 +91,10 @@ int knn_dispatch(b200_model* m, const double* z_dev, int64_t q, int k, int64_t s
     }
     tensor = true;
   } else if (m->knn_path == B200_PATH_AUTO) {
-    // the tensor filter pays off once the distance matrix is large
-    tensor = tc_supported(m, k) && (double)m->n * (double)q >= 2.5e8 && m->n >= 4096;
+    // the tensor filter pays off once the distance matrix is large; in very low dimension its worst-case
+    // error bound is loose against the tiny neighbour gaps and most queries would end in the exact
+    // kernel anyway (measured cross-over between d = 4 and 5, profiles/microbench/dispatch_lowd.py)
+    tensor = tc_supported(m, k) && (double)m->n * (double)q >= 2.5e8 && m->n >= 4096 && m->d >= 5;
   }
   if (tensor) return knn_tc(m, z_dev, q, k, self_offset, idx_dev, d2_dev, st);
   Timer t(m, st, &m->st.ms_exact);

@@ -399,8 +399,8 @@ int merge_topk(const double* d2_parts, const int32_t* idx_parts, int parts, int6
 // nearest are exactly the k smallest among { j : d2(q, j) <= B }.  One pass over the fitted points
 // (thread = point, the few queries broadcast from shared memory) lists those pairs -- a handful per
 // query -- and a second kernel ranks each query's list by (d2, index).  Same arithmetic as everywhere
-// (direct differences in dimension order, no FMA).  ~0.2 ms for a few queries against 10^6 points,
-// where the split brute-force scan takes 2-3 ms.
+// (direct differences in dimension order, no FMA).  ~0.5 ms for a few queries against 10^6 points,
+// where the split brute-force scan takes 2-3 ms; up to 512 queries go through in batches.
 namespace {
 
 struct RescanEntry {
@@ -529,30 +529,36 @@ int knn_rescan(b200_model* m, const double* z_dev, int64_t q, int k, int64_t sel
                double* d2_dev, const int32_t* fail_list, int nf, cudaStream_t st) {
   if (nf == 0) return 0;
   const int d = m->d;
-  const int cap = 16384;
+  const int cap = 65536;
   int tile_pts = (int)((64 * 1024) / ((size_t)(d | 1) * 8));
   tile_pts = std::min(256, (tile_pts / 32) * 32);
-  const size_t smem = ((size_t)nf * d + ((nf + 1) & ~1) + (size_t)tile_pts * (d | 1)) * 8;
-  if (nf > 64 || !d2_dev || tile_pts < 32 || smem > 200 * 1024)
+  // failed queries go through in batches whose coordinates fit next to the tile in shared memory
+  const int batch = (int)std::min<size_t>(256, (48 * 1024) / ((size_t)d * 8));
+  if (nf > 512 || batch < 1 || !d2_dev || tile_pts < 32)
     return knn_exact(m, z_dev, q, k, self_offset, idx_dev, d2_dev, fail_list, nf, st);
   B200_TRY(m->part_d2.reserve((size_t)cap * sizeof(RescanEntry)));
   B200_TRY(m->flags.reserve(256));
   int* count = m->flags.as<int>() + 24;  // [0] entries listed, [1] overflow flag
-  B200_CUDA(cudaMemsetAsync(count, 0, 8, st));
-  B200_CUDA(cudaFuncSetAttribute(rescan_scan_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
   const int64_t ntiles = (m->n + tile_pts - 1) / tile_pts;
   const unsigned grid = (unsigned)std::min<int64_t>(ntiles, (int64_t)m->sm_count * 3);
-  rescan_scan_kernel<<<grid, tile_pts, smem, st>>>(m->x, m->n, d, z_dev, fail_list, nf, k, self_offset, d2_dev, tile_pts,
-                                                   m->part_d2.as<RescanEntry>(), cap, count);
-  B200_CUDA(cudaGetLastError());
-  rescan_select_kernel<<<nf, 128, 0, st>>>(m->part_d2.as<RescanEntry>(), count, cap, fail_list, k, idx_dev, d2_dev,
-                                           count + 1);
-  B200_CUDA(cudaGetLastError());
-  int overflow = 0;
-  B200_CUDA(cudaMemcpyAsync(&overflow, count + 1, 4, cudaMemcpyDeviceToHost, st));
-  B200_CUDA(cudaStreamSynchronize(st));
-  m->st.launches += 2;
-  if (overflow) return knn_exact(m, z_dev, q, k, self_offset, idx_dev, d2_dev, fail_list, nf, st);
+  for (int lo = 0; lo < nf; lo += batch) {
+    const int nb = std::min(batch, nf - lo);
+    const int32_t* fl = fail_list + lo;
+    const size_t smem = ((size_t)nb * d + ((nb + 1) & ~1) + (size_t)tile_pts * (d | 1)) * 8;
+    B200_CUDA(cudaMemsetAsync(count, 0, 8, st));
+    B200_CUDA(cudaFuncSetAttribute(rescan_scan_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+    rescan_scan_kernel<<<grid, tile_pts, smem, st>>>(m->x, m->n, d, z_dev, fl, nb, k, self_offset, d2_dev, tile_pts,
+                                                     m->part_d2.as<RescanEntry>(), cap, count);
+    B200_CUDA(cudaGetLastError());
+    rescan_select_kernel<<<nb, 128, 0, st>>>(m->part_d2.as<RescanEntry>(), count, cap, fl, k, idx_dev, d2_dev,
+                                             count + 1);
+    B200_CUDA(cudaGetLastError());
+    int overflow = 0;
+    B200_CUDA(cudaMemcpyAsync(&overflow, count + 1, 4, cudaMemcpyDeviceToHost, st));
+    B200_CUDA(cudaStreamSynchronize(st));
+    m->st.launches += 2;
+    if (overflow) B200_TRY(knn_exact(m, z_dev, q, k, self_offset, idx_dev, d2_dev, fl, nb, st));
+  }
   return 0;
 }
 
