@@ -72,6 +72,7 @@ struct TcData {
   DevBuf mu;            // d doubles: per-dimension centre
   DevBuf img;           // tiles * 128 * K halfs, UMMA K-major no-swizzle tile images
   DevBuf perm;          // n int32: image position -> fitted row (positions ordered by centred norm)
+  DevBuf xs;            // (n,d) fp64: the fitted rows in image order, gathered by the re-rank (absent for huge sets)
 };
 
 struct Stats {

@@ -100,6 +100,15 @@ __global__ void norm_key_kernel(const double* __restrict__ x, int64_t n, int d, 
   val[i] = (int32_t)i;
 }
 
+// fitted rows in image order (fp64), for the re-rank's gathers
+__global__ void gather_rows_kernel(const double* __restrict__ x, int64_t n, int d, const int32_t* __restrict__ perm,
+                                   double* __restrict__ xs) {
+  const int64_t e = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
+  if (e >= n * d) return;
+  const int64_t i = e / d;
+  xs[e] = x[(int64_t)perm[i] * d + (e - i * d)];
+}
+
 __global__ void iota_kernel(int32_t* __restrict__ v, int64_t n) {
   const int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
   if (i < n) v[i] = (int32_t)i;
@@ -670,7 +679,7 @@ rerank_kernel(const double* __restrict__ x, int64_t n, int d, const double* __re
               int k, int64_t self_offset, const int32_t* __restrict__ cand_idx, int cstride,
               const int32_t* __restrict__ cand_cnt, const float* __restrict__ cand_tau,
               const QMeta* __restrict__ meta, double scale, double data_cmax, const int32_t* __restrict__ perm,
-              int32_t* __restrict__ out_idx, double* __restrict__ out_d2, int32_t* __restrict__ fail_list,
+              const double* __restrict__ xs, int32_t* __restrict__ out_idx, double* __restrict__ out_d2, int32_t* __restrict__ fail_list,
               int32_t* __restrict__ fail_cnt) {
   constexpr int U = CAP / 32;
   __shared__ double s_d2[8][CAP];
@@ -688,10 +697,13 @@ rerank_kernel(const double* __restrict__ x, int64_t n, int d, const double* __re
 #pragma unroll
   for (int u = 0; u < U; ++u) {
     const int j = lane + 32 * u;
-    int c = j < cnt ? cand_idx[p * cstride + j] : -1;
-    c = (c >= 0 && c < n) ? perm[c] : -1;  // image position -> fitted row (padding positions drop out)
+    const int pos = j < cnt ? cand_idx[p * cstride + j] : -1;
+    const int c = (pos >= 0 && pos < n) ? perm[pos] : -1;  // image position -> fitted row (padding positions drop out)
     const bool ok = c >= 0 && c != self;
-    dd[u] = ok ? sqdist_seq_wide(x + (int64_t)c * d, zp, d) : CUDART_INF;
+    // xs: the same rows in image (norm) order.  Neighbours are mostly low-norm points, so two thirds of
+    // the gathered rows come from the first quarter of xs and stay in L2; in fitted order they are scattered.
+    const double* rowp = xs ? xs + (int64_t)pos * d : x + (int64_t)c * d;
+    dd[u] = ok ? sqdist_seq_wide(rowp, zp, d) : CUDART_INF;
     id[u] = ok ? c : 0x7fffffff;
     s_d2[w][j] = dd[u];
     s_id[w][j] = id[u];
@@ -816,6 +828,15 @@ int tc_prepare(b200_model* m, cudaStream_t st) {
     m->st.launches += 2;
   }
   B200_CUDA(cudaGetLastError());
+  // a copy of the rows in image order for the re-rank (skipped for very large sets: it doubles the data)
+  t.xs.release();
+  if ((size_t)n * d * 8 <= ((size_t)16 << 30)) {
+    B200_TRY(t.xs.reserve((size_t)n * d * 8));
+    const int64_t tot = n * d;
+    tc::gather_rows_kernel<<<(unsigned)((tot + 255) / 256), 256, 0, st>>>(m->x, n, d, t.perm.as<int32_t>(), t.xs.as<double>());
+    B200_CUDA(cudaGetLastError());
+    m->st.launches += 1;
+  }
   B200_CUDA(cudaMemsetAsync(bits, 0, 8, st));
   tc::data_img_kernel<<<(unsigned)((npad + 127) / 128), 128, 0, st>>>(m->x, n, d, t.K, t.sub, t.rg, t.mu.as<double>(), t.scale,
                                                                        t.perm.as<int32_t>(), t.img.as<__half>(), npad, bits);
@@ -1060,7 +1081,8 @@ int knn_tc(b200_model* m, const double* z_dev, int64_t q, int k, int64_t self_of
   const unsigned rb = (unsigned)((q + 7) / 8);
 #define RERANK(CAPV)                                                                                     \
   tc::rerank_kernel<CAPV><<<rb, 256, 0, st>>>(m->x, m->n, m->d, z_dev, q, k, self_offset, kp.cand_idx, cfg.cap, \
-                                              cand_cnt, cand_tau, meta, t.scale, t.cmax, t.perm.as<int32_t>(), idx_dev, d2_dev, \
+                                              cand_cnt, cand_tau, meta, t.scale, t.cmax, t.perm.as<int32_t>(),                  \
+                                              (m->tc_flags & 16384) ? nullptr : t.xs.as<double>(), idx_dev, d2_dev, \
                                               fail_list, fail_cnt)
   // the SS kernel's final trim leaves at most 32 candidates per query when keep <= 32
   const bool one_pass = !ts && cfg.keep <= 32 && !(m->tc_flags & (1024 | 2048));
