@@ -239,6 +239,7 @@ lshep_eval_kernel(const double* __restrict__ x, const float* __restrict__ x32, c
   const int dsf = ((d + 3) / 4) * 4;
   float* xf = reinterpret_cast<float*>(r2hi + tile_pts);  // [tile_pts][dsf]
   float* rkf = xf + (size_t)tile_pts * dsf;               // [tile_pts] radius, rounded up
+  unsigned char* qn = reinterpret_cast<unsigned char*>(rkf + tile_pts);  // [tile_pts][LS_QB] per-thread node queues
   const int t = threadIdx.x;
   const int64_t p = (int64_t)blockIdx.x * LS_QB + t;
   const bool live = p < q;
@@ -279,9 +280,13 @@ lshep_eval_kernel(const double* __restrict__ x, const float* __restrict__ x32, c
     }
     __syncthreads();
     if (!live || hit >= 0) continue;
-    // nodes four at a time through the fp32 prefilter, the rest in index order on the exact path
-    // (see shepmod_eval_kernel)
-    for (int i0 = 0; i0 < tc && hit < 0; i0 += 4) {
+    // Phase A: nodes four at a time through the fp32 prefilter (see shepmod_eval_kernel); the nodes it
+    // cannot rule out are queued per thread in shared memory, in index order.  With `radius` = 2 several
+    // per cent of all nodes contribute to a query: taken inline, each lane would reach its contributors at
+    // different nodes and the warp would run the fp64 path at ~10 % lane use.  Phase B below runs it on
+    // every lane's own queue instead.  Thresholds are those at the start of the tile (only ever looser).
+    int cq = 0;
+    for (int i0 = 0; i0 < tc; i0 += 4) {
       float af[4] = {0.0f, 0.0f, 0.0f, 0.0f};
 #pragma unroll
       for (int j4 = 0; j4 < D4; ++j4)
@@ -304,9 +309,14 @@ lshep_eval_kernel(const double* __restrict__ x, const float* __restrict__ x32, c
         if (c == 0) thr = fmaxf(thr, thr_fb);
         if (i0 + u < tc && !(af[u] >= thr)) need |= 1u << u;
       }
-      while (need) {
-      const int i = i0 + __ffs(need) - 1;
-      need &= need - 1;
+#pragma unroll
+      for (int u = 0; u < 4; ++u)
+        if (need & (1u << u)) qn[(size_t)(cq++) * LS_QB + t] = (unsigned char)(i0 + u);
+    }
+    // Phase B: exact fp64 path over my queue
+    for (int e2 = 0; e2 < cq; ++e2) {
+      {
+      const int i = qn[(size_t)e2 * LS_QB + t];
       const double* xr = xs + (size_t)i * d;
       double df[DMAX];
       double acc = 0.0;
@@ -540,9 +550,9 @@ int lshep_predict(b200_model* m, double radius, const double* z_dev, int64_t q, 
   const int64_t n = m->n;
   const int d = m->d, r = m->lshep_r;
   const int dsf = ((d + 3) / 4) * 4;
-  const size_t per_pt = (size_t)(2 * d + 5) * 8 + (size_t)(dsf + 1) * 4;
-  int tile_pts = (int)((40 * 1024) / per_pt);  // small tiles: several blocks per SM hide the scan's latencies
-  if (tile_pts > 256) tile_pts = 256;
+  const size_t per_pt = (size_t)(2 * d + 5) * 8 + (size_t)(dsf + 1) * 4 + LS_QB;  // + one queue byte per thread
+  int tile_pts = (int)((56 * 1024) / per_pt);  // small tiles: several blocks per SM hide the scan's latencies
+  if (tile_pts > 256) tile_pts = 256;  // node numbers inside a tile fit the queues' bytes
   tile_pts &= ~3;
   if (tile_pts < 4) tile_pts = 4;
   const size_t smem = (size_t)tile_pts * per_pt;
