@@ -238,7 +238,7 @@ lshep_eval_kernel(const double* __restrict__ x, const float* __restrict__ x32, c
   constexpr int D4 = (DMAX + 3) / 4;
   const int dsf = ((d + 3) / 4) * 4;
   float* xf = reinterpret_cast<float*>(r2hi + tile_pts);  // [tile_pts][dsf]
-  float* rkf = xf + (size_t)tile_pts * dsf;               // [tile_pts] radius, rounded up
+  float* rkf = xf + (size_t)tile_pts * dsf;               // [tile_pts] prefilter threshold of the node's radius
   unsigned char* qn = reinterpret_cast<unsigned char*>(rkf + tile_pts);  // [tile_pts][LS_QB] per-thread node queues
   const int t = threadIdx.x;
   const int64_t p = (int64_t)blockIdx.x * LS_QB + t;
@@ -254,6 +254,15 @@ lshep_eval_kernel(const double* __restrict__ x, const float* __restrict__ x32, c
   }
 #pragma unroll
   for (int j = 0; j < D4 * 4; ++j) zf[j] = j < DMAX ? (float)zq[j] : 0.0f;
+  {  // one rounding gap for the whole block (the largest coordinate of its queries and of the data), so
+     // that a node's threshold is the same for every thread and is prepared once per tile
+    __shared__ double s_cm[32];
+    double wm = cm;
+    for (int o = 16; o > 0; o >>= 1) wm = fmax(wm, __shfl_xor_sync(0xffffffffu, wm, o));
+    if ((threadIdx.x & 31) == 0) s_cm[threadIdx.x >> 5] = wm;
+    __syncthreads();
+    for (int w2 = 0; w2 < (int)(blockDim.x >> 5); ++w2) cm = fmax(cm, s_cm[w2]);
+  }
   const float g0 = pre_gap(d, cm), eps1 = pre_eps1(d);
   float thr_fb = CUDART_INF_F;  // while no contributor is known: nodes nearer than 1/temp still matter
   slope[DMAX] = 0.0;
@@ -276,7 +285,7 @@ lshep_eval_kernel(const double* __restrict__ x, const float* __restrict__ x32, c
       rs[e] = rk;
       r2lo[e] = rk * rk * (1.0 - 1e-14);
       r2hi[e] = rk * rk * (1.0 + 1e-14);
-      rkf[e] = pre_up(rk);
+      rkf[e] = pre_thr(pre_up(rk), g0, eps1);
     }
     __syncthreads();
     if (!live || hit >= 0) continue;
@@ -305,7 +314,7 @@ lshep_eval_kernel(const double* __restrict__ x, const float* __restrict__ x32, c
       unsigned need = 0;
 #pragma unroll
       for (int u = 0; u < 4; ++u) {
-        float thr = pre_thr(rkf[i0 + u], g0, eps1);
+        float thr = rkf[i0 + u];
         if (c == 0) thr = fmaxf(thr, thr_fb);
         if (i0 + u < tc && !(af[u] >= thr)) need |= 1u << u;
       }
@@ -399,7 +408,7 @@ lshep_eval_kernel(const double* __restrict__ x, const float* __restrict__ x32, c
       rs[e2] = rk;
       r2lo[e2] = rk * rk * (1.0 - 1e-14);
       r2hi[e2] = rk * rk * (1.0 + 1e-14);
-      rkf[e2] = pre_up(rk);
+      rkf[e2] = pre_thr(pre_up(rk), g0, eps1);
     }
     __syncthreads();
     if (!need2 || e == 2) continue;
@@ -422,7 +431,7 @@ lshep_eval_kernel(const double* __restrict__ x, const float* __restrict__ x32, c
       unsigned need = 0;
 #pragma unroll
       for (int u = 0; u < 4; ++u)
-        if (i0 + u < tc && !(af[u] >= pre_thr(rkf[i0 + u], g0, eps1))) need |= 1u << u;
+        if (i0 + u < tc && !(af[u] >= rkf[i0 + u])) need |= 1u << u;
       while (need) {
       const int i = i0 + __ffs(need) - 1;
       need &= need - 1;

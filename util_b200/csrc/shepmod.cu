@@ -67,7 +67,7 @@ shepmod_eval_kernel(const double* __restrict__ x, const float* __restrict__ x32,
   constexpr int D4 = (DMAX + 3) / 4;
   const int dsf = ((d + 3) / 4) * 4;
   float* xf = reinterpret_cast<float*>(r2hi + tile_pts);  // [tile_pts][dsf]
-  float* rkf = xf + (size_t)tile_pts * dsf;               // [tile_pts] radius, rounded up
+  float* rkf = xf + (size_t)tile_pts * dsf;               // [tile_pts] prefilter threshold of the node's radius
   const int t = threadIdx.x;
   const int64_t p = (int64_t)blockIdx.x * SM_QB + t;
   const bool live = p < q;
@@ -81,6 +81,15 @@ shepmod_eval_kernel(const double* __restrict__ x, const float* __restrict__ x32,
   }
 #pragma unroll
   for (int j = 0; j < D4 * 4; ++j) zf[j] = j < DMAX ? (float)zq[j] : 0.0f;
+  {  // one rounding gap for the whole block (the largest coordinate of its queries and of the data), so
+     // that a node's threshold is the same for every thread and is prepared once per tile
+    __shared__ double s_cm[32];
+    double wm = cm;
+    for (int o = 16; o > 0; o >>= 1) wm = fmax(wm, __shfl_xor_sync(0xffffffffu, wm, o));
+    if ((threadIdx.x & 31) == 0) s_cm[threadIdx.x >> 5] = wm;
+    __syncthreads();
+    for (int w2 = 0; w2 < (int)(blockDim.x >> 5); ++w2) cm = fmax(cm, s_cm[w2]);
+  }
   const float g0 = pre_gap(d, cm), eps1 = pre_eps1(d);
   float thr_fb = CUDART_INF_F;  // while no contributor is known: nodes nearer than 1/temp still matter
   const int m1 = d + 1;
@@ -104,7 +113,7 @@ shepmod_eval_kernel(const double* __restrict__ x, const float* __restrict__ x32,
       rs[e] = rk;
       r2lo[e] = rk * rk * (1.0 - 1e-14);
       r2hi[e] = rk * rk * (1.0 + 1e-14);
-      rkf[e] = pre_up(rk);
+      rkf[e] = pre_thr(pre_up(rk), g0, eps1);
     }
     __syncthreads();
     if (!live || hit >= 0) continue;
@@ -132,7 +141,7 @@ shepmod_eval_kernel(const double* __restrict__ x, const float* __restrict__ x32,
       unsigned need = 0;
 #pragma unroll
       for (int u = 0; u < 4; ++u) {
-        float thr = pre_thr(rkf[i0 + u], g0, eps1);
+        float thr = rkf[i0 + u];
         if (c == 0) thr = fmaxf(thr, thr_fb);
         if (i0 + u < tc && !(af[u] >= thr)) need |= 1u << u;
       }
