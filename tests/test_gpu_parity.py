@@ -306,16 +306,21 @@ def test_nn_predict_chunked_upload_matches_single_shot():
     (api.cu b200_nn_predict); the result must not depend on it."""
     import torch
     from util_b200 import _lib
-    n, d, k = 5000, 4, 3
-    for q in (148 * 256 * 6 + 777, 148 * 256 * 2 + 500):  # several chunks / one short chunk and the rest
+    k = 3
+    # several chunks / one short chunk and the rest; d = 4: exact kernel, d = 5: tensor path, whose
+    # uncertified queries are resolved together after the last chunk
+    for n, d, q in ((5000, 4, 148 * 256 * 6 + 777), (5000, 4, 148 * 256 * 2 + 500), (6000, 5, 148 * 256 * 3 + 99)):
         x, z = synth(n, q, d)
         y = fun(x)
         m = _lib.Model(x)
         ref = m.nn_predict(z, k, _lib.SHEPARD, y=y, want_weights=True)          # pageable: one copy
         zp = torch.from_numpy(z).pin_memory().numpy()
+        unc0 = m.stat("uncertified")
         got = m.nn_predict(zp, k, _lib.SHEPARD, y=y, want_weights=True)         # pinned: chunked
         for a, b in zip(ref, got):
             assert np.array_equal(a, b)
+        if d == 5:
+            assert m.stat("uncertified") > unc0  # the deferred path was exercised
 
 
 def test_wrappers_around_gpu_models(ub, oracle):

@@ -46,6 +46,7 @@ int use(b200_model* m) {
     return 1;
   }
   B200_CUDA(cudaSetDevice(m->device));
+  m->defer_fallback = false;  // only b200_nn_predict's chunk loop switches it on, and off again
   return 0;
 }
 
@@ -280,6 +281,8 @@ int b200_nn_predict(b200_model* m, const double* z, int64_t q, int32_t k, int32_
   const size_t row_bytes = (size_t)m->d * 8;
   int64_t done = 0, next = chunked ? (q >= 6 * wave ? 2 * wave : wave) : q;  // [done, next): chunk whose copy is in flight
   B200_CUDA(cudaMemcpyAsync(m->zq.p, z, (size_t)next * row_bytes, cudaMemcpyHostToDevice, m->copy_stream));
+  m->deferred.clear();
+  m->defer_fallback = chunked;
   while (done < q) {
     B200_CUDA(cudaEventRecord(m->ev_copy, m->copy_stream));
     B200_CUDA(cudaEventSynchronize(m->ev_copy));
@@ -294,7 +297,14 @@ int b200_nn_predict(b200_model* m, const double* z, int64_t q, int32_t k, int32_
     const double* zc = m->zq.as<double>() + (size_t)lo * m->d;
     int32_t* ic = m->idx32.as<int32_t>() + (size_t)lo * k;
     double* dc = m->d2.as<double>() + (size_t)lo * k;
-    B200_TRY(knn_dispatch(m, zc, hi - lo, k, -1, ic, dc, 0));
+    m->defer_base = lo;
+    {
+      const int rc = knn_dispatch(m, zc, hi - lo, k, -1, ic, dc, 0);
+      if (rc) {
+        m->defer_fallback = false;
+        return rc;
+      }
+    }
     {
       Timer t(m, 0, &m->st.ms_weights);
       B200_TRY(nn_weights(m, zc, hi - lo, k, method, ic, dc, y ? m->y.as<double>() : nullptr, r,
@@ -302,6 +312,26 @@ int b200_nn_predict(b200_model* m, const double* z, int64_t q, int32_t k, int32_
                           y ? m->out.as<double>() + (size_t)lo * r : nullptr, 0));
     }
     done = hi;
+  }
+  m->defer_fallback = false;
+  m->defer_base = 0;
+  if (!m->deferred.empty()) {
+    // the uncertified queries of all chunks: one exact rescan, then their weights again
+    const int nf = (int)m->deferred.size();
+    B200_TRY(m->ids64.reserve((size_t)nf * 4 + 64));
+    int32_t* fl = m->ids64.as<int32_t>();
+    B200_CUDA(cudaMemcpy(fl, m->deferred.data(), (size_t)nf * 4, cudaMemcpyHostToDevice));
+    {
+      Timer t(m, 0, &m->st.ms_exact);
+      B200_TRY(knn_rescan(m, m->zq.as<double>(), q, k, -1, m->idx32.as<int32_t>(), m->d2.as<double>(), fl, nf, 0));
+    }
+    for (int32_t i : m->deferred) {
+      B200_TRY(nn_weights(m, m->zq.as<double>() + (size_t)i * m->d, 1, k, method, m->idx32.as<int32_t>() + (size_t)i * k,
+                          m->d2.as<double>() + (size_t)i * k, y ? m->y.as<double>() : nullptr, r,
+                          m->wts.as<double>() + (size_t)i * k, m->cnt.as<int32_t>() + i, m->err.as<int32_t>() + i,
+                          y ? m->out.as<double>() + (size_t)i * r : nullptr, 0));
+    }
+    m->deferred.clear();
   }
   if (ids) {
     const int32_t* src = method == B200_VORONOI ? m->misc.as<int32_t>() : m->idx32.as<int32_t>();

@@ -115,6 +115,11 @@ struct b200_model {
   cudaEvent_t ev0 = nullptr, ev1 = nullptr, ev2 = nullptr, ev3 = nullptr;
   cudaStream_t copy_stream = nullptr;  // host->device query chunks overlap the previous chunk's kernels
   cudaEvent_t ev_copy = nullptr;
+  // deferred fallback (b200_nn_predict's chunked batches): uncertified queries are only noted, as indices
+  // relative to the whole batch, and resolved together after the last chunk
+  bool defer_fallback = false;
+  int64_t defer_base = 0;
+  std::vector<int32_t> deferred;
   long long* dbg_trace = nullptr;  // tuning only: clock stamps of CTA 0
   float* dbg_scores = nullptr;  // tests only: raw tensor-path scores are dumped here
 };

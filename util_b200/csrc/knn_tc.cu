@@ -996,9 +996,11 @@ int knn_tc(b200_model* m, const double* z_dev, int64_t q, int k, int64_t self_of
       const int64_t q_main = rounds * m->sm_count * 2 * tc::TILE;
       B200_TRY(knn_tc(m, z_dev, q_main, k, self_offset, idx_dev, d2_dev, st));
       m->tc_halves = 1;
+      m->defer_base += q_main;
       const int rc = knn_tc(m, z_dev + (size_t)q_main * m->d, q - q_main, k,
                             self_offset >= 0 ? self_offset + q_main : -1, idx_dev + (size_t)q_main * k,
                             d2_dev + (size_t)q_main * k, st);
+      m->defer_base -= q_main;
       m->tc_halves = 0;
       m->st.last_halves = 2;
       return rc;
@@ -1109,6 +1111,13 @@ int knn_tc(b200_model* m, const double* z_dev, int64_t q, int k, int64_t self_of
   m->st.last_cap = cfg.cap;
   m->st.last_keep = cfg.keep;
   m->st.last_slots = cfg.slots;
+  if (h_fail > 0 && m->defer_fallback && h_fail <= 64 && m->deferred.size() + h_fail <= 512) {
+    // the caller resolves these after its last chunk (one pass over the fitted points instead of one per chunk)
+    std::vector<int32_t> loc(h_fail);
+    B200_CUDA(cudaMemcpy(loc.data(), fail_list, (size_t)h_fail * 4, cudaMemcpyDeviceToHost));
+    for (int32_t v : loc) m->deferred.push_back((int32_t)(v + m->defer_base));
+    return 0;
+  }
   if (h_fail > 0) {
     cudaEventRecord(m->ev0, st);
     if (m->tc_flags & 4096) B200_TRY(knn_exact(m, z_dev, q, k, self_offset, idx_dev, d2_dev, fail_list, h_fail, st));
