@@ -208,6 +208,8 @@ __device__ __forceinline__ double sqdist_seq(const double* __restrict__ a,
 
 // Same arithmetic (dimension order, separate roundings), 16-byte loads, sixteen (then eight) loads in flight:
 // for gather-bound callers whose lanes each walk a different row.
+// BPLAIN: b is read with ordinary loads (a row staged in shared memory) instead of __ldg.
+template <bool BPLAIN = false>
 __device__ __forceinline__ double sqdist_seq_wide(const double* __restrict__ a, const double* __restrict__ b, int d) {
   double s = 0.0;
   int j = 0;
@@ -221,7 +223,7 @@ __device__ __forceinline__ double sqdist_seq_wide(const double* __restrict__ a, 
 #pragma unroll
       for (int e = 0; e < 16; ++e) va[e] = __ldg(a2 + i + e);
 #pragma unroll
-      for (int e = 0; e < 16; ++e) vb[e] = __ldg(b2 + i + e);
+      for (int e = 0; e < 16; ++e) vb[e] = BPLAIN ? b2[i + e] : __ldg(b2 + i + e);
 #pragma unroll
       for (int e = 0; e < 16; ++e) {
         const double t0 = __dsub_rn(va[e].x, vb[e].x);
@@ -233,7 +235,7 @@ __device__ __forceinline__ double sqdist_seq_wide(const double* __restrict__ a, 
     for (; i + 8 <= h; i += 8) {
       double2 va[8], vb[8];
 #pragma unroll
-      for (int e = 0; e < 8; ++e) { va[e] = __ldg(a2 + i + e); vb[e] = __ldg(b2 + i + e); }
+      for (int e = 0; e < 8; ++e) { va[e] = __ldg(a2 + i + e); vb[e] = BPLAIN ? b2[i + e] : __ldg(b2 + i + e); }
 #pragma unroll
       for (int e = 0; e < 8; ++e) {
         const double t0 = __dsub_rn(va[e].x, vb[e].x);

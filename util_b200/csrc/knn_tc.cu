@@ -690,7 +690,12 @@ rerank_kernel(const double* __restrict__ x, int64_t n, int d, const double* __re
   if (p >= q) return;
   const int cnt = min(cand_cnt[p], min(cstride, CAP));
   const int self = self_offset >= 0 ? (int)(self_offset + p) : -1;
-  const double* zp = z + p * d;
+  // the query row goes to shared memory once (streaming loads: it is used by this warp only and should
+  // not push gathered rows out of L2); the lanes then read it as broadcasts
+  extern __shared__ double zsm[];
+  double* zp = zsm + (size_t)w * ((d + 1) & ~1);
+  for (int j = lane; j < d; j += 32) zp[j] = __ldcs(z + p * d + j);
+  __syncwarp();
   double dd[U];
   int id[U];
   int nvalid = 0;
@@ -703,7 +708,7 @@ rerank_kernel(const double* __restrict__ x, int64_t n, int d, const double* __re
     // xs: the same rows in image (norm) order.  Neighbours are mostly low-norm points, so two thirds of
     // the gathered rows come from the first quarter of xs and stay in L2; in fitted order they are scattered.
     const double* rowp = xs ? xs + (int64_t)pos * d : x + (int64_t)c * d;
-    dd[u] = ok ? sqdist_seq_wide(rowp, zp, d) : CUDART_INF;
+    dd[u] = ok ? sqdist_seq_wide<true>(rowp, zp, d) : CUDART_INF;
     id[u] = ok ? c : 0x7fffffff;
     s_d2[w][j] = dd[u];
     s_id[w][j] = id[u];
@@ -1082,7 +1087,7 @@ int knn_tc(b200_model* m, const double* z_dev, int64_t q, int k, int64_t self_of
   B200_CUDA(cudaMemsetAsync(fail_cnt, 0, 4, st));
   const unsigned rb = (unsigned)((q + 7) / 8);
 #define RERANK(CAPV)                                                                                     \
-  tc::rerank_kernel<CAPV><<<rb, 256, 0, st>>>(m->x, m->n, m->d, z_dev, q, k, self_offset, kp.cand_idx, cfg.cap, \
+  tc::rerank_kernel<CAPV><<<rb, 256, (size_t)8 * ((m->d + 1) & ~1) * 8, st>>>(m->x, m->n, m->d, z_dev, q, k, self_offset, kp.cand_idx, cfg.cap, \
                                               cand_cnt, cand_tau, meta, t.scale, t.cmax, t.perm.as<int32_t>(),                  \
                                               (m->tc_flags & 16384) ? nullptr : t.xs.as<double>(), idx_dev, d2_dev, \
                                               fail_list, fail_cnt)
