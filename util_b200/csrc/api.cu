@@ -177,6 +177,10 @@ int b200_destroy(b200_model* m) {
   if (m->ev3) cudaEventDestroy(m->ev3);
   if (m->ev_copy) cudaEventDestroy(m->ev_copy);
   if (m->copy_stream) cudaStreamDestroy(m->copy_stream);
+  for (int r = 0; r < 4; ++r) {
+    if (m->aux_event[r]) cudaEventDestroy(m->aux_event[r]);
+    if (m->aux_stream[r]) cudaStreamDestroy(m->aux_stream[r]);
+  }
   delete m;
   return 0;
 }

@@ -107,6 +107,9 @@ struct b200_model {
   int margin = -1;  // extra candidates kept by the tensor filter (-1: max(4, min(k/2, 16)))
   int tc_sub = 128;   // data rows per sub-tile image / UMMA N (64 or 128)
   int tc_halves = 0;  // force 128*halves query rows per CTA (0: automatic)
+  int tc_split = 0;   // internal: the data stream of this call is split over this many concurrent launches
+  cudaStream_t aux_stream[4] = {nullptr, nullptr, nullptr, nullptr};
+  cudaEvent_t aux_event[4] = {nullptr, nullptr, nullptr, nullptr};
   int tc_trace_start = 0;
   int tc_flags = 0;   // bit 0: suspend-time hint on mbarrier waits
   int tc_mode = 0;  // debug: 1/2 strip the epilogue to measure the MMA/TMA pipeline ceiling

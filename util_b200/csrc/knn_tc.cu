@@ -673,6 +673,16 @@ __global__ void __launch_bounds__((HALVES * 4 + 3) * 32, 1) knn_tc_kernel(const 
 // ------------------------------------------------------------------ fp64 re-rank
 // One warp per query: exact squared distances of its candidates (reference
 // arithmetic), rank by (d2, index), emit the k best, test the certificate.
+// Candidate lists of one query when the data stream was split over several launches (the last, partly
+// filled round of query blocks): list r holds positions relative to its sub-range, `off[r]` is that
+// sub-range's first position.  nlists = 1: the usual single list.
+struct RerankLists {
+  int nlists;
+  int64_t list_elems;   // elements between lists in cand_idx
+  int64_t meta_elems;   // elements between lists in cand_cnt / cand_tau
+  int off[4];
+};
+
 template <int CAP>
 __global__ void __launch_bounds__(256)
 rerank_kernel(const double* __restrict__ x, int64_t n, int d, const double* __restrict__ z, int64_t q,
@@ -680,7 +690,7 @@ rerank_kernel(const double* __restrict__ x, int64_t n, int d, const double* __re
               const int32_t* __restrict__ cand_cnt, const float* __restrict__ cand_tau,
               const QMeta* __restrict__ meta, double scale, double data_cmax, const int32_t* __restrict__ perm,
               const double* __restrict__ xs, int32_t* __restrict__ out_idx, double* __restrict__ out_d2, int32_t* __restrict__ fail_list,
-              int32_t* __restrict__ fail_cnt) {
+              int32_t* __restrict__ fail_cnt, const RerankLists L) {
   constexpr int U = CAP / 32;
   __shared__ double s_d2[8][CAP];
   __shared__ int s_id[8][CAP];
@@ -702,7 +712,13 @@ rerank_kernel(const double* __restrict__ x, int64_t n, int d, const double* __re
 #pragma unroll
   for (int u = 0; u < U; ++u) {
     const int j = lane + 32 * u;
-    const int pos = j < cnt ? cand_idx[p * cstride + j] : -1;
+    int pos;
+    if (L.nlists > 1) {  // pass u takes list u (each at most 32 entries after the kernel's final trim)
+      const int cu = u < L.nlists ? min(cand_cnt[u * L.meta_elems + p], 32) : 0;
+      pos = lane < cu ? cand_idx[u * L.list_elems + p * cstride + lane] + L.off[u] : -1;
+    } else {
+      pos = j < cnt ? cand_idx[p * cstride + j] : -1;
+    }
     const int c = (pos >= 0 && pos < n) ? perm[pos] : -1;  // image position -> fitted row (padding positions drop out)
     const bool ok = c >= 0 && c != self;
     // xs: the same rows in image (norm) order.  Neighbours are mostly low-norm points, so two thirds of
@@ -739,7 +755,8 @@ rerank_kernel(const double* __restrict__ x, int64_t n, int d, const double* __re
   __syncwarp();
   if (lane == 0) {
     bool good = nvalid >= k;
-    const float tau = cand_tau[p];
+    float tau = cand_tau[p];
+    for (int r = 1; r < L.nlists; ++r) tau = fminf(tau, cand_tau[r * L.meta_elems + p]);  // bound for every non-candidate
     if (good && tau < CUDART_INF_F) {
       // scaled units: every non-candidate j has  d2_j * s^2 >= tau - E + ||x_q||^2
       const QMeta mq = meta[p];
@@ -971,6 +988,8 @@ bool tc_supported(const b200_model* m, int k) {
   return use_ts(m) ? tc_config_ts(m->d, k, 0, true, 0, &c) : tc_config(m->d, k, 0, true, 128, 0, &c);
 }
 
+static bool t_tiles_ok(const b200_model* m, int split) { return m->tc.tiles >= (int64_t)split * 64; }
+
 int knn_tc(b200_model* m, const double* z_dev, int64_t q, int k, int64_t self_offset,
            int32_t* idx_dev, double* d2_dev, cudaStream_t st) {
   if (q == 0) return 0;
@@ -991,7 +1010,7 @@ int knn_tc(b200_model* m, const double* z_dev, int64_t q, int k, int64_t self_of
   // round would keep at most half the SMs busy, those queries go to a second launch with 128-query
   // blocks (twice as many, one round, ~0.64 of a full round's time).  8 GPUs x 125 k queries: 3.64
   // instead of 4 rounds.
-  if (cfg.halves == 2 && m->tc_halves == 0 && !ts && m->tc_mode == 0 && !m->dbg_scores && !m->dbg_trace &&
+  if (cfg.halves == 2 && m->tc_halves == 0 && m->tc_split == 0 && !ts && m->tc_mode == 0 && !m->dbg_scores && !m->dbg_trace &&
       !(m->tc_flags & 8192)) {
     const int64_t blocks = (q + 2 * tc::TILE - 1) / (2 * tc::TILE);
     const int64_t rounds = blocks / m->sm_count, tail = blocks - rounds * m->sm_count;
@@ -1000,13 +1019,20 @@ int knn_tc(b200_model* m, const double* z_dev, int64_t q, int k, int64_t self_of
         tc_config(m->d, k, m->margin, self_offset >= 0, m->tc.sub, 1, &c1)) {
       const int64_t q_main = rounds * m->sm_count * 2 * tc::TILE;
       B200_TRY(knn_tc(m, z_dev, q_main, k, self_offset, idx_dev, d2_dev, st));
-      m->tc_halves = 1;
+      // the tail: either 128-query blocks (tc_flags bit 15), or -- default -- the same 256-query blocks with
+      // the data stream split over S concurrent launches on the otherwise idle SMs, S candidate lists per
+      // query merged by the re-rank
+      const int split = (int)std::min<int64_t>(4, m->sm_count / tail);
+      const bool use_split = split >= 2 && cfg.keep <= 32 && t_tiles_ok(m, split) && !(m->tc_flags & 32768);
+      if (use_split) m->tc_split = split;
+      else m->tc_halves = 1;
       m->defer_base += q_main;
       const int rc = knn_tc(m, z_dev + (size_t)q_main * m->d, q - q_main, k,
                             self_offset >= 0 ? self_offset + q_main : -1, idx_dev + (size_t)q_main * k,
                             d2_dev + (size_t)q_main * k, st);
       m->defer_base -= q_main;
       m->tc_halves = 0;
+      m->tc_split = 0;
       m->st.last_halves = 2;
       return rc;
     }
@@ -1015,14 +1041,15 @@ int knn_tc(b200_model* m, const double* z_dev, int64_t q, int k, int64_t self_of
   const int rows = cfg.halves * tc::TILE;
   const int qblocks = (int)((q + rows - 1) / rows);
   const int64_t qpad = (int64_t)qblocks * rows;
+  const int S = m->tc_split > 1 ? m->tc_split : 1;  // concurrent launches over sub-ranges of the data stream
   B200_TRY(m->zimg.reserve((size_t)qpad * t.K * 2));
-  B200_TRY(m->cand.reserve((size_t)qpad * cfg.cap * 4));
-  B200_TRY(m->cand_meta.reserve((size_t)qpad * (8 + sizeof(tc::QMeta)) + 64));
+  B200_TRY(m->cand.reserve((size_t)S * qpad * cfg.cap * 4));
+  B200_TRY(m->cand_meta.reserve((size_t)qpad * (8 * S + sizeof(tc::QMeta)) + 64));
   B200_TRY(m->flags.reserve(256));
   B200_TRY(m->misc.reserve((size_t)q * 4 + 64));
   int32_t* cand_cnt = m->cand_meta.as<int32_t>();
-  float* cand_tau = reinterpret_cast<float*>(cand_cnt + qpad);
-  tc::QMeta* meta = reinterpret_cast<tc::QMeta*>(cand_tau + qpad);
+  float* cand_tau = reinterpret_cast<float*>(cand_cnt + (size_t)S * qpad);
+  tc::QMeta* meta = reinterpret_cast<tc::QMeta*>(cand_tau + (size_t)S * qpad);
   int32_t* fail_cnt = m->flags.as<int32_t>() + 8;
   int32_t* fail_list = m->misc.as<int32_t>();
   float* dbg = m->dbg_scores;
@@ -1050,26 +1077,59 @@ int knn_tc(b200_model* m, const double* z_dev, int64_t q, int k, int64_t self_of
   kp.dbg = dbg;
   kp.trace = m->dbg_trace;
   kp.trace_start = m->tc_trace_start;
-  int rc = 1;
   const bool dg = dbg != nullptr || kp.trace != nullptr || (m->tc_mode & 12);  // trace and MMA/TMA knock-outs live in the debug build
-  if (ts) {
-    if (cfg.cap == 32 && cfg.halves == 2) rc = launch_ts<32, 2>(m, kp, cfg, dg, st);
-    else if (cfg.cap == 48 && cfg.halves == 2) rc = launch_ts<48, 2>(m, kp, cfg, dg, st);
-    else if (cfg.cap == 64 && cfg.halves == 2) rc = launch_ts<64, 2>(m, kp, cfg, dg, st);
-    else if (cfg.cap == 128 && cfg.halves == 2) rc = launch_ts<128, 2>(m, kp, cfg, dg, st);
-    else if (cfg.cap == 32 && cfg.halves == 1) rc = launch_ts<32, 1>(m, kp, cfg, dg, st);
-    else if (cfg.cap == 48 && cfg.halves == 1) rc = launch_ts<48, 1>(m, kp, cfg, dg, st);
-    else if (cfg.cap == 64 && cfg.halves == 1) rc = launch_ts<64, 1>(m, kp, cfg, dg, st);
-    else if (cfg.cap == 128 && cfg.halves == 1) rc = launch_ts<128, 1>(m, kp, cfg, dg, st);
+  auto launch_one = [&](const tc::KParams& kq, cudaStream_t s_) -> int {
+    int rc = 1;
+    if (ts) {
+      if (cfg.cap == 32 && cfg.halves == 2) rc = launch_ts<32, 2>(m, kq, cfg, dg, s_);
+      else if (cfg.cap == 48 && cfg.halves == 2) rc = launch_ts<48, 2>(m, kq, cfg, dg, s_);
+      else if (cfg.cap == 64 && cfg.halves == 2) rc = launch_ts<64, 2>(m, kq, cfg, dg, s_);
+      else if (cfg.cap == 128 && cfg.halves == 2) rc = launch_ts<128, 2>(m, kq, cfg, dg, s_);
+      else if (cfg.cap == 32 && cfg.halves == 1) rc = launch_ts<32, 1>(m, kq, cfg, dg, s_);
+      else if (cfg.cap == 48 && cfg.halves == 1) rc = launch_ts<48, 1>(m, kq, cfg, dg, s_);
+      else if (cfg.cap == 64 && cfg.halves == 1) rc = launch_ts<64, 1>(m, kq, cfg, dg, s_);
+      else if (cfg.cap == 128 && cfg.halves == 1) rc = launch_ts<128, 1>(m, kq, cfg, dg, s_);
+      else set_error("tensor kNN: no kernel for cap=%d halves=%d", cfg.cap, cfg.halves);
+    } else if (cfg.cap == 32 && cfg.halves == 2) rc = launch_tc<32, 2>(m, kq, cfg, dg, s_);
+    else if (cfg.cap == 48 && cfg.halves == 2) rc = launch_tc<48, 2>(m, kq, cfg, dg, s_);
+    else if (cfg.cap == 48 && cfg.halves == 1) rc = launch_tc<48, 1>(m, kq, cfg, dg, s_);
+    else if (cfg.cap == 64 && cfg.halves == 2) rc = launch_tc<64, 2>(m, kq, cfg, dg, s_);
+    else if (cfg.cap == 128 && cfg.halves == 1) rc = launch_tc<128, 1>(m, kq, cfg, dg, s_);
+    else if (cfg.cap == 32 && cfg.halves == 1) rc = launch_tc<32, 1>(m, kq, cfg, dg, s_);
+    else if (cfg.cap == 64 && cfg.halves == 1) rc = launch_tc<64, 1>(m, kq, cfg, dg, s_);
     else set_error("tensor kNN: no kernel for cap=%d halves=%d", cfg.cap, cfg.halves);
-  } else if (cfg.cap == 32 && cfg.halves == 2) rc = launch_tc<32, 2>(m, kp, cfg, dg, st);
-  else if (cfg.cap == 48 && cfg.halves == 2) rc = launch_tc<48, 2>(m, kp, cfg, dg, st);
-  else if (cfg.cap == 48 && cfg.halves == 1) rc = launch_tc<48, 1>(m, kp, cfg, dg, st);
-  else if (cfg.cap == 64 && cfg.halves == 2) rc = launch_tc<64, 2>(m, kp, cfg, dg, st);
-  else if (cfg.cap == 128 && cfg.halves == 1) rc = launch_tc<128, 1>(m, kp, cfg, dg, st);
-  else if (cfg.cap == 32 && cfg.halves == 1) rc = launch_tc<32, 1>(m, kp, cfg, dg, st);
-  else if (cfg.cap == 64 && cfg.halves == 1) rc = launch_tc<64, 1>(m, kp, cfg, dg, st);
-  else set_error("tensor kNN: no kernel for cap=%d halves=%d", cfg.cap, cfg.halves);
+
+    return rc;
+  };
+  int rc = 1;
+  tc::RerankLists L;
+  L.nlists = S;
+  L.list_elems = (int64_t)qpad * cfg.cap;
+  L.meta_elems = qpad;
+  for (int r = 0; r < 4; ++r) L.off[r] = 0;
+  if (S == 1) {
+    rc = launch_one(kp, st);
+  } else {
+    for (int r = 0; r < S; ++r) {
+      if (!m->aux_stream[r]) {
+        B200_CUDA(cudaStreamCreateWithFlags(&m->aux_stream[r], cudaStreamNonBlocking));
+        B200_CUDA(cudaEventCreateWithFlags(&m->aux_event[r], cudaEventDisableTiming));
+      }
+      const int64_t lo = t.tiles * r / S, hi = t.tiles * (r + 1) / S;
+      tc::KParams kq = kp;
+      kq.b_img = kp.b_img + (size_t)lo * tc::TILE * t.K;
+      kq.ntiles = (int)(hi - lo);
+      kq.cand_idx = kp.cand_idx + (size_t)r * L.list_elems;
+      kq.cand_cnt = kp.cand_cnt + (size_t)r * qpad;
+      kq.cand_tau = kp.cand_tau + (size_t)r * qpad;
+      L.off[r] = (int)(lo * tc::TILE);
+      B200_CUDA(cudaStreamWaitEvent(m->aux_stream[r], m->ev0, 0));  // the query images are ready
+      rc = launch_one(kq, m->aux_stream[r]);
+      if (rc) break;
+      B200_CUDA(cudaEventRecord(m->aux_event[r], m->aux_stream[r]));
+      B200_CUDA(cudaStreamWaitEvent(st, m->aux_event[r], 0));
+    }
+  }
   B200_TRY(rc);
   cudaEventRecord(m->ev1, st);
   m->st.last_cap = cfg.cap;
@@ -1090,10 +1150,11 @@ int knn_tc(b200_model* m, const double* z_dev, int64_t q, int k, int64_t self_of
   tc::rerank_kernel<CAPV><<<rb, 256, (size_t)8 * ((m->d + 1) & ~1) * 8, st>>>(m->x, m->n, m->d, z_dev, q, k, self_offset, kp.cand_idx, cfg.cap, \
                                               cand_cnt, cand_tau, meta, t.scale, t.cmax, t.perm.as<int32_t>(),                  \
                                               (m->tc_flags & 16384) ? nullptr : t.xs.as<double>(), idx_dev, d2_dev, \
-                                              fail_list, fail_cnt)
+                                              fail_list, fail_cnt, L)
   // the SS kernel's final trim leaves at most 32 candidates per query when keep <= 32
   const bool one_pass = !ts && cfg.keep <= 32 && !(m->tc_flags & (1024 | 2048));
-  if (cfg.cap == 32 || one_pass) RERANK(32);
+  if (S > 1) RERANK(128);  // pass r of the 128-slot instance takes list r
+  else if (cfg.cap == 32 || one_pass) RERANK(32);
   else if (cfg.cap <= 64) RERANK(64);
   else RERANK(128);
 #undef RERANK
