@@ -1171,7 +1171,7 @@ int knn_tc(b200_model* m, const double* z_dev, int64_t q, int k, int64_t self_of
   m->st.ms_prep += ms0;
   m->st.ms_stage1 += ms1;
   m->st.ms_rerank += ms2;
-  m->st.launches += 3;
+  m->st.launches += 3 + (S - 1);  // query image, S stage-1 launches, re-rank
   m->st.tc_queries += q;
   m->st.uncertified += h_fail;
   m->st.last_cap = cfg.cap;
