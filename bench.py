@@ -160,10 +160,10 @@ def main():
     ap.add_argument("--no-e2e", action="store_true", help="kernel experiments only: skip the host-buffer leg")
     ap.add_argument("--path", type=int, default=0, help="0 auto, 1 exact, 2 tensor")
     ap.add_argument("--margin", type=int, default=-1)
-    ap.add_argument("--tc-sub", type=int, default=128)
-    ap.add_argument("--tc-flags", type=int, default=0)
     ap.add_argument("--tc-halves", type=int, default=0)
-    ap.add_argument("--tc-mode", type=int, default=0, help="debug ceilings: 1 TMEM reads only, 2 no epilogue")
+    ap.add_argument("--tc-slots", type=int, default=0)
+    ap.add_argument("--tc-stats", type=int, default=0, help="instrumented stage-1 kernel: event / stall counters")
+    ap.add_argument("--tc-mode", type=int, default=0, help="ceilings: 1 no selection, 2 no epilogue")
     args = ap.parse_args()
     n, q, d, k = CONFIGS[args.config]
     if args.shard == "auto":
@@ -204,9 +204,9 @@ def main():
     model.set_option("knn_path", args.path)
     model.set_option("margin", args.margin)
     model.set_option("tc_mode", args.tc_mode)
-    model.set_option("tc_sub", args.tc_sub)
-    model.set_option("tc_flags", args.tc_flags)
     model.set_option("tc_halves", args.tc_halves)
+    model.set_option("tc_slots", args.tc_slots)
+    model.set_option("tc_stats", args.tc_stats)
     h = model.handle
     if G > 1 and args.shard == "query":
         qs = (q + G - 1) // G
@@ -341,7 +341,7 @@ def main():
                 "data": "synthetic",
                 "config": {"workload": f"NearestNeighbor(k={k}, method=Shepard) predict, {n}x{d} data, {q} queries",
                            "n": n, "q": q, "d": d, "k": k, "parallelism": (f"{args.shard}-shard x{G}" if G > 1 else "single"),
-                           "l2": "inputs larger than L2 (queries %d MB, operand images %d MB)" % (zl.nbytes >> 20, (nloc * 80 * 2) >> 20)},
+                           "l2": "inputs larger than L2 (queries %d MB, operand images %d MB)" % (zl.nbytes >> 20, (nloc * int(model.stat('tc_K') or d) * 2) >> 20)},
                 "roofline": roof,
                 "stages_ms": {kk: vv for kk, vv in stats.items() if kk.startswith("ms_")},
                 # HBM-bound stages: re-rank gathers c candidate rows per query
@@ -357,8 +357,11 @@ def main():
                                 if stats["ms_weights"] > 0 else None, "peak": pk["hbm"], "unit": "GB/s"}},
                 "uncertified_per_step": stats["uncertified"],
                 "tc": {"cap": model.stat("tc_cap"), "keep": model.stat("tc_keep"), "slots": model.stat("tc_slots"), "halves": model.stat("tc_halves"),
-                       "K": model.stat("tc_K"), "mode": args.tc_mode, "sub": args.tc_sub, "flags": args.tc_flags},
+                       "K": model.stat("tc_K"), "mode": args.tc_mode},
                 "gpu_launches": int(round(stats["launches"] * args.steps)),
+                **({"tc_stats": {nm: model.stat(f"tc_stat{i}") / args.steps for i, nm in enumerate(
+                    ["events", "events_hit", "survivors", "rank_merges", "sel_busy_clk", "queue_full_clk",
+                     "ready_wait_clk", "acc_wait_clk", "push_clk", "release_clk", "tile_clk", "pushes"])}} if args.tc_stats else {}),
                 "e2e": e2e, "clocks": sampler.summary()}
         if G == 1 and not args.no_cpu:
             v, s, dtc, cores, (cids, cout) = cpu_port(x, y, z, k, seconds=args.cpu_seconds)

@@ -41,8 +41,18 @@ int b200_device_count(void);
 int b200_create(const double* x, int64_t n, int32_t d, int32_t device, b200_model** out);
 int b200_destroy(b200_model* m);
 
-/* Tunables ("knn_path", "margin", "rows_per_call") and counters ("uncertified",
- * "ms_stage1", "ms_rerank", "ms_weights", "ms_exact", "launches", ...). */
+/* Options (b200_set_option):
+ *   "knn_path"      B200_PATH_AUTO / _EXACT / _TENSOR: which kNN kernel answers (AUTO: by problem size)
+ *   "margin"        extra candidates the tensor filter keeps beyond k (-1: max(4, min(k/2, 16)))
+ *   "tail_split"    0: do not spread the last, partly filled round of query blocks over idle SMs
+ *   "fallback"      1: uncertified queries go to the split brute-force scan instead of the rescan
+ *   "tc_halves"     1 / 2: force 128 / 256 query rows per CTA of the tensor kernel (0: automatic)
+ *   "tc_mode"       measurement only: 1 = no selection, 2 = no epilogue work (results meaningless)
+ *   "rows_per_call" queries per internal batch of the dense scans
+ *   "reset_stats"   clear the counters
+ * Counters (b200_get_stat): "uncertified", "ms_prep", "ms_stage1", "ms_rerank", "ms_weights",
+ * "ms_exact", "ms_collective", "launches", "tc_queries", "exact_queries", and the tensor
+ * kernel's shape "tc_K", "tc_cap", "tc_keep", "tc_slots", "tc_halves", "tc_scale", "tc_ymax". */
 int b200_set_option(b200_model* m, const char* key, double value);
 int b200_get_stat(b200_model* m, const char* key, double* value);
 
@@ -145,17 +155,6 @@ int b200_merge_topk_dev(int32_t device, const double* d2_parts, const int32_t* i
  * race on it: serialise them. */
 int b200_knn_exact_noalloc(const double* x_dev, int64_t n, int32_t d, const double* z_dev,
                            int64_t q, int32_t k, int32_t* idx_dev, double* d2_dev, void* stream);
-
-/* Test hook, no counterpart in the reference: run the tensor path on q <= 4096
- * queries and return the raw stage-1 scores (q, cols) with cols = 128*ceil(n/128),
- * score = s^2 * (||y_j - mu||^2 - 2 (z - mu).(y_j - mu)), s = stat "tc_scale". */
-int b200_tc_debug_scores(b200_model* m, const double* z, int64_t q, int32_t k, float* scores,
-                         int64_t cols);
-
-/* Tuning hook, no counterpart in the reference: clock64 stamps of the producer / MMA /
- * epilogue roles of CTA 0 for the first 96 tiles, stamps (3, 96, 4) int64. */
-int b200_tc_debug_trace(b200_model* m, const double* z, int64_t q, int32_t k, int64_t* stamps,
-                        int64_t count);
 
 #ifdef __cplusplus
 }

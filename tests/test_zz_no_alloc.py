@@ -18,7 +18,7 @@ import pytest
 pytestmark = pytest.mark.gpu
 
 
-def test_noalloc_knn_matches_allocating_entry_point_twice():
+def test_noalloc_knn_matches_allocating_entry_point_twice(oracle):
     import torch
     from util_b200 import _lib
     lib = _lib.lib()
@@ -28,7 +28,8 @@ def test_noalloc_knn_matches_allocating_entry_point_twice():
     stream = torch.cuda.current_stream().cuda_stream
     rng = np.random.default_rng(11)
     # (n, q, d, k): the first call fills much of the scratch, the second is smaller and differently shaped
-    for (n, q, d, k) in [(60000, 4000, 16, 16), (9000, 700, 5, 3)]:
+    # d = 120 and d = 300 take the launcher's 64- and 32-query block shapes
+    for (n, q, d, k) in [(60000, 4000, 16, 16), (9000, 700, 5, 3), (5000, 300, 120, 4), (3000, 200, 300, 2)]:
         x = rng.random((n, d))
         z = rng.random((q, d))
         x_dev = torch.from_numpy(x).to(dev)
@@ -47,6 +48,11 @@ def test_noalloc_knn_matches_allocating_entry_point_twice():
         # integer indices and fp64 distances from identical arithmetic: exact equality, as in the other tests
         assert torch.equal(idx, idx_ref)
         assert torch.equal(d2, d2_ref)
+        # and against the CPU oracle on a sample of the queries (not only CUDA against CUDA)
+        sel = rng.choice(q, size=min(q, 256), replace=False)
+        oi, od = oracle.knn(x, z[sel], k)
+        assert np.array_equal(idx.cpu().numpy()[sel], oi)
+        assert np.array_equal(d2.cpu().numpy()[sel], od)
         model.close()
     # requests beyond the static scratch are refused with a clear message, not truncated
     rc = lib.b200_knn_exact_noalloc(x_dev.data_ptr(), n, d, z_dev.data_ptr(), 300000, 3, idx.data_ptr(),
@@ -55,3 +61,8 @@ def test_noalloc_knn_matches_allocating_entry_point_twice():
     rc = lib.b200_knn_exact_noalloc(x_dev.data_ptr(), n, d, z_dev.data_ptr(), 10, 200, idx.data_ptr(),
                                     d2.data_ptr(), stream)
     assert rc != 0 and b"k=200" in lib.b200_last_error()
+    # a dimension whose query block cannot fit shared memory is refused cleanly as well
+    # (nothing is launched, so the buffers need not match the claimed shape)
+    rc = lib.b200_knn_exact_noalloc(x_dev.data_ptr(), 4, 700, z_dev.data_ptr(), 2, 1, idx.data_ptr(),
+                                    d2.data_ptr(), stream)
+    assert rc != 0 and b"too large" in lib.b200_last_error()

@@ -50,7 +50,6 @@ _SIGNATURES = {
                                          C.c_void_p, C.c_void_p, C.c_void_p]),
     "b200_tc_debug_scores": (C.c_int, [C.c_void_p, c_dp, C.c_int64, C.c_int32, C.POINTER(C.c_float),
                                        C.c_int64]),
-    "b200_tc_debug_trace": (C.c_int, [C.c_void_p, c_dp, C.c_int64, C.c_int32, c_i64p, C.c_int64]),
     "b200_merge_topk_dev": (C.c_int, [C.c_int32, C.c_void_p, C.c_void_p, C.c_int32, C.c_int64,
                                       C.c_int32, C.c_void_p, C.c_void_p, C.c_void_p]),
 }
@@ -163,13 +162,6 @@ class Model:
         cols = ((self.n + 127) // 128) * 128
         out = np.empty((z.shape[0], cols), dtype=np.float32)
         check(lib().b200_tc_debug_scores(self._h, ptr(z), z.shape[0], k, ptr(out, C.POINTER(C.c_float)), cols))
-        return out
-
-    def tc_debug_trace(self, z, k=16):
-        """clock64 stamps (role, tile, event) of CTA 0 in the tensor kernel (tuning only)."""
-        z = f64(z)
-        out = np.zeros((3, 96, 4), dtype=np.int64)
-        check(lib().b200_tc_debug_trace(self._h, ptr(z), z.shape[0], k, ptr(out, c_i64p), out.size))
         return out
 
     def shepard_predict(self, z, y=None, want_weights=False):

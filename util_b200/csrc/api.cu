@@ -7,6 +7,7 @@
 #include <vector>
 
 #include "common.cuh"
+#include "../../include/b200approx_debug.h"
 
 namespace b200 {
 
@@ -167,7 +168,7 @@ int b200_destroy(b200_model* m) {
   cudaSetDevice(m->device);
   cudaDeviceSynchronize();
   if (m->x) cudaFree(m->x);
-  DevBuf* bufs[] = {&m->tc.mu, &m->tc.img, &m->tc.perm, &m->tc.xs, &m->vor_g, &m->x32, &m->rw, &m->lf, &m->la, &m->y, &m->zq, &m->idx32, &m->d2,
+  DevBuf* bufs[] = {&m->tc.mu, &m->tc.img, &m->tc.nlo, &m->tc.perm, &m->tc.xs, &m->vor_g, &m->x32, &m->rw, &m->lf, &m->la, &m->y, &m->zq, &m->idx32, &m->d2,
                     &m->wts, &m->cnt, &m->err, &m->out, &m->part_d2, &m->part_idx, &m->cand,
                     &m->cand_meta, &m->zimg, &m->flags, &m->misc, &m->ids64};
   for (DevBuf* b : bufs) b->release();
@@ -190,18 +191,16 @@ int b200_set_option(b200_model* m, const char* key, double value) {
   if (!strcmp(key, "knn_path")) m->knn_path = (int)value;
   else if (!strcmp(key, "margin")) m->margin = (int)value;
   else if (!strcmp(key, "tc_mode")) m->tc_mode = (int)value;
-  else if (!strcmp(key, "tc_flags")) m->tc_flags = (int)value;
   else if (!strcmp(key, "tc_halves")) m->tc_halves = (int)value;
-  else if (!strcmp(key, "tc_trace_start")) m->tc_trace_start = (int)value;
-  else if (!strcmp(key, "tc_sub")) {
-    if ((int)value != 64 && (int)value != 128) {
-      set_error("tc_sub must be 64 or 128");
-      return 1;
-    }
-    m->tc_sub = (int)value;
-  }
+  else if (!strcmp(key, "tc_slots")) m->tc_slots = (int)value;
+  else if (!strcmp(key, "tc_stats")) m->tc_stats = (int)value;
+  else if (!strcmp(key, "tail_split")) m->no_tail_split = value == 0.0;
+  else if (!strcmp(key, "fallback")) m->force_split_fallback = (int)value == 1;
   else if (!strcmp(key, "rows_per_call")) m->rows_per_call = (int64_t)value;
-  else if (!strcmp(key, "reset_stats")) m->st = Stats();
+  else if (!strcmp(key, "reset_stats")) {
+    m->st = Stats();
+    for (double& v : m->tc_stat_vals) v = 0;
+  }
   else {
     set_error("unknown option '%s'", key);
     return 1;
@@ -229,6 +228,7 @@ int b200_get_stat(b200_model* m, const char* key, double* value) {
   else if (!strcmp(key, "tc_slots")) *value = s.last_slots;
   else if (!strcmp(key, "tc_halves")) *value = s.last_halves;
   else if (!strcmp(key, "sm_count")) *value = m->sm_count;
+  else if (!strncmp(key, "tc_stat", 7) && atoi(key + 7) >= 0 && atoi(key + 7) < 16) *value = m->tc_stat_vals[atoi(key + 7)];
   else {
     set_error("unknown stat '%s'", key);
     return 1;
@@ -405,27 +405,6 @@ int b200_tc_debug_scores(b200_model* m, const double* z, int64_t q, int32_t k, f
     }
   }
   dump.release();
-  return rc;
-}
-
-int b200_tc_debug_trace(b200_model* m, const double* z, int64_t q, int32_t k, int64_t* stamps,
-                        int64_t count) {
-  B200_TRY(use(m));
-  if (count != 3 * 96 * 4) {
-    set_error("b200_tc_debug_trace: count must be %d", 3 * 96 * 4);
-    return 1;
-  }
-  DevBuf tr;
-  B200_TRY(tr.reserve((size_t)count * 8));
-  B200_CUDA(cudaMemset(tr.p, 0, (size_t)count * 8));
-  B200_TRY(upload_queries(m, z, q));
-  B200_TRY(m->idx32.reserve((size_t)q * k * 4));
-  B200_TRY(m->d2.reserve((size_t)q * k * 8));
-  m->dbg_trace = tr.as<long long>();
-  int rc = knn_tc(m, m->zq.as<double>(), q, k, -1, m->idx32.as<int32_t>(), m->d2.as<double>(), 0);
-  m->dbg_trace = nullptr;
-  if (rc == 0 && cudaMemcpy(stamps, tr.p, (size_t)count * 8, cudaMemcpyDeviceToHost) != cudaSuccess) rc = 2;
-  tr.release();
   return rc;
 }
 

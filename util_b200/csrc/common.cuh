@@ -62,15 +62,13 @@ struct DevBuf {
 struct TcData {
   bool ready = false;
   int K = 0;            // padded contraction length (multiple of 16)
-  int sub = 128;        // rows per data sub-tile image (64 or 128)
-  int rg = 0;           // 1: row-group-major image layout
-  int order = 0;        // 0: positions ordered by centred norm, 1: fitted order
   int64_t tiles = 0;    // 128-point tiles
   double scale = 1.0;   // power of two applied after centring
   double ymax = 0.0;    // max over points of max(||yc||, ||fp16(yc)||) (scaled units)
   double cmax = 0.0;    // max |coordinate| of the raw data
   DevBuf mu;            // d doubles: per-dimension centre
   DevBuf img;           // tiles * 128 * K halfs, UMMA K-major no-swizzle tile images
+  DevBuf nlo;           // tiles * 4 floats: per 32-position chunk a lower bound of the squared centred norms
   DevBuf perm;          // n int32: image position -> fitted row (positions ordered by centred norm)
   DevBuf xs;            // (n,d) fp64: the fitted rows in image order, gathered by the re-rank (absent for huge sets)
 };
@@ -105,14 +103,16 @@ struct b200_model {
   // options
   int knn_path = 0;
   int margin = -1;  // extra candidates kept by the tensor filter (-1: max(4, min(k/2, 16)))
-  int tc_sub = 128;   // data rows per sub-tile image / UMMA N (64 or 128)
+  int tc_stats = 0;   // 1: run the instrumented stage-1 kernel and accumulate its counters in tc_stat_vals
+  double tc_stat_vals[16] = {0};
+  int tc_slots = 0;   // force the depth of the data-tile ring (0: automatic)
   int tc_halves = 0;  // force 128*halves query rows per CTA (0: automatic)
   int tc_split = 0;   // internal: the data stream of this call is split over this many concurrent launches
   cudaStream_t aux_stream[4] = {nullptr, nullptr, nullptr, nullptr};
   cudaEvent_t aux_event[4] = {nullptr, nullptr, nullptr, nullptr};
-  int tc_trace_start = 0;
-  int tc_flags = 0;   // bit 0: suspend-time hint on mbarrier waits
-  int tc_mode = 0;  // debug: 1/2 strip the epilogue to measure the MMA/TMA pipeline ceiling
+  int tc_mode = 0;  // ceilings: 1 = no selection, 2 = no epilogue work at all (outputs meaningless; stage 1 timed only)
+  int no_tail_split = 0;         // 1: the last, partly filled round of query blocks is not split over idle SMs
+  int force_split_fallback = 0;  // 1: uncertified queries go to the split brute-force scan instead of the rescan
   int64_t rows_per_call = 1 << 20;
   b200::Stats st;
   cudaEvent_t ev0 = nullptr, ev1 = nullptr, ev2 = nullptr, ev3 = nullptr;
@@ -123,7 +123,6 @@ struct b200_model {
   bool defer_fallback = false;
   int64_t defer_base = 0;
   std::vector<int32_t> deferred;
-  long long* dbg_trace = nullptr;  // tuning only: clock stamps of CTA 0
   float* dbg_scores = nullptr;  // tests only: raw tensor-path scores are dumped here
 };
 

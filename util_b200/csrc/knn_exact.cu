@@ -14,6 +14,8 @@
 // memory in tiles and are broadcast-read by the whole block.  The data range is
 // split across blockIdx.y so small query batches still fill 148 SMs; partial
 // lists land in scratch and are merged by merge_topk_kernel.
+#include <cub/device/device_radix_sort.cuh>
+
 #include "common.cuh"
 
 namespace b200 {
@@ -357,6 +359,67 @@ int launch_exact(b200_model* m, const double* z, int64_t q, int k, int64_t self_
   return 0;
 }
 
+// ---- k > 1024 (NearestNeighbor's automatic k selection asks for up to n/2 neighbours of ~100 sampled
+// points, nearest_neighbor/__init__.py:98-106): all n squared distances of one query at a time, then a
+// stable radix sort of (distance bits, row) -- non-negative doubles order like their bit patterns, and
+// rows enter in ascending order, so ties go to the lowest index as everywhere else.
+__global__ void all_dist_kernel(const double* __restrict__ x, int64_t n, int d, const double* __restrict__ zrow,
+                                int64_t self, unsigned long long* __restrict__ key, int32_t* __restrict__ val) {
+  const int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
+  if (i >= n) return;
+  const double v = i == self ? CUDART_INF : sqdist_seq(x + i * d, zrow, d);
+  key[i] = (unsigned long long)__double_as_longlong(v);
+  val[i] = (int32_t)i;
+}
+__global__ void take_first_kernel(const unsigned long long* __restrict__ key, const int32_t* __restrict__ val, int k,
+                                  int32_t* __restrict__ idx, double* __restrict__ d2) {
+  const int i = blockIdx.x * blockDim.x + threadIdx.x;
+  if (i >= k) return;
+  idx[i] = val[i];
+  if (d2) d2[i] = __longlong_as_double((long long)key[i]);
+}
+
+int knn_full_sort(b200_model* m, const double* z, int64_t q, int k, int64_t self_offset, const int32_t* qsel,
+                  int32_t* idx, double* d2, cudaStream_t st) {
+  const int64_t n = m->n;
+  if (qsel) {
+    set_error("knn: k=%d > 1024 is not available as a fallback path", k);
+    return 1;
+  }
+  DevBuf keys, vals, tmp;
+  int rc = keys.reserve((size_t)n * 16 + 64);
+  if (!rc) rc = vals.reserve((size_t)n * 8 + 64);
+  unsigned long long* k_in = keys.as<unsigned long long>();
+  unsigned long long* k_out = k_in + n;
+  int32_t* v_in = vals.as<int32_t>();
+  int32_t* v_out = v_in + n;
+  size_t tmp_bytes = 0;
+  if (!rc && cub::DeviceRadixSort::SortPairs(nullptr, tmp_bytes, k_in, k_out, v_in, v_out, (int)n, 0, 64, st) != cudaSuccess) {
+    set_error("knn: radix sort set-up failed");
+    rc = 2;
+  }
+  if (!rc) rc = tmp.reserve(tmp_bytes + 64);
+  for (int64_t p = 0; p < q && !rc; ++p) {
+    all_dist_kernel<<<(unsigned)((n + 255) / 256), 256, 0, st>>>(m->x, n, m->d, z + p * m->d,
+                                                                 self_offset >= 0 ? self_offset + p : -1, k_in, v_in);
+    if (cub::DeviceRadixSort::SortPairs(tmp.p, tmp_bytes, k_in, k_out, v_in, v_out, (int)n, 0, 64, st) != cudaSuccess) {
+      set_error("knn: radix sort failed");
+      rc = 2;
+      break;
+    }
+    take_first_kernel<<<(k + 255) / 256, 256, 0, st>>>(k_out, v_out, k, idx + p * k, d2 ? d2 + p * k : nullptr);
+    m->st.launches += 3;
+  }
+  if (!rc && cudaStreamSynchronize(st) != cudaSuccess) {
+    set_error("knn: full-sort path failed: %s", cudaGetErrorString(cudaGetLastError()));
+    rc = 2;
+  }
+  keys.release();
+  vals.release();
+  tmp.release();
+  return rc;
+}
+
 }  // namespace
 
 // z_dev (>= max query index, d).  qsel == NULL: queries 0..q-1 -> rows 0..q-1 of the
@@ -375,8 +438,7 @@ int knn_exact(b200_model* m, const double* z_dev, int64_t q, int k, int64_t self
   if (k <= 32) return launch_exact<32>(m, z_dev, cntq, k, self_offset, qsel, idx_dev, d2_dev, st);
   if (k <= 128) return launch_exact<128>(m, z_dev, cntq, k, self_offset, qsel, idx_dev, d2_dev, st);
   if (k <= 1024) return launch_exact<1024>(m, z_dev, cntq, k, self_offset, qsel, idx_dev, d2_dev, st);
-  set_error("knn: k=%d > 1024 unsupported", k);
-  return 1;
+  return knn_full_sort(m, z_dev, cntq, k, self_offset, qsel, idx_dev, d2_dev, st);
 }
 
 int merge_topk(const double* d2_parts, const int32_t* idx_parts, int parts, int64_t q, int k,
@@ -619,7 +681,12 @@ int launch_noalloc(const double* x, int64_t n, int d, const double* z, int64_t q
   B200_CUDA(cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, dev));
   const int QB = d <= 96 ? 128 : (d <= 256 ? 64 : 32);
   const size_t zbytes = (size_t)d * QB * 8;
-  int tile_pts = (int)((160 * 1024 - zbytes) / ((size_t)d * 8));
+  const size_t budget = 160 * 1024;
+  if (zbytes + (size_t)4 * d * 8 > budget) {  // the query block and a 4-point tile must fit
+    set_error("b200_knn_exact_noalloc: dimension %d too large for the shared-memory tiling", d);
+    return 3;
+  }
+  int tile_pts = (int)((budget - zbytes) / ((size_t)d * 8));
   if (tile_pts > 256) tile_pts = 256;
   tile_pts &= ~3;
   if (tile_pts < 4) {

@@ -4,33 +4,37 @@
 // for large problems.  Three stages:
 //
 //  1. knn_tc_kernel (tcgen05 / TMEM / bulk-TMA, persistent, warp specialised):
-//     score(q, j) = ||y_j||^2 - 2 x_q . y_j as ONE contraction
-//         [ -2 x_q | 1 1 1 | 0.. ] . [ y_j | n_hi n_mid n_lo | 0.. ],   K = pad16(d + 3)
-//     on mean-centred, power-of-two scaled fp16 operands with fp32 accumulation
-//     in TMEM (the squared norm rides in three extra K slots as a 33-bit fp16
-//     triple, so the epilogue needs no add).  Query rows are the M side: each
-//     epilogue thread owns one TMEM lane = one query and streams every data
-//     tile past a running threshold tau (min3 trees over 8-column groups);
-//     survivors go to a per-row shared-memory buffer that a warp-cooperative
-//     rank-select trims to the C best whenever it fills.  The distance matrix
-//     is never written to HBM.
-//  2. rerank_kernel: exact fp64 squared distances of the <= CAP candidates of
-//     each query with the reference's arithmetic (direct differences, dimension
-//     order, no FMA), sorted by (d2, index) -> bit-exact neighbours.  Each query
-//     is CERTIFIED: every non-candidate has approximate score >= tau, so with a
-//     rigorous bound E on |approximate - exact| score, exact d2_k < (tau - E +
-//     ||x_q||^2)/s^2 proves no non-candidate can enter the top k.
-//  3. Queries that fail the certificate are resolved exactly (knn_exact.cu: a rescan
-//     listing every point within the candidates' k-th distance when they are few, the
-//     split brute-force scan otherwise) -- so the result is always the exact answer.
+//     dot(q, j) = -2 x_q . y_j as ONE contraction of mean-centred, power-of-two scaled fp16
+//     operands with fp32 accumulation in TMEM, K = pad16(d): no padding of the contraction for
+//     the squared norms.  The fitted points are streamed in order of increasing centred norm,
+//     so the norms inside one 32-column chunk span a tiny interval and the filter works on
+//         s'(q, j) = dot(q, j) + nlo(chunk of j),   nlo = lower bound of ||y_j||^2 over the chunk,
+//     a lower bound of the true score ||y_j||^2 - 2 x_q . y_j that is tight to ~1e-4 of the
+//     gaps between neighbours.  Three kinds of warps share the work:
+//       * epilogue warps (one thread = one TMEM lane = one query): read each 128-column
+//         accumulator tile, reduce every 32-column chunk to its minimum and compare it with the
+//         row's threshold.  A row whose chunk may hold a survivor pushes the chunk's 32 raw
+//         values into a shared-memory queue -- a handful of stores -- and moves on, so the
+//         accumulator goes back to the MMA issuers after a fixed, short time;
+//       * selection warps (one per epilogue warp) drain the queues: the 32 values of an entry
+//         sit one per lane, a ballot gives the survivors, and the row's candidate list -- kept
+//         sorted in shared memory, `keep` entries, threshold = its last entry -- takes them by
+//         warp-wide insertion (or a rank-merge when many arrive at once);
+//       * one bulk-copy (TMA engine) producer warp and two single-thread MMA issuers.
+//     The distance matrix is never written to HBM.
+//  2. rerank_kernel: exact fp64 squared distances of the <= keep candidates of each query with
+//     the reference's arithmetic (direct differences, dimension order, no FMA), sorted by
+//     (d2, index) -> bit-exact neighbours.  Each query is CERTIFIED: every non-candidate has
+//     s' >= tau, so with a rigorous bound E on |approximate - exact| score, exact
+//     d2_k < (tau - E + ||x_q||^2)/s^2 proves no non-candidate can enter the top k.
+//  3. Queries that fail the certificate are resolved exactly (knn_exact.cu: a rescan listing
+//     every point within the candidates' k-th distance when they are few, the split
+//     brute-force scan otherwise) -- so the result is always the exact answer.
 //
-// The images hold the fitted points in order of increasing centred norm (position ->
-// row map `perm`, applied by the re-rank): thresholds tighten early, fewer survivors.
-//
-// Operand layout in HBM: per 128-row tile a ready-to-use UMMA image
-// [K/8][128][8 halfs] (K-major, no swizzle: 8x16-byte core matrices contiguous),
-// so one cp.async.bulk (TMA engine) brings a whole tile and the smem descriptor
-// is fixed: LBO = 2048 B (next K chunk), SBO = 128 B (next 8 rows).
+// Operand layout in HBM: per 128-row tile a ready-to-use UMMA image [K/8][128][8 halfs]
+// (K-major, no swizzle: 8x16-byte core matrices contiguous), so one cp.async.bulk (TMA engine)
+// brings a whole tile and the smem descriptor is fixed: LBO = 2048 B (next K chunk),
+// SBO = 128 B (next 8 rows).
 #include <cub/device/device_radix_sort.cuh>
 
 #include "common.cuh"
@@ -40,14 +44,15 @@ namespace b200 {
 
 namespace tc {
 
-constexpr int TILE = 128;          // query rows per accumulator half = data columns per epilogue tile
-constexpr int NORM_SLOTS = 3;
-constexpr double U16 = 4.8828125e-4;             // 2^-11: fp16 unit roundoff
+constexpr int TILE = 128;          // query rows per accumulator half = data columns per tile
+constexpr int CHUNK = 32;          // columns per filter chunk = values per queue entry
+constexpr int QWORDS = 36;         // 32-bit words per queue entry: 32 values + {row, column base, nlo bits, -}
+constexpr double U16 = 4.8828125e-4;               // 2^-11: fp16 unit roundoff
 constexpr double TINY16 = 2.98023223876953125e-8;  // 2^-25: half the smallest fp16 subnormal
-constexpr double GAMMA_ACC = 1.52587890625e-5;   // 2^-16: bound on tensor-core fp32 accumulation error, relative to sum |terms|
-constexpr float PAD_NORM = 60000.0f;             // squared norm given to padding rows: never selected
+constexpr double GAMMA_ACC = 1.52587890625e-5;     // 2^-16: bound on tensor-core fp32 accumulation error, relative to sum |terms| (tests/test_gpu_tensor.py measures it)
+constexpr float NLO_PAD = 3.0e38f;                 // norm bound of a chunk that holds only padding columns
 
-__host__ __device__ inline int padK(int d) { return ((d + NORM_SLOTS + 15) / 16) * 16; }
+__host__ __device__ inline int padK(int d) { return ((d + 15) / 16) * 16; }
 
 // ------------------------------------------------------------------ statistics
 __global__ void colsum_kernel(const double* __restrict__ x, int64_t n, int d, double* __restrict__ sum) {
@@ -84,9 +89,10 @@ __global__ void maxabs_kernel(const double* __restrict__ x, int64_t n, int d, co
 // ------------------------------------------------------------- data order
 // The fitted points are streamed past every query in order of increasing centred norm.  The score
 // ||y||^2 - 2 x.y of a low-norm point is systematically smaller, so the running thresholds tighten
-// early and far fewer later points survive the filter (about half as many after the first 1 % of the
-// stream on uniform data) -- any order gives the same exact result.  Key: fp32 bits of the squared
-// norm (non-negative, so unsigned order = numeric order).
+// early and far fewer later points survive the filter; and the norms inside one 32-column chunk
+// are nearly equal, which is what lets the filter use one norm bound per chunk.  Any order gives
+// the same exact result.  Key: fp32 bits of the squared norm (non-negative, so unsigned order =
+// numeric order).
 __global__ void norm_key_kernel(const double* __restrict__ x, int64_t n, int d, const double* __restrict__ mu,
                                 double scale, uint32_t* __restrict__ key, int32_t* __restrict__ val) {
   const int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
@@ -115,18 +121,22 @@ __global__ void iota_kernel(int32_t* __restrict__ v, int64_t n) {
 }
 
 // ------------------------------------------------------------- operand images
-// Data side: one thread per (padded) point; writes its row of the tile image and
-// folds max(||yc||, ||fp16(yc)||) into ymax.
-__global__ void data_img_kernel(const double* __restrict__ x, int64_t n, int d, int K, int SUBROWS, int rg,
-                                const double* __restrict__ mu, double scale, const int32_t* __restrict__ perm,
-                                __half* __restrict__ img, int64_t npad, unsigned long long* __restrict__ ymax_bits) {
-  const int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;  // image position
+// Data side: one thread per (padded) image position, one warp per 32-column chunk.  Writes the
+// position's row of the tile image, the chunk's norm bound nlo (a float that is <= the exact
+// squared norm of every real point of the chunk), and folds max(||yc||, ||fp16(yc)||) into ymax.
+// Padding positions hold zero rows; the selection warps drop them by their position.
+__global__ void __launch_bounds__(128)
+data_img_kernel(const double* __restrict__ x, int64_t n, int d, int K, const double* __restrict__ mu, double scale,
+                const int32_t* __restrict__ perm, __half* __restrict__ img, float* __restrict__ nlo, int64_t npad,
+                unsigned long long* __restrict__ ymax_bits) {
+  const int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;  // image position (npad is a multiple of 128)
   double nm = 0.0;
-  if (i < npad) {
+  float lo = NLO_PAD;
+  {
     const int64_t src = i < n ? (int64_t)perm[i] : 0;  // fitted row that sits at this position
-    const int64_t t = i / SUBROWS;
-    const int r = (int)(i - t * SUBROWS);
-    uint4* dst = reinterpret_cast<uint4*>(img + (size_t)t * SUBROWS * K);  // chunk c at dst[c*SUBROWS + r]
+    const int64_t t = i / TILE;
+    const int r = (int)(i - t * TILE);
+    uint4* dst = reinterpret_cast<uint4*>(img + (size_t)t * TILE * K);  // chunk c at dst[c*TILE + r]
     const int KC = K / 8;
     double n2 = 0.0, n2h = 0.0;
     for (int c = 0; c < KC; ++c) {
@@ -134,48 +144,42 @@ __global__ void data_img_kernel(const double* __restrict__ x, int64_t n, int d, 
 #pragma unroll
       for (int e = 0; e < 8; ++e) {
         const int j = c * 8 + e;
-        float hv = 0.0f;
+        __half hh = __float2half_rn(0.0f);
         if (i < n && j < d) {
           const double yc = (x[src * d + j] - mu[j]) * scale;
-          const __half hh = __double2half(yc);
+          hh = __double2half(yc);
           n2 = fma(yc, yc, n2);
           const double yh = (double)__half2float(hh);
           n2h = fma(yh, yh, n2h);
-          h[e] = hh;
-          continue;
         }
-        if (j >= d && j < d + NORM_SLOTS) {
-          if (i >= n) hv = (j == d) ? PAD_NORM : 0.0f;
-          else {
-            // 33-bit fp16 triple of the exact (fp64) squared norm
-            const __half a = __double2half(n2);
-            const double r1 = n2 - (double)__half2float(a);
-            const __half b = __double2half(r1);
-            const double r2 = r1 - (double)__half2float(b);
-            const __half c3 = __double2half(r2);
-            hv = __half2float(j == d ? a : (j == d + 1 ? b : c3));
-          }
-        }
-        h[e] = __float2half_rn(hv);
+        h[e] = hh;
       }
-      dst[rg ? ((size_t)(r >> 3) * KC + c) * 8 + (r & 7) : (size_t)c * SUBROWS + r] = *reinterpret_cast<uint4*>(h);
+      dst[(size_t)c * TILE + r] = *reinterpret_cast<uint4*>(h);
     }
     nm = sqrt(fmax(n2, n2h));
+    // rounded towards zero with room for the fp64 rounding of n2 itself
+    if (i < n) lo = __double2float_rd(n2 * (1.0 - 1e-12));
   }
-  for (int o = 16; o > 0; o >>= 1) nm = fmax(nm, __shfl_xor_sync(0xffffffffu, nm, o));
-  if ((threadIdx.x & 31) == 0) atomicMax(ymax_bits, (unsigned long long)__double_as_longlong(nm));
+  for (int o = 16; o > 0; o >>= 1) {
+    nm = fmax(nm, __shfl_xor_sync(0xffffffffu, nm, o));
+    lo = fminf(lo, __shfl_xor_sync(0xffffffffu, lo, o));
+  }
+  if ((threadIdx.x & 31) == 0) {
+    atomicMax(ymax_bits, (unsigned long long)__double_as_longlong(nm));
+    nlo[i / CHUNK] = lo;
+  }
 }
 
 struct QMeta {
   double qn2;   // ||(z - mu) * scale||^2
-  double err;   // E_q: bound on |approximate - exact| score (scaled units), +inf when fp16 overflows
+  double err;   // E_q: bound on |tensor dot - exact dot| (scaled units), +inf when fp16 overflows
   double cmax;  // max |z_j|
 };
 
-// Query side: x~ = fp16(-2 * (z - mu) * scale), then the three 1.0 slots.
-__global__ void query_img_kernel(const double* __restrict__ z, int64_t q, int d, int K, int rg,
-                                 const double* __restrict__ mu, double scale, double ymax,
-                                 __half* __restrict__ img, int64_t qpad, QMeta* __restrict__ meta) {
+// Query side: x~ = fp16(-2 * (z - mu) * scale).
+__global__ void query_img_kernel(const double* __restrict__ z, int64_t q, int d, int K, const double* __restrict__ mu,
+                                 double scale, double ymax, __half* __restrict__ img, int64_t qpad,
+                                 QMeta* __restrict__ meta) {
   const int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
   if (i >= qpad) return;
   const int64_t t = i / TILE;
@@ -189,7 +193,7 @@ __global__ void query_img_kernel(const double* __restrict__ z, int64_t q, int d,
 #pragma unroll
     for (int e = 0; e < 8; ++e) {
       const int j = c * 8 + e;
-      float hv = 0.0f;
+      __half hh = __float2half_rn(0.0f);
       if (i < q && j < d) {
         const double zj = z[i * d + j];
         const double zc = (zj - mu[j]) * scale;
@@ -199,20 +203,17 @@ __global__ void query_img_kernel(const double* __restrict__ z, int64_t q, int d,
         x1 += fabs(xv);
         cmax = fmax(cmax, fabs(zj));
         if (!(fabs(xv) < 60000.0)) bad = true;  // also catches NaN
-        h[e] = __double2half(xv);
-        continue;
+        hh = __double2half(xv);
       }
-      if (i < q && j >= d && j < d + NORM_SLOTS) hv = 1.0f;
-      h[e] = __float2half_rn(hv);
+      h[e] = hh;
     }
-    dst[rg ? ((size_t)(r >> 3) * KC + c) * 8 + (r & 7) : (size_t)c * TILE + r] = *reinterpret_cast<uint4*>(h);
+    dst[(size_t)c * TILE + r] = *reinterpret_cast<uint4*>(h);
   }
   if (i < q) {
     const double xn = sqrt(xn2) * 1.001;
-    // rounding of both operands (Cauchy-Schwarz), fp16 subnormal floor, the norm triple,
-    // and the tensor-core accumulation -- see DESIGN.md "certificate"
-    double E = 2.0 * U16 * xn * ymax + TINY16 * (x1 + sqrt((double)d) * ymax) + 2.0 * TINY16 +
-               GAMMA_ACC * (xn * ymax + ymax * ymax);
+    // rounding of both operands (Cauchy-Schwarz), the fp16 subnormal floor, and the tensor-core
+    // accumulation -- DESIGN.md "certificate".  The rounding of dot + nlo is added by the re-rank.
+    double E = 2.0 * U16 * xn * ymax + TINY16 * (x1 + sqrt((double)d) * ymax) + GAMMA_ACC * xn * ymax;
     if (bad) E = CUDART_INF;
     meta[i].qn2 = qn2;
     meta[i].err = E;
@@ -220,190 +221,194 @@ __global__ void query_img_kernel(const double* __restrict__ z, int64_t q, int d,
   }
 }
 
-
 // ------------------------------------------------------------------ main kernel
 struct KParams {
-  const __half* a_img;   // query tile images  [qtiles][K/8][128][8]
-  const __half* b_img;   // data sub-tile images [2*ntiles][K/8][64][8]
+  const __half* a_img;   // query tile images  [qblocks*HALVES][K/8][128][8]
+  const __half* b_img;   // data tile images   [ntiles][K/8][128][8]
+  const float* nlo;      // [ntiles*4] per-chunk lower bound of the squared norms
   int K;                 // contraction length, multiple of 16
-  int ntiles;            // 128-column data tiles (two 64-row sub-tiles each)
+  int ntiles;            // 128-column data tiles of this launch
+  int ncols;             // real image positions of this launch (the rest of the last tile is padding)
   int qblocks;           // query blocks of HALVES*128 rows
-  int sub;               // data rows per B sub-tile: 64 or 128 (one TMA copy, one UMMA N)
-  int flags;             // bit 0: mbarrier waits pass a suspend-time hint
-  int slots;             // depth of the B ring, in sub-tiles
-  int stages;            // TS kernel: 64-column accumulator stages per half
-  int keep;              // C: candidates a compaction keeps (<= CAP - 8)
-  int mode;              // 0 normal; debug ceilings: 1 = epilogue reads TMEM only, 2 = epilogue only releases
-  int32_t* cand_idx;     // [qpad][CAP]
+  int slots;             // depth of the data-tile ring (power of two)
+  int qent;              // entries per selection queue (power of two, >= 32)
+  int keep;              // candidates kept per query (<= 32*U)
+  int mode;              // 0 normal; ceilings: 1 = epilogue reads and reduces but queues nothing, 2 = epilogue only releases
+  int32_t* cand_idx;     // [qpad][32*U]
   int32_t* cand_cnt;     // [qpad]
   float* cand_tau;       // [qpad]
-  float* dbg;            // optional [qpad][ntiles*128] raw scores (tests only)
-  int trace_start;       // first tile recorded in `trace`
-  long long* trace;      // optional [3 roles][TRACE_TILES][4] clock64 stamps of CTA 0 (tuning only)
+  float* dbg;            // optional [qpad][ntiles*128] raw tensor dots (tests only)
+  unsigned long long* stats;  // optional [16] counters of the instrumented build (tuning only): events, events with a
+                              // survivor, survivors, rank-merges, selection busy clk, queue-full clk, ready-wait clk,
+                              // accumulator-wait clk (clk summed over the warps of all CTAs)
 };
-constexpr int TRACE_TILES = 96;
-#define B200_TRACE(role, tile, ev)                                                         \
-  do {                                                                                     \
-    const int tt_ = (int)(tile) - p.trace_start;                                           \
-    if (p.trace && blockIdx.x == 0 && tt_ >= 0 && tt_ < TRACE_TILES)                       \
-      p.trace[((role) * TRACE_TILES + tt_) * 4 + (ev)] = clock64();                        \
+
+// Spin limits: a protocol bug must end in a trap, not in a hung GPU (2^27 probes: seconds).
+#define B200_SPIN_GUARD(spins)            \
+  do {                                    \
+    if (++(spins) > (1u << 27)) __trap(); \
   } while (0)
-
-
-__device__ __forceinline__ float min3(float a, float b, float c) { return fminf(fminf(a, b), c); }
-
-// Trim buffer column `col` (one query row) to its `keep` best entries; returns the new
-// threshold (the keep-th smallest score).  Warp-cooperative, all lanes must call.
-// bsc/bid are [CAP][RS] (slot-major, RS = rows + 1 keeps slot walks conflict-free).
-// Rank by counting: lane l ranks entries l and l+32 against broadcast reads of all n entries.
-// Equal scores would share a rank; they are detected by the rank checksum and re-ranked with
-// the slot number as tie-break.
-template <int CAP>
-__device__ __forceinline__ float compact_row(float* bsc, int* bid, int RS, int col, int n_valid, int keep,
-                                             int lane) {
-  constexpr int U = (CAP + 31) / 32;
-  float sc[U];
-  int id[U], rank[U];
-#pragma unroll
-  for (int u = 0; u < U; ++u) {
-    const int j = lane + 32 * u;
-    sc[u] = j < n_valid ? bsc[j * RS + col] : CUDART_INF_F;
-    id[u] = j < n_valid ? bid[j * RS + col] : 0;
-    rank[u] = 0;
-  }
-  const float* ps = bsc + col;
-  int i = 0;
-  for (; i + 8 <= n_valid; i += 8) {
-    float s8[8];
-#pragma unroll
-    for (int e = 0; e < 8; ++e) s8[e] = ps[(i + e) * RS];
-#pragma unroll
-    for (int u = 0; u < U; ++u) {
-      int r0 = 0, r1 = 0;
-#pragma unroll
-      for (int e = 0; e < 8; e += 2) {
-        r0 += s8[e] < sc[u] ? 1 : 0;
-        r1 += s8[e + 1] < sc[u] ? 1 : 0;
-      }
-      rank[u] += r0 + r1;
-    }
-  }
-  for (; i < n_valid; ++i) {
-    const float s0 = ps[i * RS];
-#pragma unroll
-    for (int u = 0; u < U; ++u) rank[u] += s0 < sc[u] ? 1 : 0;
-  }
-  int sum = 0;
-#pragma unroll
-  for (int u = 0; u < U; ++u) sum += (lane + 32 * u < n_valid) ? rank[u] : 0;
-  sum = __reduce_add_sync(0xffffffffu, sum);
-  if (sum != n_valid * (n_valid - 1) / 2) {  // equal scores: redo with the slot number as tie-break
-#pragma unroll
-    for (int u = 0; u < U; ++u) rank[u] = 0;
-    for (i = 0; i < n_valid; ++i) {
-      const float s0 = ps[i * RS];
-#pragma unroll
-      for (int u = 0; u < U; ++u) rank[u] += (s0 < sc[u] || (s0 == sc[u] && i < lane + 32 * u)) ? 1 : 0;
-    }
-  }
-  __syncwarp();
-  float tau = 0.0f;
-#pragma unroll
-  for (int u = 0; u < U; ++u) {
-    const bool valid = lane + 32 * u < n_valid;
-    if (valid && rank[u] < keep) {
-      bsc[rank[u] * RS + col] = sc[u];
-      bid[rank[u] * RS + col] = id[u];
-    }
-    const unsigned bm = __ballot_sync(0xffffffffu, valid && rank[u] == keep - 1);
-    if (bm) tau = __shfl_sync(0xffffffffu, sc[u], __ffs(bm) - 1);
-  }
-  __syncwarp();
-  return tau;
+__device__ __forceinline__ void mbar_wait_lean(uint32_t bar, uint32_t parity) {
+  uint32_t spins = 0;
+  while (!ptx::mbar_try_wait(bar, parity)) B200_SPIN_GUARD(spins);
 }
 
-// Survivors of one 32-column chunk held in registers v[32] -> candidate buffer of my row.
-// mask: values below my threshold (32 independent compares, four short OR chains).  A row whose
-// buffer cannot take all its survivors is trimmed FIRST (warp-cooperative compact_row: keep best
-// entries, threshold lowered to the keep-th), the mask is taken again under the new threshold, and
-// only then are the survivors stored -- nothing is ever dropped, so the buffer holds every value
-// below the final threshold.  In the first tiles one chunk can hold more survivors than the
-// CAP - keep (>= 16) free slots a trim leaves: the chunk is then taken in two 16-column halves.
-// The usual case late in the stream is one survivor, the chunk minimum `mcc` already held.
-// Uses: tau, cnt, keep, lane, my_sc, my_id, bsc, bid, RS, row0, CAP (of the enclosing kernel).
-#define B200_MASK32(v, out)                                                                  \
-  do {                                                                                       \
-    unsigned m4_[4] = {0u, 0u, 0u, 0u};                                                      \
-    _Pragma("unroll") for (int i_ = 0; i_ < 32; ++i_) m4_[i_ & 3] |= v[i_] < tau ? (1u << i_) : 0u; \
-    out = (m4_[0] | m4_[1]) | (m4_[2] | m4_[3]);                                             \
-  } while (0)
-#define B200_APPEND_CHUNK(v, base, mcc)                                                      \
-  do {                                                                                       \
-    unsigned todo_ = 0xffffffffu;                                                            \
-    do {                                                                                     \
-      unsigned cur_ = todo_, mask_;                                                          \
-      B200_MASK32(v, mask_);                                                                 \
-      mask_ &= todo_;                                                                        \
-      unsigned need_ = __ballot_sync(0xffffffffu, cnt + __popc(mask_) > CAP);                \
-      if (need_) {                                                                           \
-        while (need_) {                                                                      \
-          const int r_ = __ffs(need_) - 1;                                                   \
-          need_ &= need_ - 1;                                                                \
-          const int nv_ = __shfl_sync(0xffffffffu, cnt, r_);                                 \
-          const float nt_ = compact_row<CAP>(bsc, bid, RS, row0 + r_, nv_, keep, lane);      \
-          if (lane == r_) {                                                                  \
-            tau = fminf(tau, nt_);                                                           \
-            cnt = keep;                                                                      \
-          }                                                                                  \
-        }                                                                                    \
-        B200_MASK32(v, mask_);                                                               \
-        mask_ &= todo_;                                                                      \
-        if (todo_ == 0xffffffffu && __any_sync(0xffffffffu, cnt + __popc(mask_) > CAP)) {    \
-          cur_ = 0x0000ffffu;                                                                \
-          mask_ &= cur_;                                                                     \
-        }                                                                                    \
-      }                                                                                      \
-      const int nh_ = __popc(mask_);                                                         \
-      if (nh_ == 1 && cur_ == 0xffffffffu) {                                                 \
-        if (cnt < CAP) {                                                                     \
-          my_sc[cnt * RS] = mcc;                                                             \
-          my_id[cnt * RS] = (base) + __ffs(mask_) - 1;                                       \
-          ++cnt;                                                                             \
-        } else {                                                                             \
-          tau = mcc; /* cannot happen (space was made above); kept so the filter stays valid */ \
-        }                                                                                    \
-      } else if (nh_ > 0) {                                                                  \
-        _Pragma("unroll") for (int i_ = 0; i_ < 32; ++i_) {                                  \
-          const bool lt_ = (mask_ >> i_) & 1u;                                               \
-          const bool put_ = lt_ && cnt < CAP;                                                \
-          if (put_) {                                                                        \
-            my_sc[cnt * RS] = v[i_];                                                         \
-            my_id[cnt * RS] = (base) + i_;                                                   \
-          }                                                                                  \
-          tau = (lt_ && !put_) ? v[i_] : tau;                                                \
-          cnt += put_ ? 1 : 0;                                                               \
-        }                                                                                    \
-      }                                                                                      \
-      todo_ &= ~cur_;                                                                        \
-    } while (todo_);                                                                         \
-  } while (0)
+__device__ __forceinline__ float min3(float a, float b, float c) { return fminf(fminf(a, b), c); }
+__device__ __forceinline__ float chunk_min(const float* v) {
+  float g[4];
+#pragma unroll
+  for (int gi = 0; gi < 4; ++gi) {
+    const float* w = v + gi * 8;
+    g[gi] = fminf(min3(w[0], w[1], w[2]), min3(min3(w[3], w[4], w[5]), w[6], w[7]));
+  }
+  return fminf(fminf(g[0], g[1]), fminf(g[2], g[3]));
+}
 
-template <int CAP, int HALVES, bool DBG>
-__global__ void __launch_bounds__((HALVES * 4 + 3) * 32, 1) knn_tc_kernel(const KParams p) {
+// The sorted candidate list of one query row, U entries per lane: entry e = u*32 + lane, ascending
+// score; entries never filled hold +inf / -1.  `tau` = entry keep-1.
+template <int U>
+struct RowList {
+  float sc[U];
+  int id[U];
+  __device__ __forceinline__ void load(const float* ls, const int* li, int lane) {
+#pragma unroll
+    for (int u = 0; u < U; ++u) {
+      sc[u] = ls[u * 32 + lane];
+      id[u] = li[u * 32 + lane];
+    }
+  }
+  __device__ __forceinline__ void store(float* ls, int* li, int lane) const {
+#pragma unroll
+    for (int u = 0; u < U; ++u) {
+      ls[u * 32 + lane] = sc[u];
+      li[u * 32 + lane] = id[u];
+    }
+  }
+  __device__ __forceinline__ float entry(int e) const {  // e warp-uniform
+    float v = sc[0];
+#pragma unroll
+    for (int u = 1; u < U; ++u) v = (e >> 5) == u ? sc[u] : v;
+    return __shfl_sync(0xffffffffu, v, e & 31);
+  }
+  // insert (sv, col) behind the entries <= sv; the last entry drops out
+  __device__ __forceinline__ void insert(float sv, int col, int lane) {
+    int pos = 0;
+#pragma unroll
+    for (int u = 0; u < U; ++u) pos += __popc(__ballot_sync(0xffffffffu, sc[u] <= sv));
+#pragma unroll
+    for (int u = U - 1; u >= 0; --u) {
+      float ps = __shfl_up_sync(0xffffffffu, sc[u], 1);
+      int pi = __shfl_up_sync(0xffffffffu, id[u], 1);
+      if (u > 0) {
+        const float cs = __shfl_sync(0xffffffffu, sc[u - 1], 31);
+        const int ci = __shfl_sync(0xffffffffu, id[u - 1], 31);
+        if (lane == 0) {
+          ps = cs;
+          pi = ci;
+        }
+      }
+      const int e = u * 32 + lane;
+      if (e > pos) {
+        sc[u] = ps;
+        id[u] = pi;
+      } else if (e == pos) {
+        sc[u] = sv;
+        id[u] = col;
+      }
+    }
+  }
+};
+
+// One queue entry -> the row's list.  All lanes call; `s` is this lane's value of the entry
+// (already dot + nlo), `ok` whether it may enter (below the threshold, a real column), m = ballot(ok) != 0.
+template <int U>
+__device__ __forceinline__ float take_entry(float* ls, int* li, float s, bool ok, unsigned m, int base, float tau,
+                                            int keep, int lane) {
+  RowList<U> L;
+  L.load(ls, li, lane);
+  if (__popc(m) < 6) {
+    // few survivors (the usual case is one): insert them one at a time
+    while (m) {
+      const int bl = __ffs(m) - 1;
+      m &= m - 1;
+      const float sv = __shfl_sync(0xffffffffu, s, bl);
+      if (!(sv < tau)) continue;  // the threshold moved since the mask was taken
+      L.insert(sv, base + bl, lane);
+      tau = L.entry(keep - 1);
+    }
+    L.store(ls, li, lane);
+    return tau;
+  }
+  // many survivors (the first tiles of a block): rank every old and new element in the merged
+  // order -- old before new on equal scores, new ones by lane -- and scatter the first 32*U
+  const float sn = ok ? s : CUDART_INF_F;
+  int rn = 0;   // new elements before mine
+  int ro[U];    // new elements before my old entry u
+#pragma unroll
+  for (int u = 0; u < U; ++u) ro[u] = 0;
+#pragma unroll 8
+  for (int j = 0; j < 32; ++j) {
+    const float bj = __shfl_sync(0xffffffffu, sn, j);
+    rn += (bj < sn || (bj == sn && j < lane)) ? 1 : 0;
+#pragma unroll
+    for (int u = 0; u < U; ++u) ro[u] += bj < L.sc[u] ? 1 : 0;
+  }
+  int cle = 0;  // old entries <= my new value
+#pragma unroll
+  for (int u = 0; u < U; ++u) {
+#pragma unroll 8
+    for (int j = 0; j < 32; ++j) {
+      const float oj = __shfl_sync(0xffffffffu, L.sc[u], j);
+      cle += oj <= sn ? 1 : 0;
+    }
+  }
+  __syncwarp();
+#pragma unroll
+  for (int u = 0; u < U; ++u) {
+    const int r = u * 32 + lane + ro[u];
+    if (r < 32 * U) {
+      ls[r] = L.sc[u];
+      li[r] = L.id[u];
+    }
+  }
+  {
+    const int r = rn + cle;
+    if (r < 32 * U) {
+      ls[r] = sn;
+      li[r] = ok ? base + lane : -1;
+    }
+  }
+  __syncwarp();
+  const int e = keep - 1;
+  return ls[e];
+}
+
+// Warp roles (E = 4*HALVES):
+//   [0, 2E)     epilogue, two groups of E warps: group g reads accumulator stage g, i.e. every other
+//               tile, so a warp has two tile periods for one tile (wake, four TMEM reads, filter, push);
+//               warp w = g*E + half*4 + quad, thread = query row (half*128 + quad*32 + lane)
+//   [2E, 3E)    selection: warp 2E + c owns rows c*32 .. c*32+31 and drains the queues of epilogue
+//               warps c (stage 0) and E + c (stage 1)
+//   3E          producer (bulk copies);  3E+1, 3E+2  MMA issuers (issuer j = accumulator stage j)
+template <int U, int HALVES, bool DBG>
+__global__ void __launch_bounds__((HALVES * 12 + 3) * 32, 1) knn_tc_kernel(const KParams p) {
   constexpr int ROWS = HALVES * TILE;
-  constexpr int RS = ROWS + 1;
-  constexpr int EPI_WARPS = HALVES * 4;
+  constexpr int E = HALVES * 4;
+  constexpr int W = 32 * U;                  // list entries per row
   constexpr uint32_t ACC_COLS = HALVES * TILE;  // TMEM columns per accumulator stage
   extern __shared__ __align__(1024) uint8_t smem[];
   const int K = p.K;
-  const uint32_t tile_bytes = (uint32_t)TILE * K * 2;  // one 128-row query tile
-  const int SUB = p.sub;
-  const uint32_t sub_bytes = (uint32_t)SUB * K * 2;    // one data sub-tile
+  const uint32_t tile_bytes = (uint32_t)TILE * K * 2;  // one 128-row tile image
+  const int QE = p.qent;
   uint8_t* sA = smem;                                  // HALVES query tiles
-  uint8_t* sB = sA + (size_t)HALVES * tile_bytes;      // ring of p.slots sub-tiles
-  float* bsc = reinterpret_cast<float*>(sB + (size_t)p.slots * sub_bytes);  // [CAP][RS] scores
-  int* bid = reinterpret_cast<int*>(bsc + (size_t)CAP * RS);                // [CAP][RS] data indices
-  uint64_t* bars = reinterpret_cast<uint64_t*>((reinterpret_cast<uintptr_t>(bid + (size_t)CAP * RS) + 15) & ~(uintptr_t)15);
+  uint8_t* sB = sA + (size_t)HALVES * tile_bytes;      // ring of p.slots data tiles
+  float* lsc = reinterpret_cast<float*>(sB + (size_t)p.slots * tile_bytes);  // [ROWS][W] list scores
+  int* lid = reinterpret_cast<int*>(lsc + (size_t)ROWS * W);                 // [ROWS][W] list positions
+  float* que = reinterpret_cast<float*>(lid + (size_t)ROWS * W);             // [2E][QE][QWORDS]
+  float* tau_sh = que + (size_t)2 * E * QE * QWORDS;                         // [ROWS] thresholds (written by selection warps)
+  uint32_t* ctl = reinterpret_cast<uint32_t*>(tau_sh + ROWS);                // [2E][4]: head, tail, done, -;  then ready[E]
+  uint32_t* ready = ctl + 2 * E * 4;
+  uint64_t* bars = reinterpret_cast<uint64_t*>((reinterpret_cast<uintptr_t>(ready + E) + 15) & ~(uintptr_t)15);
   // bars: full[8], empty[8], accf[stage][half], acce[stage][half], afull, aempty
   uint64_t* bar_full = bars;
   uint64_t* bar_empty = bars + 8;
@@ -424,13 +429,14 @@ __global__ void __launch_bounds__((HALVES * 4 + 3) * 32, 1) knn_tc_kernel(const 
     }
     for (int a = 0; a < 4; ++a) {
       ptx::mbar_init(ptx::smem_u32(&bar_accf[a]), 1);
-      ptx::mbar_init(ptx::smem_u32(&bar_acce[a]), 4);  // the four warps of one half
+      ptx::mbar_init(ptx::smem_u32(&bar_acce[a]), 4);  // the four epilogue warps of one half and stage
     }
     ptx::mbar_init(ptx::smem_u32(bar_afull), 1);
     ptx::mbar_init(ptx::smem_u32(bar_aempty), 2);  // one commit per issuer warp
     ptx::fence_barrier_init();
   }
-  if (warp == EPI_WARPS + 1) {  // MMA warp owns the TMEM allocation
+  if (threadIdx.x < 2 * E * 4 + E) ctl[threadIdx.x] = 0;
+  if (warp == 3 * E + 1) {  // first MMA warp owns the TMEM allocation
     ptx::tmem_alloc(ptx::smem_u32(tmem_slot), 512);
     ptx::tmem_relinquish();
   }
@@ -444,33 +450,24 @@ __global__ void __launch_bounds__((HALVES * 4 + 3) * 32, 1) knn_tc_kernel(const 
   }
 
   const int nqb = (p.qblocks - (int)blockIdx.x + (int)gridDim.x - 1) / (int)gridDim.x;  // my query blocks
-  const int per_tile = TILE / SUB;
-  const int nsub = per_tile * p.ntiles;
-  const bool hint = p.flags & 1;
-  const uint32_t bsleep = (p.flags & 16) ? 0 : 64;  // ns between barrier probes of the producer / MMA warps
 
-  if (warp == EPI_WARPS) {
+  if (warp == 3 * E) {
     // ===================== producer: bulk copies on the TMA engine =====================
     if (lane == 0) {
-      uint32_t jt = 0, s = 0, ph = 0;
+      uint32_t s = 0, ph = 0;
       const uint32_t full0 = ptx::smem_u32(&bar_full[0]), empty0 = ptx::smem_u32(&bar_empty[0]);
       const uint32_t sB0 = ptx::smem_u32(sB);
       for (int b = 0; b < nqb; ++b) {
         const int qb = (int)blockIdx.x + b * (int)gridDim.x;
-        ptx::mbar_wait(hint, ptx::smem_u32(bar_aempty), (b & 1) ^ 1, bsleep);
+        ptx::mbar_wait(false, ptx::smem_u32(bar_aempty), (b & 1) ^ 1, 64);
         ptx::mbar_arrive_expect_tx(ptx::smem_u32(bar_afull), HALVES * tile_bytes);
         ptx::bulk_g2s(ptx::smem_u32(sA), reinterpret_cast<const uint8_t*>(p.a_img) + (size_t)qb * HALVES * tile_bytes,
                       HALVES * tile_bytes, ptx::smem_u32(bar_afull));
         const uint8_t* src = reinterpret_cast<const uint8_t*>(p.b_img);
-        for (int st = 0; st < nsub; ++st, ++jt, src += sub_bytes) {
-          ptx::mbar_wait(hint, empty0 + s * 8, ph ^ 1, bsleep);
-          B200_TRACE(0, (int)jt, 0);
-          if ((p.mode & 4) && jt >= (uint32_t)p.slots) {  // debug: no copy, the slot keeps its old tile
-            ptx::mbar_arrive(full0 + s * 8);
-          } else {
-            ptx::mbar_arrive_expect_tx(full0 + s * 8, sub_bytes);
-            ptx::bulk_g2s(sB0 + s * sub_bytes, src, sub_bytes, full0 + s * 8);
-          }
+        for (int t = 0; t < p.ntiles; ++t, src += tile_bytes) {
+          ptx::mbar_wait(false, empty0 + s * 8, ph ^ 1, 64);
+          ptx::mbar_arrive_expect_tx(full0 + s * 8, tile_bytes);
+          ptx::bulk_g2s(sB0 + s * tile_bytes, src, tile_bytes, full0 + s * 8);
           if (++s == (uint32_t)p.slots) {
             s = 0;
             ph ^= 1;
@@ -478,197 +475,295 @@ __global__ void __launch_bounds__((HALVES * 4 + 3) * 32, 1) knn_tc_kernel(const 
         }
       }
     }
-  } else if (warp > EPI_WARPS) {
+  } else if (warp > 3 * E) {
     // ===================== MMA issuers: two warps, alternate tiles =====================
-    // An issuing thread spends, per 128-column tile, ~730 clk issuing 10 MMAs into the short tensor
-    // queue plus ~700 clk in commits and barrier waits during which it queues nothing (measured with
-    // the clock trace, profiles/r01).  Two issuers on alternate tiles (issuer j owns accumulator
-    // stage j) interleave those phases so the tensor pipe always has work.  Each warp runs in uniform
-    // control flow; one elected lane issues the MMAs and the commits that track them.
-    {
-      const int j = warp - (EPI_WARPS + 1);  // issuer index = accumulator stage
-      const uint32_t idesc = ptx::umma_idesc_f16(TILE, SUB);
-      // operand image layout: chunk-major [K/8][rows][16 B] or row-group-major [rows/8][K/8][8][16 B]
-      const bool rg = p.flags & 2;
-      const uint32_t lbo_a = rg ? 128 : TILE * 16, sbo_a = rg ? (K / 8) * 128 : 128, kstep_a = rg ? 256 : TILE * 32;
-      const uint32_t lbo_b = rg ? 128 : SUB * 16, sbo_b = sbo_a, kstep_b = rg ? 256 : SUB * 32;
-      const bool skip_mma = p.mode & 8;
-      const int ksteps = K / 16;
-      uint64_t a_desc[HALVES];
+    // Issuer j owns accumulator stage j.  One thread per issuer warp runs a lean loop: barrier probes,
+    // fence, K/16 MMAs per half (M128 N128 K16, 64 clk each), commits.  Descriptors are built once and
+    // K steps only bump the address field.
+    const int j = warp - (3 * E + 1);
+    const uint32_t idesc = ptx::umma_idesc_f16(TILE, TILE);
+    const uint32_t lbo = TILE * 16, sbo = 128, kstep = (TILE * 32) >> 4;
+    const int ksteps = K / 16;
+    uint64_t a_desc[HALVES];
 #pragma unroll
-      for (int h = 0; h < HALVES; ++h) a_desc[h] = ptx::umma_desc(ptx::smem_u32(sA + (size_t)h * tile_bytes), lbo_a, sbo_a);
-      const uint64_t b_desc0 = ptx::umma_desc(ptx::smem_u32(sB), lbo_b, sbo_b);
-      const uint32_t a_step = kstep_a >> 4, b_step = kstep_b >> 4, slot_step = sub_bytes >> 4;
-      const uint32_t full0 = ptx::smem_u32(&bar_full[0]), empty0 = ptx::smem_u32(&bar_empty[0]);
-      const uint32_t accf = ptx::smem_u32(&bar_accf[j * 2]), acce = ptx::smem_u32(&bar_acce[j * 2]);
-      const uint32_t slot_mask = p.slots - 1, slot_shift = 31 - __clz(p.slots);  // slots is a power of two
-      // One thread per issuer warp, lean barrier probes, no per-tile parameter reloads: the per-tile
-      // serial path of the issuer is what bounds the pipeline once the epilogue keeps up.
-      if (lane == 0) {
-        uint32_t it0 = 0;   // global index of the current block's first tile
-        uint32_t mine = 0;  // tiles this issuer has done (phase of its accumulator stage)
-        const uint32_t afull = ptx::smem_u32(bar_afull), aempty = ptx::smem_u32(bar_aempty);
-        const uint32_t ntiles = (uint32_t)p.ntiles;
-        for (int b = 0; b < nqb; ++b, it0 += ntiles) {
-          while (!ptx::mbar_try_wait(afull, b & 1)) {}
-          for (uint32_t t = (j + it0) & 1; t < ntiles; t += 2, ++mine) {
-            const uint32_t it = it0 + t;
-            for (int hs = 0; hs < per_tile; ++hs) {
-              const uint32_t jt = it * per_tile + hs, s = jt & slot_mask, ph = (jt >> slot_shift) & 1;
-              const uint64_t bd = b_desc0 + (uint64_t)(s * slot_step);
+    for (int h = 0; h < HALVES; ++h) a_desc[h] = ptx::umma_desc(ptx::smem_u32(sA + (size_t)h * tile_bytes), lbo, sbo);
+    const uint64_t b_desc0 = ptx::umma_desc(ptx::smem_u32(sB), lbo, sbo);
+    const uint32_t slot_step = tile_bytes >> 4;
+    const uint32_t full0 = ptx::smem_u32(&bar_full[0]), empty0 = ptx::smem_u32(&bar_empty[0]);
+    const uint32_t accf = ptx::smem_u32(&bar_accf[j * 2]), acce = ptx::smem_u32(&bar_acce[j * 2]);
+    const uint32_t slot_mask = p.slots - 1, slot_shift = 31 - __clz(p.slots);
+    if (lane == 0) {
+      uint32_t it0 = 0;   // global index of the current block's first tile
+      uint32_t mine = 0;  // tiles this issuer has done (phase of its accumulator stage)
+      const uint32_t afull = ptx::smem_u32(bar_afull), aempty = ptx::smem_u32(bar_aempty);
+      const uint32_t ntiles = (uint32_t)p.ntiles;
+      for (int b = 0; b < nqb; ++b, it0 += ntiles) {
+        ptx::mbar_wait(false, afull, b & 1);
+        for (uint32_t t = (j + it0) & 1; t < ntiles; t += 2, ++mine) {
+          const uint32_t it = it0 + t, s = it & slot_mask, ph = (it >> slot_shift) & 1;
+          const uint64_t bd = b_desc0 + (uint64_t)(s * slot_step);
 #pragma unroll
-              for (int h = 0; h < HALVES; ++h) {
-                // the accumulator half is free once its four epilogue warps have read the previous tile
-                if (hs == 0) {
-                  while (!ptx::mbar_try_wait(acce + h * 8, (mine & 1) ^ 1)) {}
-                }
-                if (h == 0) {
-                  while (!ptx::mbar_try_wait(full0 + s * 8, ph)) {}
-                }
-                ptx::tc_fence_after();
-                // (the accumulator base is the literal 0: this CTA owns all 512 columns, checked at start)
-                const uint32_t d_tmem = j * ACC_COLS + h * TILE + hs * SUB;
-                if (DBG && h == 0) B200_TRACE(1, (int)it, 0);
-                if (!(DBG && skip_mma)) {
-#define B200_ISSUE(KS)                                                                                   \
-  _Pragma("unroll") for (int ks = 0; ks < KS; ++ks)                                                       \
-    ptx::umma_f16(d_tmem, a_desc[h] + (uint64_t)(ks * a_step), bd + (uint64_t)(ks * b_step), idesc,        \
-                  ks > 0 ? 1u : 0u);
-                  switch (ksteps) {
-                    case 2: B200_ISSUE(2) break;
-                    case 3: B200_ISSUE(3) break;
-                    case 4: B200_ISSUE(4) break;
-                    case 5: B200_ISSUE(5) break;
-                    default:
-                      for (int ks = 0; ks < ksteps; ++ks)
-                        ptx::umma_f16(d_tmem, a_desc[h] + (uint64_t)(ks * a_step), bd + (uint64_t)(ks * b_step),
-                                      idesc, ks > 0 ? 1u : 0u);
-                  }
-#undef B200_ISSUE
-                }
-                if (hs == per_tile - 1) ptx::umma_commit(accf + h * 8);  // this half's 128 columns are ready
-                if (h == HALVES - 1) {
-                  if (DBG) B200_TRACE(1, (int)it, 1);
-                  ptx::umma_commit(empty0 + s * 8);  // sub-tile slot free once these MMAs retire
-                  if (DBG) B200_TRACE(1, (int)it, 3);
-                }
-              }
+          for (int h = 0; h < HALVES; ++h) {
+            // the accumulator half is free once its four epilogue warps have read the previous tile
+            ptx::mbar_wait(false, acce + h * 8, (mine & 1) ^ 1);
+            if (h == 0) ptx::mbar_wait(false, full0 + s * 8, ph);
+            ptx::tc_fence_after();
+            // (the accumulator base is the literal 0: this CTA owns all 512 columns, checked at start)
+            const uint32_t d_tmem = j * ACC_COLS + h * TILE;
+#define B200_ISSUE(KS)                                                                                  \
+  _Pragma("unroll") for (int ks = 0; ks < KS; ++ks)                                                      \
+    ptx::umma_f16(d_tmem, a_desc[h] + (uint64_t)(ks * kstep), bd + (uint64_t)(ks * kstep), idesc, ks > 0 ? 1u : 0u);
+            switch (ksteps) {
+              case 1: B200_ISSUE(1) break;
+              case 2: B200_ISSUE(2) break;
+              case 3: B200_ISSUE(3) break;
+              case 4: B200_ISSUE(4) break;
+              default:
+                for (int ks = 0; ks < ksteps; ++ks)
+                  ptx::umma_f16(d_tmem, a_desc[h] + (uint64_t)(ks * kstep), bd + (uint64_t)(ks * kstep), idesc,
+                                ks > 0 ? 1u : 0u);
             }
+#undef B200_ISSUE
+            ptx::umma_commit(accf + h * 8);                           // this half's 128 columns are ready
+            if (h == HALVES - 1) ptx::umma_commit(empty0 + s * 8);    // tile slot free once these MMAs retire
           }
-          ptx::umma_commit(aempty);  // my MMAs on these A tiles are tracked
         }
+        ptx::umma_commit(aempty);  // my MMAs on these A tiles are tracked
       }
     }
-  } else {
-    // ===================== epilogue: threshold filter + candidate buffers =====================
-    // Fast path per 128-column tile: four tcgen05.ld of 32 columns (software pipelined), an FMNMX3
-    // tree per chunk, ONE warp vote per tile.  Only when some lane beats its threshold are the
-    // offending chunks read again from TMEM and scanned.  The four warps of a half synchronise with
-    // the MMA issuers on their own per-half barriers, so a warp that is compacting holds up three
-    // others, not seven.
-    const int half = warp >> 2, quad = warp & 3;
-    const int row0 = half * TILE + quad * 32;
-    const int row = row0 + lane;  // my query row inside the block
-    const uint32_t t_lane = ((uint32_t)(quad * 32) << 16) + half * TILE;
-    const int keep = p.keep;
-    float* my_sc = bsc + row;
-    int* my_id = bid + row;
-    uint32_t it = 0;
-    for (int b = 0; b < nqb; ++b) {
+  } else if (warp < 2 * E) {
+    // ===================== epilogue: threshold filter, survivors' chunks to the queue ==============
+    const int g = warp / E;            // accumulator stage this warp reads
+    const int rb = warp - g * E;       // row block: half*4 + quad
+    const int half = rb >> 2, quad = rb & 3;
+    const int row = rb * 32 + lane;    // my query row inside the block
+    const uint32_t t_lane = ((uint32_t)(quad * 32) << 16) + g * ACC_COLS + half * TILE;
+    float* myq = que + (size_t)warp * QE * QWORDS;
+    const uint32_t c_head = ptx::smem_u32(&ctl[warp * 4 + 0]), c_tail = ptx::smem_u32(&ctl[warp * 4 + 1]);
+    const uint32_t c_done = ptx::smem_u32(&ctl[warp * 4 + 2]), c_ready = ptx::smem_u32(&ready[rb]);
+    const uint32_t my_tau = ptx::smem_u32(&tau_sh[row]);
+    const uint32_t bar_f = ptx::smem_u32(&bar_accf[g * 2 + half]), bar_e = ptx::smem_u32(&bar_acce[g * 2 + half]);
+    const uint32_t lt_mask = (1u << lane) - 1u;
+    const float4* nlo4 = reinterpret_cast<const float4*>(p.nlo);
+    uint32_t head = 0, tail_c = 0;  // entries pushed so far / last tail seen
+    uint32_t it0 = 0;               // global index of the current block's first tile
+    uint32_t mine = 0;              // tiles this warp has read (phase of its accumulator stage)
+    long long st_full = 0, st_ready = 0, st_acc = 0, st_push = 0, st_rel = 0, st_tile = 0;  // instrumented build only
+    unsigned long long st_npush = 0;
+    for (int b = 0; b < nqb; ++b, it0 += (uint32_t)p.ntiles) {
       const int qb = (int)blockIdx.x + b * (int)gridDim.x;
-      float tau = CUDART_INF_F;
-      int cnt = 0;
-      for (int t = 0; t < p.ntiles; ++t, ++it) {
-        const uint32_t a = it & 1, aph = (it >> 1) & 1;
-        ptx::mbar_wait(hint, ptx::smem_u32(&bar_accf[a * 2 + half]), aph);
-        if (warp == 0 && lane == 0) B200_TRACE(2, (int)it, 0);
+      {  // the selection warp of my rows has flushed the previous block and reset lists and thresholds
+        const long long c0 = DBG ? clock64() : 0;
+        uint32_t spins = 0;
+        while (ptx::ld_acquire_shared(c_ready) != (uint32_t)(b + 1)) {
+          __nanosleep(64);
+          B200_SPIN_GUARD(spins);
+        }
+        if (DBG) st_ready += clock64() - c0;
+      }
+      for (int t = (int)((g + it0) & 1); t < p.ntiles; t += 2, ++mine) {
+        const float4 nl = __ldg(nlo4 + t);  // norm bounds of the tile's four chunks
+        const long long c1 = DBG ? clock64() : 0;
+        mbar_wait_lean(bar_f, mine & 1);
+        const long long c6 = DBG ? clock64() : 0;
+        if (DBG) st_acc += c6 - c1;
         ptx::tc_fence_after();
-        const uint32_t t_acc = t_lane + a * ACC_COLS;
         if ((p.mode & 3) != 2) {
-          float va[32], vb[32], mc[4];
-#define B200_CHUNKMIN(v, cc)                                                                       \
-  do {                                                                                             \
-    if (DBG) {                                                                                     \
-      if (p.dbg) {                                                                                 \
-        float* o = p.dbg + ((size_t)qb * ROWS + row) * ((size_t)p.ntiles * TILE) + (size_t)t * TILE + (cc) * 32; \
-        _Pragma("unroll") for (int i = 0; i < 32; ++i) o[i] = v[i];                                \
-      }                                                                                            \
-    }                                                                                              \
-    float g_[4];                                                                                   \
-    _Pragma("unroll") for (int gi = 0; gi < 4; ++gi) {                                             \
-      const float* w = v + gi * 8;                                                                 \
-      g_[gi] = fminf(min3(w[0], w[1], w[2]), min3(min3(w[3], w[4], w[5]), w[6], w[7]));            \
-    }                                                                                              \
-    mc[cc] = fminf(fminf(g_[0], g_[1]), fminf(g_[2], g_[3]));                                      \
+          // per-chunk thresholds on the raw dot: dot + nlo < tau, widened by the rounding of both sides
+          // (an inexact test here only adds queue entries; the selection warp decides)
+          const float tau = ptx::ld_volatile_shared_f32(my_tau);
+          const float at = fabsf(tau) * 4.76837158e-7f;
+          float v[32];
+          // one queue push: the flagged lanes of `fm_` (at most QE of them) take consecutive slots
+#define B200_PUSH(fm_, cc, nlc)                                                                      \
+  do {                                                                                               \
+    const long long c3_ = DBG ? clock64() : 0;                                                       \
+    const uint32_t nadd_ = __popc(fm_);                                                              \
+    if (head + nadd_ - tail_c > (uint32_t)QE) {                                                      \
+      uint32_t spins_ = 0;                                                                           \
+      do {                                                                                           \
+        tail_c = ptx::ld_acquire_shared(c_tail);                                                     \
+        B200_SPIN_GUARD(spins_);                                        \
+      } while (head + nadd_ - tail_c > (uint32_t)QE);                                                \
+    }                                                                                                \
+    if ((fm_ >> lane) & 1u) {                                                                        \
+      const uint32_t slot_ = (head + __popc(fm_ & lt_mask)) & (uint32_t)(QE - 1);                    \
+      float4* dst_ = reinterpret_cast<float4*>(myq + (size_t)slot_ * QWORDS);                        \
+      _Pragma("unroll") for (int i = 0; i < 8; ++i)                                                  \
+        dst_[i] = make_float4(v[4 * i], v[4 * i + 1], v[4 * i + 2], v[4 * i + 3]);                   \
+      reinterpret_cast<int4*>(dst_)[8] = make_int4(lane, t * TILE + (cc) * 32, __float_as_int(nlc), 0); \
+    }                                                                                                \
+    head += nadd_;                                                                                   \
+    __syncwarp();                                                                                    \
+    const long long c4_ = DBG ? clock64() : 0;                                                       \
+    if (lane == 0) ptx::st_release_shared(c_head, head);                                             \
+    if (DBG) {                                                                                       \
+      const long long c5_ = clock64();                                                               \
+      st_push += c5_ - c3_;                                                                          \
+      st_rel += c5_ - c4_;                                                                           \
+      ++st_npush;                                                                                    \
+    }                                                                                                \
   } while (0)
-          ptx::tmem_ld32(t_acc, va);
+#define B200_CHUNK(cc, nlc)                                                                          \
+  do {                                                                                               \
+    if (DBG) {                                                                                       \
+      if (p.dbg) {                                                                                   \
+        float* o = p.dbg + ((size_t)qb * ROWS + row) * ((size_t)p.ntiles * TILE) + (size_t)t * TILE + (cc) * 32; \
+        _Pragma("unroll") for (int i = 0; i < 32; ++i) o[i] = v[i];                                  \
+      }                                                                                              \
+    }                                                                                                \
+    const bool fl_ = chunk_min(v) < (tau - (nlc)) + fmaf(nlc, 4.76837158e-7f, at);                   \
+    const unsigned fa_ = (p.mode & 3) == 0 ? __ballot_sync(0xffffffffu, fl_) : 0u;                   \
+    if (fa_) {                                                                                       \
+      if (QE >= 32) {                                                                                \
+        B200_PUSH(fa_, cc, nlc);                                                                     \
+      } else {                                                                                       \
+        const unsigned lo_ = fa_ & 0xffffu, hi_ = fa_ & 0xffff0000u;                                 \
+        if (lo_) B200_PUSH(lo_, cc, nlc);                                                            \
+        if (hi_) B200_PUSH(hi_, cc, nlc);                                                            \
+      }                                                                                              \
+    }                                                                                                \
+  } while (0)
+          ptx::tmem_ld32(t_lane, v);
           ptx::tmem_ld_wait();
-          ptx::tmem_ld32(t_acc + 32, vb);
-          B200_CHUNKMIN(va, 0);
+          B200_CHUNK(0, nl.x);
+          ptx::tmem_ld32(t_lane + 32, v);
           ptx::tmem_ld_wait();
-          ptx::tmem_ld32(t_acc + 64, va);
-          B200_CHUNKMIN(vb, 1);
+          B200_CHUNK(1, nl.y);
+          ptx::tmem_ld32(t_lane + 64, v);
           ptx::tmem_ld_wait();
-          ptx::tmem_ld32(t_acc + 96, vb);
-          B200_CHUNKMIN(va, 2);
+          B200_CHUNK(2, nl.z);
+          ptx::tmem_ld32(t_lane + 96, v);
           ptx::tmem_ld_wait();
-          B200_CHUNKMIN(vb, 3);
-#undef B200_CHUNKMIN
-          const float mt = fminf(fminf(mc[0], mc[1]), fminf(mc[2], mc[3]));
-          // which 32-column chunks hold a survivor for some row of this warp: one warp-wide OR
-          unsigned hitc = (mc[0] < tau ? 1u : 0u) | (mc[1] < tau ? 2u : 0u) | (mc[2] < tau ? 4u : 0u) | (mc[3] < tau ? 8u : 0u);
-          hitc = (p.mode & 3) == 0 ? __reduce_or_sync(0xffffffffu, hitc) : 0u;
-          if (p.mode & 128) hitc |= 1u;  // experiment: keep the slow-path code hot (chunk 0 rescanned every tile)
-          // ---- slow path (uniform loop over the flagged chunks): read the chunk again, append every
-          // value below the row's threshold with branch-free predicated stores
-          while (hitc) {
-            const int c = __ffs(hitc) - 1;
-            hitc &= hitc - 1;
-            ptx::tmem_ld32(t_acc + c * 32, va);
-            ptx::tmem_ld_wait();
-            const int base = t * TILE + c * 32;
-            const float mcc = c == 0 ? mc[0] : (c == 1 ? mc[1] : (c == 2 ? mc[2] : mc[3]));
-            B200_APPEND_CHUNK(va, base, mcc);
-          }
+          // every column of the tile has been read: hand the accumulator back before the last chunk
+          ptx::tc_fence_before();
+          __syncwarp();
+          if (lane == 0) ptx::mbar_arrive(bar_e);
+          B200_CHUNK(3, nl.w);
+          if (DBG) st_tile += clock64() - c6;
+#undef B200_CHUNK
+#undef B200_PUSH
+        } else {
+          ptx::tc_fence_before();
+          __syncwarp();
+          if (lane == 0) ptx::mbar_arrive(bar_e);
         }
-        ptx::tc_fence_before();
-        __syncwarp();
-        if (lane == 0) ptx::mbar_arrive(ptx::smem_u32(&bar_acce[a * 2 + half]));
-        if (warp == 0 && lane == 0) B200_TRACE(2, (int)it, 1);
-      }
-      // ---- final trim: a row left with more than 32 entries is cut to its keep best, so the re-rank
-      // takes every query's candidates in one pass of its warp (one candidate row per lane)
-      if (p.keep <= 32 && !(p.flags & 1024)) {
-        const int keep = p.keep;
-        unsigned need = __ballot_sync(0xffffffffu, cnt > 32);
-        while (need) {
-          const int r = __ffs(need) - 1;
-          need &= need - 1;
-          const int nv = __shfl_sync(0xffffffffu, cnt, r);
-          const float nt = compact_row<CAP>(bsc, bid, RS, row0 + r, nv, keep, lane);
-          if (lane == r) {
-            tau = fminf(tau, nt);
-            cnt = keep;
-          }
-        }
-      }
-      // ---- flush this block's candidate lists (coalesced, one row at a time)
-      const int64_t q0 = (int64_t)qb * ROWS + row0;
-      p.cand_cnt[q0 + lane] = cnt;
-      p.cand_tau[q0 + lane] = tau;
-      for (int r = 0; r < 32; ++r) {
-        const int nv = __shfl_sync(0xffffffffu, cnt, r);
-        for (int j = lane; j < nv; j += 32) p.cand_idx[(q0 + r) * CAP + j] = bid[j * RS + row0 + r];
       }
       __syncwarp();
+      if (lane == 0) ptx::st_release_shared(c_done, (uint32_t)(b + 1));  // everything of this block is queued
+    }
+    if (DBG && p.stats && lane == 0) {
+      atomicAdd(p.stats + 5, (unsigned long long)st_full);
+      atomicAdd(p.stats + 6, (unsigned long long)st_ready);
+      atomicAdd(p.stats + 7, (unsigned long long)st_acc);
+      atomicAdd(p.stats + 8, (unsigned long long)st_push);
+      atomicAdd(p.stats + 9, (unsigned long long)st_rel);
+      atomicAdd(p.stats + 10, (unsigned long long)st_tile);
+      atomicAdd(p.stats + 11, st_npush);
+    }
+  } else {
+    // ===================== selection: queue entries -> sorted candidate lists ======================
+    const int c = warp - 2 * E;  // row block: rows c*32 .. c*32+31, fed by epilogue warps c and E + c
+    float* ls0 = lsc + (size_t)c * 32 * W;
+    int* li0 = lid + (size_t)c * 32 * W;
+    float* tau0 = tau_sh + c * 32;
+    const uint32_t c_ready = ptx::smem_u32(&ready[c]);
+    const int keep = p.keep;
+    uint32_t tail[2] = {0u, 0u};
+    long long st_busy = 0;  // instrumented build only
+    unsigned long long st_ev = 0, st_hit = 0, st_surv = 0, st_bulk = 0;
+    for (int b = 0; b < nqb; ++b) {
+      const int qb = (int)blockIdx.x + b * (int)gridDim.x;
+      for (int e = lane; e < 32 * W; e += 32) {
+        ls0[e] = CUDART_INF_F;
+        li0[e] = -1;
+      }
+      tau0[lane] = CUDART_INF_F;
+      __syncwarp();
+      if (lane == 0) ptx::st_release_shared(c_ready, (uint32_t)(b + 1));
+      uint32_t spins = 0;
+      for (;;) {
+        bool any = false;
+#pragma unroll
+        for (int g = 0; g < 2; ++g) {
+          const int w = g * E + c;
+          const float* myq = que + (size_t)w * QE * QWORDS;
+          const uint32_t c_head = ptx::smem_u32(&ctl[w * 4 + 0]), c_tail = ptx::smem_u32(&ctl[w * 4 + 1]);
+          const uint32_t h = ptx::ld_acquire_shared(c_head);
+          uint32_t tl = tail[g];
+          any = any || tl != h;
+          const long long c0 = (DBG && tl != h) ? clock64() : 0;
+          while (tl != h) {
+            const float* e = myq + (size_t)(tl & (uint32_t)(QE - 1)) * QWORDS;
+            const int4 meta = *reinterpret_cast<const int4*>(e + 32);
+            const float s = e[lane] + __int_as_float(meta.z);  // dot + nlo of the chunk
+            ++tl;
+            const int rl = meta.x, base = meta.y;
+            const float tau = tau0[rl];
+            const bool ok = s < tau && base + lane < p.ncols;
+            const unsigned m = __ballot_sync(0xffffffffu, ok);
+            // the entry's words are in registers (the ballot consumed them): the slot may be refilled
+            if (lane == 0) ptx::st_volatile_shared_u32(c_tail, tl);
+            if (DBG) {
+              ++st_ev;
+              st_hit += m != 0;
+              st_surv += __popc(m);
+              st_bulk += __popc(m) >= 6;
+            }
+            if (m == 0) continue;
+            const float nt = take_entry<U>(ls0 + (size_t)rl * W, li0 + (size_t)rl * W, s, ok, m, base, tau, keep, lane);
+            if (lane == 0 && nt != tau) ptx::st_volatile_shared_f32(ptx::smem_u32(&tau0[rl]), nt);
+            __syncwarp();
+          }
+          if (DBG && c0) st_busy += clock64() - c0;
+          tail[g] = tl;
+        }
+        if (any) {
+          spins = 0;
+          continue;
+        }
+        // both queues looked empty: finished once both epilogue warps have queued everything
+        // (done is written after the last head update, so re-reading the heads after it is conclusive)
+        if (ptx::ld_acquire_shared(ptx::smem_u32(&ctl[c * 4 + 2])) == (uint32_t)(b + 1) &&
+            ptx::ld_acquire_shared(ptx::smem_u32(&ctl[(E + c) * 4 + 2])) == (uint32_t)(b + 1)) {
+          if (ptx::ld_acquire_shared(ptx::smem_u32(&ctl[c * 4 + 0])) == tail[0] &&
+              ptx::ld_acquire_shared(ptx::smem_u32(&ctl[(E + c) * 4 + 0])) == tail[1])
+            break;
+          continue;
+        }
+        __nanosleep(32);
+        B200_SPIN_GUARD(spins);
+      }
+      // ---- flush this block's candidate lists (coalesced, one row at a time)
+      const int64_t q0 = (int64_t)qb * ROWS + c * 32;
+      int my_cnt = 0;
+      for (int r = 0; r < 32; ++r) {
+        int nv = 0;
+#pragma unroll
+        for (int u = 0; u < U; ++u) {
+          const int e = u * 32 + lane;
+          const int id = li0[(size_t)r * W + e];
+          p.cand_idx[(q0 + r) * W + e] = id;
+          nv += __popc(__ballot_sync(0xffffffffu, id >= 0 && e < keep));
+        }
+        if (lane == r) my_cnt = nv;
+      }
+      p.cand_cnt[q0 + lane] = my_cnt;
+      p.cand_tau[q0 + lane] = tau0[lane];
+      __syncwarp();
+    }
+    if (DBG && p.stats && lane == 0) {
+      atomicAdd(p.stats + 0, st_ev);
+      atomicAdd(p.stats + 1, st_hit);
+      atomicAdd(p.stats + 2, st_surv);
+      atomicAdd(p.stats + 3, st_bulk);
+      atomicAdd(p.stats + 4, (unsigned long long)st_busy);
     }
   }
   ptx::tc_fence_before();
   __syncthreads();
-  if (warp == EPI_WARPS + 1) ptx::tmem_dealloc(tmem_base, 512);
+  if (warp == 3 * E + 1) ptx::tmem_dealloc(tmem_base, 512);
 }
-
-#include "knn_tc_ts.cuh"
 
 // ------------------------------------------------------------------ fp64 re-rank
 // One warp per query: exact squared distances of its candidates (reference
@@ -757,10 +852,12 @@ rerank_kernel(const double* __restrict__ x, int64_t n, int d, const double* __re
     bool good = nvalid >= k;
     float tau = cand_tau[p];
     for (int r = 1; r < L.nlists; ++r) tau = fminf(tau, cand_tau[r * L.meta_elems + p]);  // bound for every non-candidate
+    const QMeta mq = meta[p];
+    good = good && mq.err < CUDART_INF;  // a query the fp16 image cannot hold is never certified
     if (good && tau < CUDART_INF_F) {
-      // scaled units: every non-candidate j has  d2_j * s^2 >= tau - E + ||x_q||^2
-      const QMeta mq = meta[p];
-      const double lb = (double)tau - mq.err + mq.qn2;
+      // scaled units: every non-candidate j has  dot_j + nlo_j >= tau (1 - 2^-24) (fp32 rounding of the sum),
+      // hence  d2_j * s^2 >= tau - 2^-23 |tau| - E + ||x_q||^2
+      const double lb = (double)tau - 1.1920928955078125e-7 * fabs((double)tau) - mq.err + mq.qn2;
       const double cm = fmax(data_cmax, mq.cmax) * scale;
       const double slack = 1e-7 * fabs(lb) + 1e-9 * (double)d * cm * cm;  // fp64 rounding of the centred form
       good = s_dk[w] * scale * scale < lb - slack;
@@ -774,28 +871,17 @@ rerank_kernel(const double* __restrict__ x, int64_t n, int d, const double* __re
 // ------------------------------------------------------------------ host side
 namespace {
 
-// Two stage-1 kernels.  knn_tc_kernel (SS form, default) takes 128- or 64-row sub-tile images in
-// either layout.  knn_ts_kernel (TS form, tc_flags bit 6; 64-row chunk-major images) has the faster
-// pipeline -- its distance + min-tree path alone runs at 0.97 of the measured cuBLAS peak against
-// 0.86 -- but its epilogue warps are saturated, so survivor handling is not hidden and the whole
-// kernel is ~8 % slower at C5 (profiles/r01/README.md); kept selectable for the next round.
-inline bool use_ts(const b200_model* m) { return (m->tc_flags & 64) != 0; }
-
 int tc_prepare(b200_model* m, cudaStream_t st) {
   TcData& t = m->tc;
-  const int want_sub = use_ts(m) ? 64 : m->tc_sub, want_rg = use_ts(m) ? 0 : ((m->tc_flags >> 1) & 1);
-  const int want_order = (m->tc_flags >> 7) & 1;
-  if (t.ready && t.sub == want_sub && t.rg == want_rg && t.order == want_order) return 0;
-  t.sub = want_sub;
-  t.rg = want_rg;
-  t.order = want_order;
+  if (t.ready) return 0;
   const int64_t n = m->n;
   const int d = m->d;
   t.K = tc::padK(d);
-  t.tiles = (n + tc::TILE - 1) / tc::TILE;  // 128-column tiles = pairs of 64-row sub-tile images
+  t.tiles = (n + tc::TILE - 1) / tc::TILE;
   const int64_t npad = t.tiles * tc::TILE;
   B200_TRY(t.mu.reserve((size_t)d * 8 + 64));
   B200_TRY(t.img.reserve((size_t)npad * t.K * 2));
+  B200_TRY(t.nlo.reserve((size_t)t.tiles * 4 * sizeof(float) + 64));
   B200_TRY(m->flags.reserve(256));
   B200_CUDA(cudaMemsetAsync(t.mu.p, 0, (size_t)d * 8, st));
   B200_CUDA(cudaMemsetAsync(m->flags.p, 0, 256, st));
@@ -825,12 +911,10 @@ int tc_prepare(b200_model* m, cudaStream_t st) {
     t.scale = ldexp(1.0, -ex);   // |centred value| * scale < 1
   }
   t.cmax = mr;
-  // image position -> fitted row, by increasing centred norm (tc_flags bit 7: fitted order, for A/B runs)
+  // image position -> fitted row, by increasing centred norm
   B200_TRY(t.perm.reserve((size_t)n * 4 + 64));
   const unsigned nb = (unsigned)((n + 255) / 256);
-  if (m->tc_flags & 128) {
-    tc::iota_kernel<<<nb, 256, 0, st>>>(t.perm.as<int32_t>(), n);
-  } else {
+  {
     DevBuf keys, vals, tmp;
     B200_TRY(keys.reserve((size_t)n * 8 + 64));
     B200_TRY(vals.reserve((size_t)n * 4 + 64));
@@ -860,8 +944,8 @@ int tc_prepare(b200_model* m, cudaStream_t st) {
     m->st.launches += 1;
   }
   B200_CUDA(cudaMemsetAsync(bits, 0, 8, st));
-  tc::data_img_kernel<<<(unsigned)((npad + 127) / 128), 128, 0, st>>>(m->x, n, d, t.K, t.sub, t.rg, t.mu.as<double>(), t.scale,
-                                                                       t.perm.as<int32_t>(), t.img.as<__half>(), npad, bits);
+  tc::data_img_kernel<<<(unsigned)(npad / 128), 128, 0, st>>>(m->x, n, d, t.K, t.mu.as<double>(), t.scale, t.perm.as<int32_t>(),
+                                                              t.img.as<__half>(), t.nlo.as<float>(), npad, bits);
   B200_CUDA(cudaGetLastError());
   B200_CUDA(cudaMemcpyAsync(hb, bits, 8, cudaMemcpyDeviceToHost, st));
   B200_CUDA(cudaStreamSynchronize(st));
@@ -872,107 +956,53 @@ int tc_prepare(b200_model* m, cudaStream_t st) {
 }
 
 struct TcConfig {
-  int cap, halves, slots, keep, stages;
+  int u, halves, slots, keep, qent;
   size_t smem;
 };
 
-// Candidate capacity and CTA shape for k (+1 when the query's own row is dropped later):
-// a compaction keeps `keep` = k + margin entries of a CAP-slot buffer; CAP leaves room for
-// at least 16 appends between compactions; the B ring gets whatever shared memory is left.
-bool tc_config(int d, int k, int margin, bool self, int subrows, int force_halves, TcConfig* c) {
+// Kernel shape for k (+1 when the query's own row is dropped later): the sorted list of a row holds
+// 32*u entries (u = 1, 2, 4), of which the first keep = k + margin count; two 128-row halves per CTA
+// when shared memory allows, else one; the data-tile ring and the selection queues share what is left.
+bool tc_config(int d, int k, int margin, bool self, int force_halves, TcConfig* c, int force_slots = 0) {
   const int K = tc::padK(d);
   const int base = k + (self ? 1 : 0);
   int keep = base + (margin < 0 ? std::max(4, std::min(k / 2, 16)) : margin);
-  const int caps[4] = {32, 48, 64, 128};
-  int cap = 128;
-  for (int c0 : caps)
-    if (c0 >= keep + 20) {
-      cap = c0;
-      break;
-    }
-  if (keep > cap - 16) keep = cap - 16;
-  if (keep < base) return false;
-  const size_t tile = (size_t)tc::TILE * K * 2, sub = (size_t)subrows * K * 2;
-  const size_t limit = 227 * 1024 - 512;
+  if (base > 128) return false;
+  if (keep > 128) keep = 128;
+  const int u = keep <= 32 ? 1 : (keep <= 64 ? 2 : 4);
+  const size_t tile = (size_t)tc::TILE * K * 2;
+  const size_t limit = 227 * 1024 - 1024;
   for (int halves = 2; halves >= 1; --halves) {
     if (force_halves && halves != force_halves) continue;
-    const size_t fixed = halves * tile + (size_t)cap * (halves * tc::TILE + 1) * 8 + 256;
-    if (fixed + (force_halves ? 2 : 3) * sub > limit) continue;
-    int slots = (int)std::min<size_t>(8, (limit - fixed) / sub);
-    slots = slots >= 8 ? 8 : (slots >= 4 ? 4 : 2);  // power of two: ring index by mask/shift
-    c->cap = cap;
-    c->halves = halves;
-    c->slots = slots;
-    c->keep = keep;
-    c->smem = fixed + slots * sub;
-    return true;
+    const int rows = halves * tc::TILE, epi = halves * 4;
+    const size_t fixed = halves * tile + (size_t)rows * 32 * u * 8 + (size_t)rows * 4 + (size_t)epi * 36 + 512;
+    const int choices[6][2] = {{8, 32}, {4, 32}, {8, 16}, {4, 16}, {2, 32}, {2, 16}};  // {ring slots, queue entries}
+    for (const auto& ch : choices) {
+      if (force_slots && ch[0] != force_slots) continue;
+      const size_t tot = fixed + (size_t)ch[0] * tile + (size_t)2 * epi * ch[1] * tc::QWORDS * 4;
+      if (tot > limit) continue;
+      c->u = u;
+      c->halves = halves;
+      c->slots = ch[0];
+      c->qent = ch[1];
+      c->keep = keep;
+      c->smem = tot;
+      return true;
+    }
   }
   return false;
 }
 
-// TS kernel: A lives in TMEM, so shared memory holds only the B ring (64-row sub-tiles) and the
-// candidate buffers; TMEM holds `stages` 64-column accumulators per half next to A (K/2 columns).
-bool tc_config_ts(int d, int k, int margin, bool self, int force_halves, TcConfig* c) {
-  const int K = tc::padK(d);
-  const int base = k + (self ? 1 : 0);
-  int keep = base + (margin < 0 ? std::max(4, std::min(k / 2, 16)) : margin);
-  const int caps[4] = {32, 48, 64, 128};
-  int cap = 128;
-  for (int c0 : caps)
-    if (c0 >= keep + 20) {
-      cap = c0;
-      break;
-    }
-  if (keep > cap - 16) keep = cap - 16;
-  if (keep < base) return false;
-  const size_t sub = (size_t)64 * K * 2;
-  const size_t limit = 227 * 1024 - 512;
-  for (int halves = 2; halves >= 1; --halves) {
-    if (force_halves && halves != force_halves) continue;
-    const int stages = std::min(6, (512 / halves - K / 2) / 64);
-    if (stages < 2) continue;
-    const size_t fixed = (size_t)cap * (halves * tc::TILE + 1) * 8 + 1024;
-    if (fixed + 4 * sub > limit) continue;
-    int slots = (int)std::min<size_t>(16, (limit - fixed) / sub);
-    slots = slots >= 16 ? 16 : (slots >= 8 ? 8 : 4);
-    c->cap = cap;
-    c->halves = halves;
-    c->slots = slots;
-    c->keep = keep;
-    c->stages = stages;
-    c->smem = fixed + slots * sub;
-    return true;
-  }
-  return false;
-}
-
-template <int CAP, int HALVES>
-int launch_ts(b200_model* m, const tc::KParams& kp, const TcConfig& cfg, bool dbg, cudaStream_t st) {
-  const int threads = (HALVES * 6 + 1) * 32;  // 4 epilogue + 2 issuer warps per half, one producer
-  const int grid = std::min(kp.qblocks, m->sm_count);
-  if (dbg) {
-    auto kern = tc::knn_ts_kernel<CAP, HALVES, true>;
-    B200_CUDA(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)cfg.smem));
-    kern<<<grid, threads, cfg.smem, st>>>(kp);
-  } else {
-    auto kern = tc::knn_ts_kernel<CAP, HALVES, false>;
-    B200_CUDA(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)cfg.smem));
-    kern<<<grid, threads, cfg.smem, st>>>(kp);
-  }
-  B200_CUDA(cudaGetLastError());
-  return 0;
-}
-
-template <int CAP, int HALVES>
+template <int U, int HALVES>
 int launch_tc(b200_model* m, const tc::KParams& kp, const TcConfig& cfg, bool dbg, cudaStream_t st) {
-  const int threads = (HALVES * 4 + 3) * 32;
+  const int threads = (HALVES * 12 + 3) * 32;
   const int grid = std::min(kp.qblocks, m->sm_count);
   if (dbg) {
-    auto kern = tc::knn_tc_kernel<CAP, HALVES, true>;
+    auto kern = tc::knn_tc_kernel<U, HALVES, true>;
     B200_CUDA(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)cfg.smem));
     kern<<<grid, threads, cfg.smem, st>>>(kp);
   } else {
-    auto kern = tc::knn_tc_kernel<CAP, HALVES, false>;
+    auto kern = tc::knn_tc_kernel<U, HALVES, false>;
     B200_CUDA(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)cfg.smem));
     kern<<<grid, threads, cfg.smem, st>>>(kp);
   }
@@ -984,8 +1014,7 @@ int launch_tc(b200_model* m, const tc::KParams& kp, const TcConfig& cfg, bool db
 
 bool tc_supported(const b200_model* m, int k) {
   TcConfig c;
-  if (m->d + tc::NORM_SLOTS > 256) return false;
-  return use_ts(m) ? tc_config_ts(m->d, k, 0, true, 0, &c) : tc_config(m->d, k, 0, true, 128, 0, &c);
+  return tc_config(m->d, k, 0, true, 0, &c);
 }
 
 static bool t_tiles_ok(const b200_model* m, int split) { return m->tc.tiles >= (int64_t)split * 64; }
@@ -999,51 +1028,42 @@ int knn_tc(b200_model* m, const double* z_dev, int64_t q, int k, int64_t self_of
   }
   B200_TRY(tc_prepare(m, st));
   TcConfig cfg;
-  const bool ts = use_ts(m);
-  cfg.stages = 0;
-  if (!(ts ? tc_config_ts(m->d, k, m->margin, self_offset >= 0, m->tc_halves, &cfg)
-           : tc_config(m->d, k, m->margin, self_offset >= 0, m->tc.sub, m->tc_halves, &cfg))) {
+  if (!tc_config(m->d, k, m->margin, self_offset >= 0, m->tc_halves, &cfg, m->tc_slots)) {
     set_error("tensor kNN path unsupported for d=%d k=%d", m->d, k);
     return 1;
   }
   // Wave quantisation: the persistent grid takes sm_count 256-query blocks per round.  When the last
-  // round would keep at most half the SMs busy, those queries go to a second launch with 128-query
-  // blocks (twice as many, one round, ~0.64 of a full round's time).  8 GPUs x 125 k queries: 3.64
-  // instead of 4 rounds.
-  if (cfg.halves == 2 && m->tc_halves == 0 && m->tc_split == 0 && !ts && m->tc_mode == 0 && !m->dbg_scores && !m->dbg_trace &&
-      !(m->tc_flags & 8192)) {
+  // round would keep at most half the SMs busy, those queries go to a second call whose data stream is
+  // split over S concurrent launches on the otherwise idle SMs, S candidate lists per query merged by
+  // the re-rank.  8 GPUs x 125 k queries: 3.3 rounds instead of 4.
+  if (cfg.halves == 2 && cfg.u == 1 && m->tc_halves == 0 && m->tc_split == 0 && m->tc_mode == 0 && !m->dbg_scores &&
+      !m->no_tail_split) {
     const int64_t blocks = (q + 2 * tc::TILE - 1) / (2 * tc::TILE);
     const int64_t rounds = blocks / m->sm_count, tail = blocks - rounds * m->sm_count;
-    TcConfig c1;
-    if (rounds >= 1 && tail > 0 && 2 * tail <= m->sm_count &&
-        tc_config(m->d, k, m->margin, self_offset >= 0, m->tc.sub, 1, &c1)) {
-      const int64_t q_main = rounds * m->sm_count * 2 * tc::TILE;
-      B200_TRY(knn_tc(m, z_dev, q_main, k, self_offset, idx_dev, d2_dev, st));
-      // the tail: either 128-query blocks (tc_flags bit 15), or -- default -- the same 256-query blocks with
-      // the data stream split over S concurrent launches on the otherwise idle SMs, S candidate lists per
-      // query merged by the re-rank
+    if (rounds >= 1 && tail > 0 && 2 * tail <= m->sm_count) {
       const int split = (int)std::min<int64_t>(4, m->sm_count / tail);
-      const bool use_split = split >= 2 && cfg.keep <= 32 && t_tiles_ok(m, split) && !(m->tc_flags & 32768);
-      if (use_split) m->tc_split = split;
-      else m->tc_halves = 1;
-      m->defer_base += q_main;
-      const int rc = knn_tc(m, z_dev + (size_t)q_main * m->d, q - q_main, k,
-                            self_offset >= 0 ? self_offset + q_main : -1, idx_dev + (size_t)q_main * k,
-                            d2_dev + (size_t)q_main * k, st);
-      m->defer_base -= q_main;
-      m->tc_halves = 0;
-      m->tc_split = 0;
-      m->st.last_halves = 2;
-      return rc;
+      if (split >= 2 && t_tiles_ok(m, split)) {
+        const int64_t q_main = rounds * m->sm_count * 2 * tc::TILE;
+        B200_TRY(knn_tc(m, z_dev, q_main, k, self_offset, idx_dev, d2_dev, st));
+        m->tc_split = split;
+        m->defer_base += q_main;
+        const int rc = knn_tc(m, z_dev + (size_t)q_main * m->d, q - q_main, k,
+                              self_offset >= 0 ? self_offset + q_main : -1, idx_dev + (size_t)q_main * k,
+                              d2_dev + (size_t)q_main * k, st);
+        m->defer_base -= q_main;
+        m->tc_split = 0;
+        return rc;
+      }
     }
   }
   const TcData& t = m->tc;
   const int rows = cfg.halves * tc::TILE;
+  const int W = 32 * cfg.u;
   const int qblocks = (int)((q + rows - 1) / rows);
   const int64_t qpad = (int64_t)qblocks * rows;
   const int S = m->tc_split > 1 ? m->tc_split : 1;  // concurrent launches over sub-ranges of the data stream
   B200_TRY(m->zimg.reserve((size_t)qpad * t.K * 2));
-  B200_TRY(m->cand.reserve((size_t)S * qpad * cfg.cap * 4));
+  B200_TRY(m->cand.reserve((size_t)S * qpad * W * 4));
   B200_TRY(m->cand_meta.reserve((size_t)qpad * (8 * S + sizeof(tc::QMeta)) + 64));
   B200_TRY(m->flags.reserve(256));
   B200_TRY(m->misc.reserve((size_t)q * 4 + 64));
@@ -1055,56 +1075,45 @@ int knn_tc(b200_model* m, const double* z_dev, int64_t q, int k, int64_t self_of
   float* dbg = m->dbg_scores;
 
   cudaEventRecord(m->ev3, st);
-  tc::query_img_kernel<<<(unsigned)((qpad + 127) / 128), 128, 0, st>>>(z_dev, q, m->d, t.K, t.rg, t.mu.as<double>(), t.scale,
-                                                                        t.ymax, m->zimg.as<__half>(), qpad, meta);
+  tc::query_img_kernel<<<(unsigned)((qpad + 127) / 128), 128, 0, st>>>(z_dev, q, m->d, t.K, t.mu.as<double>(), t.scale, t.ymax,
+                                                                        m->zimg.as<__half>(), qpad, meta);
   B200_CUDA(cudaGetLastError());
   cudaEventRecord(m->ev0, st);
   tc::KParams kp;
   kp.a_img = m->zimg.as<__half>();
   kp.b_img = t.img.as<__half>();
+  kp.nlo = t.nlo.as<float>();
   kp.K = t.K;
   kp.ntiles = (int)t.tiles;
+  kp.ncols = (int)m->n;
   kp.qblocks = qblocks;
   kp.slots = cfg.slots;
-  kp.stages = cfg.stages;
-  kp.sub = t.sub;
-  kp.flags = m->tc_flags;
+  kp.qent = cfg.qent;
   kp.keep = cfg.keep;
   kp.mode = m->tc_mode;
   kp.cand_idx = m->cand.as<int32_t>();
   kp.cand_cnt = cand_cnt;
   kp.cand_tau = cand_tau;
   kp.dbg = dbg;
-  kp.trace = m->dbg_trace;
-  kp.trace_start = m->tc_trace_start;
-  const bool dg = dbg != nullptr || kp.trace != nullptr || (m->tc_mode & 12);  // trace and MMA/TMA knock-outs live in the debug build
+  kp.stats = nullptr;
+  if (m->tc_stats) {  // instrumented build: event and stall counters (tuning only)
+    kp.stats = reinterpret_cast<unsigned long long*>(m->flags.as<char>() + 64);
+    B200_CUDA(cudaMemsetAsync(kp.stats, 0, 128, st));
+  }
+  const bool dg = dbg != nullptr || kp.stats != nullptr;
   auto launch_one = [&](const tc::KParams& kq, cudaStream_t s_) -> int {
-    int rc = 1;
-    if (ts) {
-      if (cfg.cap == 32 && cfg.halves == 2) rc = launch_ts<32, 2>(m, kq, cfg, dg, s_);
-      else if (cfg.cap == 48 && cfg.halves == 2) rc = launch_ts<48, 2>(m, kq, cfg, dg, s_);
-      else if (cfg.cap == 64 && cfg.halves == 2) rc = launch_ts<64, 2>(m, kq, cfg, dg, s_);
-      else if (cfg.cap == 128 && cfg.halves == 2) rc = launch_ts<128, 2>(m, kq, cfg, dg, s_);
-      else if (cfg.cap == 32 && cfg.halves == 1) rc = launch_ts<32, 1>(m, kq, cfg, dg, s_);
-      else if (cfg.cap == 48 && cfg.halves == 1) rc = launch_ts<48, 1>(m, kq, cfg, dg, s_);
-      else if (cfg.cap == 64 && cfg.halves == 1) rc = launch_ts<64, 1>(m, kq, cfg, dg, s_);
-      else if (cfg.cap == 128 && cfg.halves == 1) rc = launch_ts<128, 1>(m, kq, cfg, dg, s_);
-      else set_error("tensor kNN: no kernel for cap=%d halves=%d", cfg.cap, cfg.halves);
-    } else if (cfg.cap == 32 && cfg.halves == 2) rc = launch_tc<32, 2>(m, kq, cfg, dg, s_);
-    else if (cfg.cap == 48 && cfg.halves == 2) rc = launch_tc<48, 2>(m, kq, cfg, dg, s_);
-    else if (cfg.cap == 48 && cfg.halves == 1) rc = launch_tc<48, 1>(m, kq, cfg, dg, s_);
-    else if (cfg.cap == 64 && cfg.halves == 2) rc = launch_tc<64, 2>(m, kq, cfg, dg, s_);
-    else if (cfg.cap == 128 && cfg.halves == 1) rc = launch_tc<128, 1>(m, kq, cfg, dg, s_);
-    else if (cfg.cap == 32 && cfg.halves == 1) rc = launch_tc<32, 1>(m, kq, cfg, dg, s_);
-    else if (cfg.cap == 64 && cfg.halves == 1) rc = launch_tc<64, 1>(m, kq, cfg, dg, s_);
-    else set_error("tensor kNN: no kernel for cap=%d halves=%d", cfg.cap, cfg.halves);
-
-    return rc;
+    if (cfg.u == 1 && cfg.halves == 2) return launch_tc<1, 2>(m, kq, cfg, dg, s_);
+    if (cfg.u == 1 && cfg.halves == 1) return launch_tc<1, 1>(m, kq, cfg, dg, s_);
+    if (cfg.u == 2 && cfg.halves == 2) return launch_tc<2, 2>(m, kq, cfg, dg, s_);
+    if (cfg.u == 2 && cfg.halves == 1) return launch_tc<2, 1>(m, kq, cfg, dg, s_);
+    if (cfg.u == 4 && cfg.halves == 1) return launch_tc<4, 1>(m, kq, cfg, dg, s_);
+    set_error("tensor kNN: no kernel for u=%d halves=%d", cfg.u, cfg.halves);
+    return 1;
   };
   int rc = 1;
   tc::RerankLists L;
   L.nlists = S;
-  L.list_elems = (int64_t)qpad * cfg.cap;
+  L.list_elems = (int64_t)qpad * W;
   L.meta_elems = qpad;
   for (int r = 0; r < 4; ++r) L.off[r] = 0;
   if (S == 1) {
@@ -1118,7 +1127,9 @@ int knn_tc(b200_model* m, const double* z_dev, int64_t q, int k, int64_t self_of
       const int64_t lo = t.tiles * r / S, hi = t.tiles * (r + 1) / S;
       tc::KParams kq = kp;
       kq.b_img = kp.b_img + (size_t)lo * tc::TILE * t.K;
+      kq.nlo = kp.nlo + (size_t)lo * 4;
       kq.ntiles = (int)(hi - lo);
+      kq.ncols = (int)std::min<int64_t>(m->n - lo * tc::TILE, (hi - lo) * tc::TILE);
       kq.cand_idx = kp.cand_idx + (size_t)r * L.list_elems;
       kq.cand_cnt = kp.cand_cnt + (size_t)r * qpad;
       kq.cand_tau = kp.cand_tau + (size_t)r * qpad;
@@ -1132,11 +1143,11 @@ int knn_tc(b200_model* m, const double* z_dev, int64_t q, int k, int64_t self_of
   }
   B200_TRY(rc);
   cudaEventRecord(m->ev1, st);
-  m->st.last_cap = cfg.cap;
+  m->st.last_cap = W;
   m->st.last_keep = cfg.keep;
   m->st.last_slots = cfg.slots;
   m->st.last_halves = cfg.halves;
-  if (m->tc_mode != 0) {  // debug ceilings: outputs are meaningless, only stage 1 is timed
+  if (m->tc_mode != 0) {  // ceilings: outputs are meaningless, only stage 1 is timed
     B200_CUDA(cudaEventSynchronize(m->ev1));
     float msd = 0;
     cudaEventElapsedTime(&msd, m->ev0, m->ev1);
@@ -1147,15 +1158,12 @@ int knn_tc(b200_model* m, const double* z_dev, int64_t q, int k, int64_t self_of
   B200_CUDA(cudaMemsetAsync(fail_cnt, 0, 4, st));
   const unsigned rb = (unsigned)((q + 7) / 8);
 #define RERANK(CAPV)                                                                                     \
-  tc::rerank_kernel<CAPV><<<rb, 256, (size_t)8 * ((m->d + 1) & ~1) * 8, st>>>(m->x, m->n, m->d, z_dev, q, k, self_offset, kp.cand_idx, cfg.cap, \
-                                              cand_cnt, cand_tau, meta, t.scale, t.cmax, t.perm.as<int32_t>(),                  \
-                                              (m->tc_flags & 16384) ? nullptr : t.xs.as<double>(), idx_dev, d2_dev, \
-                                              fail_list, fail_cnt, L)
-  // the SS kernel's final trim leaves at most 32 candidates per query when keep <= 32
-  const bool one_pass = !ts && cfg.keep <= 32 && !(m->tc_flags & (1024 | 2048));
-  if (S > 1) RERANK(128);  // pass r of the 128-slot instance takes list r
-  else if (cfg.cap == 32 || one_pass) RERANK(32);
-  else if (cfg.cap <= 64) RERANK(64);
+  tc::rerank_kernel<CAPV><<<rb, 256, (size_t)8 * ((m->d + 1) & ~1) * 8, st>>>(                           \
+      m->x, m->n, m->d, z_dev, q, k, self_offset, kp.cand_idx, W, cand_cnt, cand_tau, meta, t.scale, t.cmax, \
+      t.perm.as<int32_t>(), t.xs.as<double>(), idx_dev, d2_dev, fail_list, fail_cnt, L)
+  if (S > 1) RERANK(128);  // pass r of the 128-slot instance takes list r (u = 1: at most 32 entries each)
+  else if (cfg.u == 1) RERANK(32);
+  else if (cfg.u == 2) RERANK(64);
   else RERANK(128);
 #undef RERANK
   B200_CUDA(cudaGetLastError());
@@ -1163,10 +1171,14 @@ int knn_tc(b200_model* m, const double* z_dev, int64_t q, int k, int64_t self_of
   int h_fail = 0;
   B200_CUDA(cudaMemcpyAsync(&h_fail, fail_cnt, 4, cudaMemcpyDeviceToHost, st));
   B200_CUDA(cudaStreamSynchronize(st));
-  float ms1 = 0, ms2 = 0;
+  if (kp.stats) {
+    unsigned long long hs[16];
+    B200_CUDA(cudaMemcpy(hs, kp.stats, 128, cudaMemcpyDeviceToHost));
+    for (int i = 0; i < 16; ++i) m->tc_stat_vals[i] += (double)hs[i];
+  }
+  float ms1 = 0, ms2 = 0, ms0 = 0;
   cudaEventElapsedTime(&ms1, m->ev0, m->ev1);
   cudaEventElapsedTime(&ms2, m->ev1, m->ev2);
-  float ms0 = 0;
   cudaEventElapsedTime(&ms0, m->ev3, m->ev0);
   m->st.ms_prep += ms0;
   m->st.ms_stage1 += ms1;
@@ -1174,9 +1186,6 @@ int knn_tc(b200_model* m, const double* z_dev, int64_t q, int k, int64_t self_of
   m->st.launches += 3 + (S - 1);  // query image, S stage-1 launches, re-rank
   m->st.tc_queries += q;
   m->st.uncertified += h_fail;
-  m->st.last_cap = cfg.cap;
-  m->st.last_keep = cfg.keep;
-  m->st.last_slots = cfg.slots;
   if (h_fail > 0 && m->defer_fallback && h_fail <= 64 && m->deferred.size() + h_fail <= 512) {
     // the caller resolves these after its last chunk (one pass over the fitted points instead of one per chunk)
     std::vector<int32_t> loc(h_fail);
@@ -1186,7 +1195,7 @@ int knn_tc(b200_model* m, const double* z_dev, int64_t q, int k, int64_t self_of
   }
   if (h_fail > 0) {
     cudaEventRecord(m->ev0, st);
-    if (m->tc_flags & 4096) B200_TRY(knn_exact(m, z_dev, q, k, self_offset, idx_dev, d2_dev, fail_list, h_fail, st));
+    if (m->force_split_fallback) B200_TRY(knn_exact(m, z_dev, q, k, self_offset, idx_dev, d2_dev, fail_list, h_fail, st));
     else B200_TRY(knn_rescan(m, z_dev, q, k, self_offset, idx_dev, d2_dev, fail_list, h_fail, st));
     cudaEventRecord(m->ev1, st);
     B200_CUDA(cudaEventSynchronize(m->ev1));

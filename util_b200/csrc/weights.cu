@@ -162,7 +162,7 @@ avg_shepard_thread_kernel(const double* __restrict__ d2, int64_t q, int k, int m
       double s = 0.0;  // base.py:169: left to right from 0
 #pragma unroll
       for (int i = 0; i < KMAX; ++i)
-        if (i < k) s = __dadd_rn(s, __dmul_rn(y[(int64_t)nb[i] * r + c], w[i]));
+        if (i < k) s = __dadd_rn(s, nb[i] >= 0 ? __dmul_rn(y[(int64_t)nb[i] * r + c], w[i]) : CUDART_NAN);
       out[p * r + c] = s;
     }
   }
@@ -197,7 +197,8 @@ voronoi_kernel(const double* __restrict__ x, int d, const double* __restrict__ z
   for (int j = t; j < d; j += nt) pts[j] = z[p * d + j];
   for (int e = t; e < k * d; e += nt) {
     const int i = e / d, j = e - i * d;
-    P[(size_t)i * dp + j] = x[(int64_t)id[i] * d + j];
+    // a neighbour slot can only be empty (-1) for a query with non-finite coordinates: the result is then NaN
+    P[(size_t)i * dp + j] = id[i] >= 0 ? x[(int64_t)id[i] * d + j] : CUDART_NAN;
   }
   __syncthreads();
   const double HUGEV = 1.7976931348623157e308;
@@ -258,7 +259,8 @@ voronoi_kernel(const double* __restrict__ x, int d, const double* __restrict__ z
         if (wts) wts[p * k + m] = wi;
         if (ids_out) ids_out[p * k + m] = id[i];
         if (out)
-          for (int c = 0; c < rr; ++c) acc[c] = __dadd_rn(acc[c], __dmul_rn(y[(int64_t)id[i] * r + c], wi));
+          for (int c = 0; c < rr; ++c)
+            acc[c] = __dadd_rn(acc[c], id[i] >= 0 ? __dmul_rn(y[(int64_t)id[i] * r + c], wi) : CUDART_NAN);
         ++m;
       }
     }
@@ -283,8 +285,10 @@ __global__ void wsum_kernel(const int32_t* __restrict__ ids, const double* __res
   const int64_t p = e / rc;
   const int c = c0 + (int)(e - p * rc);
   double s = 0.0;
-  for (int i = 0; i < cnt[p]; ++i)
-    s = __dadd_rn(s, __dmul_rn(y[(int64_t)ids[p * stride + i] * r + c], wts[p * stride + i]));
+  for (int i = 0; i < cnt[p]; ++i) {
+    const int id = ids[p * stride + i];
+    s = __dadd_rn(s, id >= 0 ? __dmul_rn(y[(int64_t)id * r + c], wts[p * stride + i]) : CUDART_NAN);
+  }
   out[p * r + c] = s;
 }
 
