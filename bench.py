@@ -162,6 +162,7 @@ def main():
     ap.add_argument("--margin", type=int, default=-1)
     ap.add_argument("--tc-halves", type=int, default=0)
     ap.add_argument("--tc-slots", type=int, default=0)
+    ap.add_argument("--tc-parts", type=int, default=1)
     ap.add_argument("--tc-stats", type=int, default=0, help="instrumented stage-1 kernel: event / stall counters")
     ap.add_argument("--tc-mode", type=int, default=0, help="ceilings: 1 no selection, 2 no epilogue")
     args = ap.parse_args()
@@ -206,6 +207,7 @@ def main():
     model.set_option("tc_mode", args.tc_mode)
     model.set_option("tc_halves", args.tc_halves)
     model.set_option("tc_slots", args.tc_slots)
+    model.set_option("tc_parts", args.tc_parts)
     model.set_option("tc_stats", args.tc_stats)
     h = model.handle
     if G > 1 and args.shard == "query":
@@ -361,7 +363,8 @@ def main():
                 "gpu_launches": int(round(stats["launches"] * args.steps)),
                 **({"tc_stats": {nm: model.stat(f"tc_stat{i}") / args.steps for i, nm in enumerate(
                     ["events", "events_hit", "survivors", "rank_merges", "sel_busy_clk", "queue_full_clk",
-                     "ready_wait_clk", "acc_wait_clk", "push_clk", "release_clk", "tile_clk", "pushes"])}} if args.tc_stats else {}),
+                     "ready_wait_clk", "acc_wait_clk", "push_clk", "release_clk", "tile_clk", "pushes",
+                     "push_clk_after_tile64", "pushes_after_tile64", "clk_to_tile512", "clk_to_tile64"])}} if args.tc_stats else {}),
                 "e2e": e2e, "clocks": sampler.summary()}
         if G == 1 and not args.no_cpu:
             v, s, dtc, cores, (cids, cout) = cpu_port(x, y, z, k, seconds=args.cpu_seconds)

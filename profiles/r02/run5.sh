@@ -1,0 +1,13 @@
+mkdir -p gpurun_out
+for args in "" "--tc-mode 1" "--tc-mode 2"; do
+  echo "== c5q $args"
+  timeout 600 python bench.py --config c5q --no-cpu --no-e2e --steps 3 $args 2>>gpurun_out/b.err | python -c "
+import sys,json
+for l in sys.stdin:
+    j=json.loads(l); print(j['ms_per_step'], j['roofline']['frac'], j['stages_ms']['ms_stage1'], j['uncertified_per_step'])"
+done
+timeout 900 python bench.py --steps 3 --no-cpu 2>> gpurun_out/b.err | python -c "
+import sys,json
+for l in sys.stdin:
+    j=json.loads(l); print(j['ms_per_step'], j['roofline']['frac'], j['stages_ms'], j['e2e']['value'], j['uncertified_per_step'], j['clocks'])"
+tail -3 gpurun_out/b.err

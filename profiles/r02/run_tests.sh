@@ -1,0 +1,3 @@
+mkdir -p gpurun_out
+timeout 2400 python -m pytest tests -x -q -m gpu 2>&1 | tail -15 > gpurun_out/t_all.log; cat gpurun_out/t_all.log
+python -c "import __graft_entry__ as g; g.smoke()" 2>&1 | tail -3

@@ -194,6 +194,7 @@ int b200_set_option(b200_model* m, const char* key, double value) {
   else if (!strcmp(key, "tc_halves")) m->tc_halves = (int)value;
   else if (!strcmp(key, "tc_slots")) m->tc_slots = (int)value;
   else if (!strcmp(key, "tc_stats")) m->tc_stats = (int)value;
+  else if (!strcmp(key, "tc_parts")) m->tc_parts = ((int)value == 2 || (int)value == 4) ? (int)value : 1;
   else if (!strcmp(key, "tail_split")) m->no_tail_split = value == 0.0;
   else if (!strcmp(key, "fallback")) m->force_split_fallback = (int)value == 1;
   else if (!strcmp(key, "rows_per_call")) m->rows_per_call = (int64_t)value;

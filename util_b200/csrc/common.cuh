@@ -105,6 +105,7 @@ struct b200_model {
   int margin = -1;  // extra candidates kept by the tensor filter (-1: max(4, min(k/2, 16)))
   int tc_stats = 0;   // 1: run the instrumented stage-1 kernel and accumulate its counters in tc_stat_vals
   double tc_stat_vals[16] = {0};
+  int tc_parts = 1;   // bulk copies per data tile
   int tc_slots = 0;   // force the depth of the data-tile ring (0: automatic)
   int tc_halves = 0;  // force 128*halves query rows per CTA (0: automatic)
   int tc_split = 0;   // internal: the data stream of this call is split over this many concurrent launches

@@ -231,7 +231,8 @@ struct KParams {
   int ncols;             // real image positions of this launch (the rest of the last tile is padding)
   int qblocks;           // query blocks of HALVES*128 rows
   int slots;             // depth of the data-tile ring (power of two)
-  int qent;              // entries per selection queue (power of two, >= 32)
+  int qent;              // entries per selection queue (power of two, >= 16)
+  int parts;             // bulk copies per data tile (1, 2 or 4)
   int keep;              // candidates kept per query (<= 32*U)
   int mode;              // 0 normal; ceilings: 1 = epilogue reads and reduces but queues nothing, 2 = epilogue only releases
   int32_t* cand_idx;     // [qpad][32*U]
@@ -246,11 +247,18 @@ struct KParams {
 // Spin limits: a protocol bug must end in a trap, not in a hung GPU (2^27 probes: seconds).
 #define B200_SPIN_GUARD(spins)            \
   do {                                    \
-    if (++(spins) > (1u << 27)) __trap(); \
+    if (++(spins) > (1u << 26)) __trap(); \
   } while (0)
 __device__ __forceinline__ void mbar_wait_lean(uint32_t bar, uint32_t parity) {
   uint32_t spins = 0;
   while (!ptx::mbar_try_wait(bar, parity)) B200_SPIN_GUARD(spins);
+}
+// The same with a suspend-time hint: the warp sleeps in hardware until the phase completes (or the
+// hint elapses) instead of re-issuing the probe.  This kernel is bound by instruction issue; sixteen
+// epilogue warps probing in a tight loop took a fifth of all issue slots.
+__device__ __forceinline__ void mbar_wait_suspend(uint32_t bar, uint32_t parity) {
+  uint32_t spins = 0;
+  while (!ptx::mbar_try_wait_hint(bar, parity, 4000)) B200_SPIN_GUARD(spins);
 }
 
 __device__ __forceinline__ float min3(float a, float b, float c) { return fminf(fminf(a, b), c); }
@@ -384,11 +392,12 @@ __device__ __forceinline__ float take_entry(float* ls, int* li, float s, bool ok
 }
 
 // Warp roles (E = 4*HALVES):
-//   [0, 2E)     epilogue, two groups of E warps: group g reads accumulator stage g, i.e. every other
-//               tile, so a warp has two tile periods for one tile (wake, four TMEM reads, filter, push);
+//   [0, 2E)     epilogue, two groups of E warps: group g reads columns [64g, 64g+64) of every tile, so an
+//               accumulator is handed back after two TMEM reads per warp instead of four -- the round
+//               trip MMA -> epilogue -> MMA on a stage is what the tensor pipe waits for;
 //               warp w = g*E + half*4 + quad, thread = query row (half*128 + quad*32 + lane)
 //   [2E, 3E)    selection: warp 2E + c owns rows c*32 .. c*32+31 and drains the queues of epilogue
-//               warps c (stage 0) and E + c (stage 1)
+//               warps c (columns 0-63) and E + c (columns 64-127)
 //   3E          producer (bulk copies);  3E+1, 3E+2  MMA issuers (issuer j = accumulator stage j)
 template <int U, int HALVES, bool DBG>
 __global__ void __launch_bounds__((HALVES * 12 + 3) * 32, 1) knn_tc_kernel(const KParams p) {
@@ -406,8 +415,12 @@ __global__ void __launch_bounds__((HALVES * 12 + 3) * 32, 1) knn_tc_kernel(const
   int* lid = reinterpret_cast<int*>(lsc + (size_t)ROWS * W);                 // [ROWS][W] list positions
   float* que = reinterpret_cast<float*>(lid + (size_t)ROWS * W);             // [2E][QE][QWORDS]
   float* tau_sh = que + (size_t)2 * E * QE * QWORDS;                         // [ROWS] thresholds (written by selection warps)
-  uint32_t* ctl = reinterpret_cast<uint32_t*>(tau_sh + ROWS);                // [2E][4]: head, tail, done, -;  then ready[E]
-  uint32_t* ready = ctl + 2 * E * 4;
+  // queue control words, indexed [row block][column group]: heads, tails, done marks; then ready[row block]
+  uint32_t* ctl = reinterpret_cast<uint32_t*>((reinterpret_cast<uintptr_t>(tau_sh + ROWS) + 7) & ~(uintptr_t)7);
+  uint32_t* q_head = ctl;
+  uint32_t* q_tail = ctl + 2 * E;
+  uint32_t* q_done = ctl + 4 * E;
+  uint32_t* ready = ctl + 6 * E;
   uint64_t* bars = reinterpret_cast<uint64_t*>((reinterpret_cast<uintptr_t>(ready + E) + 15) & ~(uintptr_t)15);
   // bars: full[8], empty[8], accf[stage][half], acce[stage][half], afull, aempty
   uint64_t* bar_full = bars;
@@ -429,13 +442,13 @@ __global__ void __launch_bounds__((HALVES * 12 + 3) * 32, 1) knn_tc_kernel(const
     }
     for (int a = 0; a < 4; ++a) {
       ptx::mbar_init(ptx::smem_u32(&bar_accf[a]), 1);
-      ptx::mbar_init(ptx::smem_u32(&bar_acce[a]), 4);  // the four epilogue warps of one half and stage
+      ptx::mbar_init(ptx::smem_u32(&bar_acce[a]), 8);  // the eight epilogue warps (4 quadrants x 2 column groups) of one half
     }
     ptx::mbar_init(ptx::smem_u32(bar_afull), 1);
     ptx::mbar_init(ptx::smem_u32(bar_aempty), 2);  // one commit per issuer warp
     ptx::fence_barrier_init();
   }
-  if (threadIdx.x < 2 * E * 4 + E) ctl[threadIdx.x] = 0;
+  if (threadIdx.x < 7 * E) ctl[threadIdx.x] = 0;
   if (warp == 3 * E + 1) {  // first MMA warp owns the TMEM allocation
     ptx::tmem_alloc(ptx::smem_u32(tmem_slot), 512);
     ptx::tmem_relinquish();
@@ -467,7 +480,10 @@ __global__ void __launch_bounds__((HALVES * 12 + 3) * 32, 1) knn_tc_kernel(const
         for (int t = 0; t < p.ntiles; ++t, src += tile_bytes) {
           ptx::mbar_wait(false, empty0 + s * 8, ph ^ 1, 64);
           ptx::mbar_arrive_expect_tx(full0 + s * 8, tile_bytes);
-          ptx::bulk_g2s(sB0 + s * tile_bytes, src, tile_bytes, full0 + s * 8);
+          // one tile as `parts` bulk copies: more requests in flight per slot (tile_bytes is a multiple of 4 KB)
+          const uint32_t part = tile_bytes / (uint32_t)p.parts;
+          for (int c = 0; c < p.parts; ++c)
+            ptx::bulk_g2s(sB0 + s * tile_bytes + c * part, src + c * part, part, full0 + s * 8);
           if (++s == (uint32_t)p.slots) {
             s = 0;
             ph ^= 1;
@@ -533,134 +549,149 @@ __global__ void __launch_bounds__((HALVES * 12 + 3) * 32, 1) knn_tc_kernel(const
     }
   } else if (warp < 2 * E) {
     // ===================== epilogue: threshold filter, survivors' chunks to the queue ==============
-    const int g = warp / E;            // accumulator stage this warp reads
+    // The kernel is bound by instruction issue (~1000 warp instructions per tile and SM sub-partition
+    // against 512 clk of tensor time), so this loop is written for instruction count.
+    const int g = warp / E;            // column group: this warp reads columns [64g, 64g+64) of every tile
     const int rb = warp - g * E;       // row block: half*4 + quad
     const int half = rb >> 2, quad = rb & 3;
     const int row = rb * 32 + lane;    // my query row inside the block
-    const uint32_t t_lane = ((uint32_t)(quad * 32) << 16) + g * ACC_COLS + half * TILE;
+    const uint32_t t_acc0 = ((uint32_t)(quad * 32) << 16) + half * TILE + g * 64;
     float* myq = que + (size_t)warp * QE * QWORDS;
-    const uint32_t c_head = ptx::smem_u32(&ctl[warp * 4 + 0]), c_tail = ptx::smem_u32(&ctl[warp * 4 + 1]);
-    const uint32_t c_done = ptx::smem_u32(&ctl[warp * 4 + 2]), c_ready = ptx::smem_u32(&ready[rb]);
+    const uint32_t c_head = ptx::smem_u32(&q_head[rb * 2 + g]), c_tail = ptx::smem_u32(&q_tail[rb * 2 + g]);
+    const uint32_t c_done = ptx::smem_u32(&q_done[rb * 2 + g]), c_ready = ptx::smem_u32(&ready[rb]);
     const uint32_t my_tau = ptx::smem_u32(&tau_sh[row]);
-    const uint32_t bar_f = ptx::smem_u32(&bar_accf[g * 2 + half]), bar_e = ptx::smem_u32(&bar_acce[g * 2 + half]);
+    const uint32_t bar_f0 = ptx::smem_u32(&bar_accf[half]), bar_e0 = ptx::smem_u32(&bar_acce[half]);
     const uint32_t lt_mask = (1u << lane) - 1u;
-    const float4* nlo4 = reinterpret_cast<const float4*>(p.nlo);
+    const int colg = g * 64;
+    // keep these loop constants in registers: left alone, the compiler re-derives the shared-memory
+    // addresses from the kernel parameters in every tile step (a dozen instructions each)
+#define B200_PIN32(x) asm volatile("" : "+r"(x))
+    uint32_t a_tacc = t_acc0, a_head = c_head, a_tail = c_tail, a_tau = my_tau, a_bf = bar_f0, a_be = bar_e0;
+    B200_PIN32(a_tacc);
+    B200_PIN32(a_head);
+    B200_PIN32(a_tail);
+    B200_PIN32(a_tau);
+    B200_PIN32(a_bf);
+    B200_PIN32(a_be);
+    asm volatile("" : "+l"(myq));
+#undef B200_PIN32
     uint32_t head = 0, tail_c = 0;  // entries pushed so far / last tail seen
-    uint32_t it0 = 0;               // global index of the current block's first tile
-    uint32_t mine = 0;              // tiles this warp has read (phase of its accumulator stage)
-    long long st_full = 0, st_ready = 0, st_acc = 0, st_push = 0, st_rel = 0, st_tile = 0;  // instrumented build only
-    unsigned long long st_npush = 0;
-    for (int b = 0; b < nqb; ++b, it0 += (uint32_t)p.ntiles) {
+    uint32_t it = 0;                // global tile index: stage it & 1, phase (it >> 1) & 1
+    unsigned long long st_npush = 0;  // instrumented build only
+    for (int b = 0; b < nqb; ++b) {
       const int qb = (int)blockIdx.x + b * (int)gridDim.x;
       {  // the selection warp of my rows has flushed the previous block and reset lists and thresholds
-        const long long c0 = DBG ? clock64() : 0;
         uint32_t spins = 0;
         while (ptx::ld_acquire_shared(c_ready) != (uint32_t)(b + 1)) {
           __nanosleep(64);
           B200_SPIN_GUARD(spins);
         }
-        if (DBG) st_ready += clock64() - c0;
       }
-      for (int t = (int)((g + it0) & 1); t < p.ntiles; t += 2, ++mine) {
-        const float4 nl = __ldg(nlo4 + t);  // norm bounds of the tile's four chunks
-        const long long c1 = DBG ? clock64() : 0;
-        mbar_wait_lean(bar_f, mine & 1);
-        const long long c6 = DBG ? clock64() : 0;
-        if (DBG) st_acc += c6 - c1;
-        ptx::tc_fence_after();
-        if ((p.mode & 3) != 2) {
-          // per-chunk thresholds on the raw dot: dot + nlo < tau, widened by the rounding of both sides
-          // (an inexact test here only adds queue entries; the selection warp decides)
-          const float tau = ptx::ld_volatile_shared_f32(my_tau);
-          const float at = fabsf(tau) * 4.76837158e-7f;
-          float v[32];
-          // one queue push: the flagged lanes of `fm_` (at most QE of them) take consecutive slots
-#define B200_PUSH(fm_, cc, nlc)                                                                      \
+      const float2* nlp = reinterpret_cast<const float2*>(p.nlo) + g;  // my two chunks' norm bounds of tile 0
+      float v[32];
+      bool pending = false;  // entries stored but not yet published (warp-uniform)
+      // Queue push in two steps.  STORE: the flagged lanes of `fm_` (at most QE of them) take
+      // consecutive slots and write their 32 values; PUBLISH: the new head becomes visible to the
+      // selection warp.  The first chunk is only stored before the accumulator goes back to the MMA
+      // issuers; it is published after the release.
+#define B200_PUBLISH()                                                                               \
   do {                                                                                               \
-    const long long c3_ = DBG ? clock64() : 0;                                                       \
+    if (pending) {                                                                                   \
+      __syncwarp();                                                                                  \
+      if (lane == 0) ptx::st_release_shared(a_head, head);                                           \
+      pending = false;                                                                               \
+    }                                                                                                \
+  } while (0)
+#define B200_STORE(fm_, col_, nlc)                                                                   \
+  do {                                                                                               \
     const uint32_t nadd_ = __popc(fm_);                                                              \
     if (head + nadd_ - tail_c > (uint32_t)QE) {                                                      \
+      B200_PUBLISH(); /* the selection warp must see what is stored before this warp waits for it */ \
       uint32_t spins_ = 0;                                                                           \
       do {                                                                                           \
-        tail_c = ptx::ld_acquire_shared(c_tail);                                                     \
-        B200_SPIN_GUARD(spins_);                                        \
-      } while (head + nadd_ - tail_c > (uint32_t)QE);                                                \
+        tail_c = ptx::ld_acquire_shared(a_tail);                                                     \
+        if (head + nadd_ - tail_c <= (uint32_t)QE) break;                                            \
+        __nanosleep(100);                                                                            \
+        B200_SPIN_GUARD(spins_);                                                                     \
+      } while (true);                                                                                \
     }                                                                                                \
     if ((fm_ >> lane) & 1u) {                                                                        \
       const uint32_t slot_ = (head + __popc(fm_ & lt_mask)) & (uint32_t)(QE - 1);                    \
       float4* dst_ = reinterpret_cast<float4*>(myq + (size_t)slot_ * QWORDS);                        \
       _Pragma("unroll") for (int i = 0; i < 8; ++i)                                                  \
         dst_[i] = make_float4(v[4 * i], v[4 * i + 1], v[4 * i + 2], v[4 * i + 3]);                   \
-      reinterpret_cast<int4*>(dst_)[8] = make_int4(lane, t * TILE + (cc) * 32, __float_as_int(nlc), 0); \
+      reinterpret_cast<int4*>(dst_)[8] = make_int4(lane, col_, __float_as_int(nlc), 0);              \
     }                                                                                                \
     head += nadd_;                                                                                   \
-    __syncwarp();                                                                                    \
-    const long long c4_ = DBG ? clock64() : 0;                                                       \
-    if (lane == 0) ptx::st_release_shared(c_head, head);                                             \
-    if (DBG) {                                                                                       \
-      const long long c5_ = clock64();                                                               \
-      st_push += c5_ - c3_;                                                                          \
-      st_rel += c5_ - c4_;                                                                           \
-      ++st_npush;                                                                                    \
-    }                                                                                                \
+    pending = true;                                                                                  \
+    if (DBG) ++st_npush;                                                                             \
   } while (0)
-#define B200_CHUNK(cc, nlc)                                                                          \
+      // one 32-column chunk in v: dump (tests), reduce to its minimum, compare with the row's threshold
+      // on the raw dot -- dot + nlo < tau, widened by the rounding of both sides (an inexact test here
+      // only adds queue entries; the selection warp decides) -- and store the flagged rows' values
+#define B200_CHUNK(col_, nlc)                                                                        \
   do {                                                                                               \
     if (DBG) {                                                                                       \
       if (p.dbg) {                                                                                   \
-        float* o = p.dbg + ((size_t)qb * ROWS + row) * ((size_t)p.ntiles * TILE) + (size_t)t * TILE + (cc) * 32; \
+        float* o = p.dbg + ((size_t)qb * ROWS + row) * ((size_t)p.ntiles * TILE) + (col_);           \
         _Pragma("unroll") for (int i = 0; i < 32; ++i) o[i] = v[i];                                  \
       }                                                                                              \
     }                                                                                                \
     const bool fl_ = chunk_min(v) < (tau - (nlc)) + fmaf(nlc, 4.76837158e-7f, at);                   \
-    const unsigned fa_ = (p.mode & 3) == 0 ? __ballot_sync(0xffffffffu, fl_) : 0u;                   \
+    const unsigned fa_ = (!DBG || (p.mode & 3) == 0) ? __ballot_sync(0xffffffffu, fl_) : 0u;         \
     if (fa_) {                                                                                       \
       if (QE >= 32) {                                                                                \
-        B200_PUSH(fa_, cc, nlc);                                                                     \
+        B200_STORE(fa_, col_, nlc);                                                                  \
       } else {                                                                                       \
         const unsigned lo_ = fa_ & 0xffffu, hi_ = fa_ & 0xffff0000u;                                 \
-        if (lo_) B200_PUSH(lo_, cc, nlc);                                                            \
-        if (hi_) B200_PUSH(hi_, cc, nlc);                                                            \
+        if (lo_) B200_STORE(lo_, col_, nlc);                                                         \
+        if (hi_) B200_STORE(hi_, col_, nlc);                                                         \
       }                                                                                              \
     }                                                                                                \
   } while (0)
-          ptx::tmem_ld32(t_lane, v);
-          ptx::tmem_ld_wait();
-          B200_CHUNK(0, nl.x);
-          ptx::tmem_ld32(t_lane + 32, v);
-          ptx::tmem_ld_wait();
-          B200_CHUNK(1, nl.y);
-          ptx::tmem_ld32(t_lane + 64, v);
-          ptx::tmem_ld_wait();
-          B200_CHUNK(2, nl.z);
-          ptx::tmem_ld32(t_lane + 96, v);
-          ptx::tmem_ld_wait();
-          // every column of the tile has been read: hand the accumulator back before the last chunk
-          ptx::tc_fence_before();
-          __syncwarp();
-          if (lane == 0) ptx::mbar_arrive(bar_e);
-          B200_CHUNK(3, nl.w);
-          if (DBG) st_tile += clock64() - c6;
-#undef B200_CHUNK
-#undef B200_PUSH
-        } else {
-          ptx::tc_fence_before();
-          __syncwarp();
-          if (lane == 0) ptx::mbar_arrive(bar_e);
-        }
+      // one tile on accumulator stage A: wait, two TMEM reads, release, filter
+#define B200_TILE(A, PH)                                                                             \
+  do {                                                                                               \
+    const float2 nl = __ldg(nlp);                                                                    \
+    nlp += 2;                                                                                        \
+    mbar_wait_suspend(a_bf + (A) * 16, (PH));                                                  \
+    ptx::tc_fence_after();                                                                           \
+    if (!DBG || (p.mode & 3) != 2) {                                                                 \
+      const float tau = ptx::ld_volatile_shared_f32(a_tau);                                         \
+      const float at = fabsf(tau) * 4.76837158e-7f;                                                  \
+      ptx::tmem_ld32(a_tacc + (A) * ACC_COLS, v);                                                      \
+      ptx::tmem_ld_wait();                                                                           \
+      B200_CHUNK(col, nl.x);                                                                         \
+      ptx::tmem_ld32(a_tacc + (A) * ACC_COLS + 32, v);                                               \
+      ptx::tmem_ld_wait();                                                                           \
+      /* my columns of the tile have been read: hand the accumulator back before the last chunk */   \
+      ptx::tc_fence_before();                                                                        \
+      __syncwarp();                                                                                  \
+      if (lane == 0) ptx::mbar_arrive(a_be + (A) * 16);                                        \
+      B200_CHUNK(col + 32, nl.y);                                                                    \
+      B200_PUBLISH();                                                                                \
+    } else {                                                                                         \
+      ptx::tc_fence_before();                                                                        \
+      __syncwarp();                                                                                  \
+      if (lane == 0) ptx::mbar_arrive(a_be + (A) * 16);                                        \
+    }                                                                                                \
+    col += TILE;                                                                                     \
+  } while (0)
+      int col = colg;  // first of my columns in the current tile
+      // (one instance of the tile step with run-time stage selects: instantiating it per stage made the
+      // loop four times as long and cost more in instruction fetch than the selects do)
+      for (int t = 0; t < p.ntiles; ++t, ++it) {
+        const uint32_t a = it & 1;
+        B200_TILE(a, (it >> 1) & 1);
       }
+#undef B200_TILE
+#undef B200_CHUNK
+#undef B200_STORE
+#undef B200_PUBLISH
       __syncwarp();
       if (lane == 0) ptx::st_release_shared(c_done, (uint32_t)(b + 1));  // everything of this block is queued
     }
-    if (DBG && p.stats && lane == 0) {
-      atomicAdd(p.stats + 5, (unsigned long long)st_full);
-      atomicAdd(p.stats + 6, (unsigned long long)st_ready);
-      atomicAdd(p.stats + 7, (unsigned long long)st_acc);
-      atomicAdd(p.stats + 8, (unsigned long long)st_push);
-      atomicAdd(p.stats + 9, (unsigned long long)st_rel);
-      atomicAdd(p.stats + 10, (unsigned long long)st_tile);
-      atomicAdd(p.stats + 11, st_npush);
-    }
+    if (DBG && p.stats && lane == 0) atomicAdd(p.stats + 11, st_npush);
   } else {
     // ===================== selection: queue entries -> sorted candidate lists ======================
     const int c = warp - 2 * E;  // row block: rows c*32 .. c*32+31, fed by epilogue warps c and E + c
@@ -681,18 +712,36 @@ __global__ void __launch_bounds__((HALVES * 12 + 3) * 32, 1) knn_tc_kernel(const
       tau0[lane] = CUDART_INF_F;
       __syncwarp();
       if (lane == 0) ptx::st_release_shared(c_ready, (uint32_t)(b + 1));
-      uint32_t spins = 0;
+      uint32_t spins = 0, nap = 32;
+      uint32_t a_heads = ptx::smem_u32(&q_head[c * 2]), a_tails = ptx::smem_u32(&q_tail[c * 2]);
+      uint32_t a_dones = ptx::smem_u32(&q_done[c * 2]);
+      asm volatile("" : "+r"(a_heads));
+      asm volatile("" : "+r"(a_tails));
+      asm volatile("" : "+r"(a_dones));
       for (;;) {
-        bool any = false;
+        // idle probe: both heads in one 8-byte load (the acquire load follows only when there is work)
+        const uint2 hh = ptx::ld_volatile_shared_v2(a_heads);
+        if (hh.x == tail[0] && hh.y == tail[1]) {
+          // both queues empty: finished once both epilogue warps have queued everything (done is
+          // written after the last head update, so re-reading the heads after it is conclusive)
+          const uint2 dd = ptx::ld_volatile_shared_v2(a_dones);
+          if (dd.x == (uint32_t)(b + 1) && dd.y == (uint32_t)(b + 1)) {
+            if (ptx::ld_acquire_shared(a_heads) == tail[0] && ptx::ld_acquire_shared(a_heads + 4) == tail[1]) break;
+            continue;
+          }
+          __nanosleep(nap);  // back off: an entry then waits at most ~0.3 us, and the queues hold 16
+          if (nap < 256) nap *= 2;
+          B200_SPIN_GUARD(spins);
+          continue;
+        }
+        spins = 0;
+        nap = 32;
 #pragma unroll
         for (int g = 0; g < 2; ++g) {
-          const int w = g * E + c;
-          const float* myq = que + (size_t)w * QE * QWORDS;
-          const uint32_t c_head = ptx::smem_u32(&ctl[w * 4 + 0]), c_tail = ptx::smem_u32(&ctl[w * 4 + 1]);
-          const uint32_t h = ptx::ld_acquire_shared(c_head);
+          const float* myq = que + (size_t)(g * E + c) * QE * QWORDS;
+          const uint32_t h = ptx::ld_acquire_shared(a_heads + 4 * g);
           uint32_t tl = tail[g];
-          any = any || tl != h;
-          const long long c0 = (DBG && tl != h) ? clock64() : 0;
+          const long long c0 = (DBG && p.stats && tl != h) ? clock64() : 0;
           while (tl != h) {
             const float* e = myq + (size_t)(tl & (uint32_t)(QE - 1)) * QWORDS;
             const int4 meta = *reinterpret_cast<const int4*>(e + 32);
@@ -703,7 +752,7 @@ __global__ void __launch_bounds__((HALVES * 12 + 3) * 32, 1) knn_tc_kernel(const
             const bool ok = s < tau && base + lane < p.ncols;
             const unsigned m = __ballot_sync(0xffffffffu, ok);
             // the entry's words are in registers (the ballot consumed them): the slot may be refilled
-            if (lane == 0) ptx::st_volatile_shared_u32(c_tail, tl);
+            if (lane == 0) ptx::st_volatile_shared_u32(a_tails + 4 * g, tl);
             if (DBG) {
               ++st_ev;
               st_hit += m != 0;
@@ -718,21 +767,6 @@ __global__ void __launch_bounds__((HALVES * 12 + 3) * 32, 1) knn_tc_kernel(const
           if (DBG && c0) st_busy += clock64() - c0;
           tail[g] = tl;
         }
-        if (any) {
-          spins = 0;
-          continue;
-        }
-        // both queues looked empty: finished once both epilogue warps have queued everything
-        // (done is written after the last head update, so re-reading the heads after it is conclusive)
-        if (ptx::ld_acquire_shared(ptx::smem_u32(&ctl[c * 4 + 2])) == (uint32_t)(b + 1) &&
-            ptx::ld_acquire_shared(ptx::smem_u32(&ctl[(E + c) * 4 + 2])) == (uint32_t)(b + 1)) {
-          if (ptx::ld_acquire_shared(ptx::smem_u32(&ctl[c * 4 + 0])) == tail[0] &&
-              ptx::ld_acquire_shared(ptx::smem_u32(&ctl[(E + c) * 4 + 0])) == tail[1])
-            break;
-          continue;
-        }
-        __nanosleep(32);
-        B200_SPIN_GUARD(spins);
       }
       // ---- flush this block's candidate lists (coalesced, one row at a time)
       const int64_t q0 = (int64_t)qb * ROWS + c * 32;
@@ -1089,6 +1123,7 @@ int knn_tc(b200_model* m, const double* z_dev, int64_t q, int k, int64_t self_of
   kp.qblocks = qblocks;
   kp.slots = cfg.slots;
   kp.qent = cfg.qent;
+  kp.parts = m->tc_parts;
   kp.keep = cfg.keep;
   kp.mode = m->tc_mode;
   kp.cand_idx = m->cand.as<int32_t>();
@@ -1100,7 +1135,7 @@ int knn_tc(b200_model* m, const double* z_dev, int64_t q, int k, int64_t self_of
     kp.stats = reinterpret_cast<unsigned long long*>(m->flags.as<char>() + 64);
     B200_CUDA(cudaMemsetAsync(kp.stats, 0, 128, st));
   }
-  const bool dg = dbg != nullptr || kp.stats != nullptr;
+  const bool dg = dbg != nullptr || kp.stats != nullptr || m->tc_mode != 0;  // ceilings run in the instrumented build
   auto launch_one = [&](const tc::KParams& kq, cudaStream_t s_) -> int {
     if (cfg.u == 1 && cfg.halves == 2) return launch_tc<1, 2>(m, kq, cfg, dg, s_);
     if (cfg.u == 1 && cfg.halves == 1) return launch_tc<1, 1>(m, kq, cfg, dg, s_);

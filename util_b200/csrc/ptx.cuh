@@ -226,6 +226,11 @@ __device__ __forceinline__ float ld_volatile_shared_f32(uint32_t addr) {
   asm volatile("ld.volatile.shared.f32 %0, [%1];" : "=f"(v) : "r"(addr) : "memory");
   return v;
 }
+__device__ __forceinline__ uint2 ld_volatile_shared_v2(uint32_t addr) {  // addr 8-byte aligned
+  uint2 v;
+  asm volatile("ld.volatile.shared.v2.u32 {%0, %1}, [%2];" : "=r"(v.x), "=r"(v.y) : "r"(addr) : "memory");
+  return v;
+}
 __device__ __forceinline__ void st_volatile_shared_u32(uint32_t addr, uint32_t v) {
   asm volatile("st.volatile.shared.u32 [%0], %1;" ::"r"(addr), "r"(v) : "memory");
 }
