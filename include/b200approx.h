@@ -56,6 +56,12 @@ int b200_destroy(b200_model* m);
 int b200_set_option(b200_model* m, const char* key, double value);
 int b200_get_stat(b200_model* m, const char* key, double* value);
 
+/* Response values y (n,r) of the fitted points, kept on the device: what WeightedApproximator.fit
+ * stores as self.y (base.py:127-143).  The predict entry points below then form the weighted sums
+ * (base.py:159-169) when called with y == NULL and out != NULL, without sending y again; a call that
+ * passes y uses (and keeps) that y instead.  y == NULL here forgets the stored values. */
+int b200_set_values(b200_model* m, const double* y, int32_t r);
+
 /* k nearest fitted points of each query, ascending by (squared distance, index):
  * the batched form of `self.tree.query(pt[None,:], k=..., return_distance=False)`
  * (nearest_neighbor/__init__.py:75-76).  idx (q,k); d2 (q,k) squared distances
@@ -111,12 +117,18 @@ int b200_shepmod_predict(b200_model* m, const double* z, int64_t q, int32_t cap,
                          double* wts, int32_t* cnt, int32_t* ier, const double* y, int32_t r,
                          double* out);
 
-/* LSHEP non-robust fit (linear_shepard.f95:23-134,177; DGELSS replaced by a
- * batched Householder QR, rank-deficient nodes flagged IER=2): f (n,r) response
- * columns; a (r,n,d) gradients, rw (n) radii BEFORE the wrapper's `radius`
- * multiplier (linear_shepard/__init__.py:55); *ier 0/1/2. */
+/* LSHEP non-robust fit (linear_shepard.f95:23-134,177; DGELSS replaced by a batched Householder QR,
+ * and by a Jacobi SVD with DGELSS's singular-value cut -- minimum-norm solution, IER=2 -- for nodes
+ * at or near rank deficiency): f (n,r) response columns; a (r,n,d) gradients, rw (n) radii BEFORE
+ * the wrapper's `radius` multiplier (linear_shepard/__init__.py:55); *ier 0/1/2. */
 int b200_lshep_fit(b200_model* m, const double* f, int32_t r, double* a, double* rw,
                    int32_t* ier);
+/* LSHEP with RLSHEP present -- the robust fit the Fortran module exports but the shipped wrapper never
+ * reaches (linear_shepard.f95:136-175 with IRLS :181-282, MAD :284-308, QUANTILE :310-335): unit weights,
+ * then Huber and Tukey-bisquare re-weighted least squares (five iterations each), RW cut at the first
+ * neighbour whose final weight is below 0.8.  One response column f (n); a (n,d), rw (n); *ier 0/1/2/3.
+ * b200_lshep_predict then evaluates this fit. */
+int b200_lshep_fit_robust(b200_model* m, const double* f, double* a, double* rw, int32_t* ier);
 /* LSHEPVAL over a batch (linear_shepard.f95:365-472) with the radii scaled by
  * `radius`: out (q,r), ier (q,r) 0/1/2. */
 int b200_lshep_predict(b200_model* m, double radius, const double* z, int64_t q, double* out,

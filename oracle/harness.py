@@ -22,7 +22,7 @@ def build(force=False):
     """Compile liboracle.so with the recipe in oracle/Makefile."""
     so = os.path.join(_HERE, "liboracle.so")
     srcs = [os.path.join(_HERE, f) for f in
-            ("oracle.cpp", "oracle_lshep_voronoi.cpp", "oracle_common.h", "Makefile")]
+            ("oracle.cpp", "oracle_lshep_voronoi.cpp", "oracle_robust.cpp", "oracle_common.h", "Makefile")]
     if force or not os.path.exists(so) or any(os.path.getmtime(s) > os.path.getmtime(so) for s in srcs):
         subprocess.check_call(["make", "-C", _HERE, "-s", "-B", "liboracle.so"])
     return so
@@ -124,6 +124,33 @@ def lshep_fit(x, f):
     ier = lib().orc_lshep_fit(_p(x), C.c_int64(n), d, _p(f), _p(a), _p(rw), _p(rank, C.c_int32),
                               C.c_void_p(_dgelss_ptr()))
     return a, rw, ier, rank
+
+
+def quantile(a, k):
+    """QUANTILE (linear_shepard.f95:310-335): the k-th smallest (1-based) element."""
+    a = _f64(a)
+    lib().orc_quantile.restype = C.c_double
+    return lib().orc_quantile(_p(a), len(a), int(k))
+
+
+def mad(res):
+    """MAD (linear_shepard.f95:284-308)."""
+    res = _f64(res)
+    lib().orc_mad.restype = C.c_double
+    return lib().orc_mad(_p(res), len(res))
+
+
+def lshep_fit_robust(x, f):
+    """LSHEP with RLSHEP present (linear_shepard.f95:136-175): (a (n,d), rw (n), ier, omega (n,np))."""
+    x, f = _f64(x), _f64(f)
+    n, d = x.shape
+    npn = min(n - 1, (3 * d + 1) // 2)
+    a = np.ones((n, d))
+    rw = np.ones(n)
+    om = np.ones((n, npn))
+    ier = lib().orc_lshep_fit_robust(_p(x), C.c_int64(n), d, _p(f), _p(a), _p(rw), _p(om),
+                                     C.c_void_p(_dgelss_ptr()))
+    return a, rw, ier, om
 
 
 def lshep_predict(x, f, a, rw, z):

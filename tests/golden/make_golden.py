@@ -118,6 +118,41 @@ def gen_wrappers():
              unique_indices=b.unique_indices, split=s(zs))
 
 
+def gen_auto():
+    """nearest_neighbor.auto (nearest_neighbor/__init__.py:93-132) of the reference on seeded inputs; the
+    rows it sampled are recorded (util.random.random_range wrapped) so that the test can hand them in."""
+    import random
+    import util.random as ur
+    import util.approximate.nearest_neighbor as rnn
+    real = ur.random_range
+    drawn = []
+
+    def recording(*a, **k):
+        for v in real(*a, **k):
+            drawn.append(v)
+            yield v
+    ur.random_range = recording
+    cases = [dict(n=300, d=2, kw={}), dict(n=2000, d=5, kw=dict(mean=False)), dict(n=2500, d=3, kw=dict(k_step=2)),
+             dict(n=900, d=4, kw=dict(samples=40)), dict(n=6000, d=3, kw=dict(samples=30)),
+             dict(n=40000, d=6, kw=dict(samples=50, mean=False))]  # the last one draws rows with the LCG walk
+    # (a caller-supplied max_k cannot be pinned: the reference only imports log2 when max_k is None and
+    # raises UnboundLocalError at :112 otherwise)
+    out = {}
+    for i, c in enumerate(cases):
+        x = np.random.default_rng(100 + i).random((c["n"], c["d"]))
+        y = fun(x) + (0.3 * np.random.default_rng(200 + i).standard_normal(c["n"]) if i % 2 else 0.0)
+        random.seed(i)
+        drawn.clear()
+        k = rnn.auto(x, y, **c["kw"])
+        out[f"k{i}"] = k
+        out[f"rows{i}"] = np.array(drawn, dtype=np.int64)
+        out[f"x_sum{i}"] = x.sum()
+        print("auto", i, c, "->", k, len(drawn))
+    ur.random_range = real
+    np.savez_compressed(os.path.join(HERE, "auto_k.npz"), **out)
+
+
 if __name__ == "__main__":
     main()
     gen_wrappers()
+    gen_auto()

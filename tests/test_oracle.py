@@ -140,3 +140,30 @@ def test_oracle_eval_mesh_agrees_with_predict(oracle):
     for p, row in zip(z, mesh):
         w, e = oracle.voronoi_predict(x, p)
         assert e == 0 and np.allclose(row, w, rtol=1e-10, atol=1e-13)
+
+
+def test_oracle_robust_lshep_invariants(oracle):
+    """Robust LSHEP pieces (linear_shepard.f95:136-175, 181-335) -- parity unpinned, so the invariants the
+    source implies: QUANTILE is the k-th order statistic (with ties), MAD = median |r - median r| / 0.6745,
+    IRLS weights lie in [0, 1], gross outliers get small weights and shrink RW, clean linear data keeps the
+    plane's gradient."""
+    rng = np.random.default_rng(0)
+    for a in (rng.standard_normal(15), np.round(rng.standard_normal(20), 1), np.zeros(7)):
+        for k in range(1, len(a) + 1):
+            assert oracle.quantile(a, k) == np.sort(a)[k - 1]
+    for n in (15, 16, 5):
+        r = rng.standard_normal(n)
+        assert oracle.mad(r) == pytest.approx(np.median(np.abs(r - np.median(r))) / 0.6745, rel=1e-15)
+    x = rng.random((600, 3))
+    g = np.array([1.0, 2.0, -3.0])
+    f = x @ g + 0.5
+    f[::17] += 5.0
+    a, rw, ier, om = oracle.lshep_fit_robust(x, f)
+    a0, rw0, _, _ = oracle.lshep_fit(x, f)
+    assert om.min() >= 0.0 and om.max() <= 1.0
+    clean = np.ones(600, dtype=bool)
+    clean[::17] = False
+    off = lambda grads: (np.abs(grads[clean] - g).max(axis=1) > 1e-6).mean()
+    assert off(a0) > 0.15                                               # the plain fit is pulled by outlier neighbours
+    assert off(a) < 0.75 * off(a0)                                      # the robust fit less often (NP = 5 leaves little redundancy)
+    assert np.all(rw <= rw0 + 1e-15) and (rw < rw0).mean() > 0.1        # RW is cut at down-weighted neighbours

@@ -29,6 +29,7 @@ _SIGNATURES = {
     "b200_destroy": (C.c_int, [C.c_void_p]),
     "b200_set_option": (C.c_int, [C.c_void_p, C.c_char_p, C.c_double]),
     "b200_get_stat": (C.c_int, [C.c_void_p, C.c_char_p, c_dp]),
+    "b200_set_values": (C.c_int, [C.c_void_p, c_dp, C.c_int32]),
     "b200_knn": (C.c_int, [C.c_void_p, c_dp, C.c_int64, C.c_int32, C.c_int64, c_i64p, c_dp]),
     "b200_nn_predict": (C.c_int, [C.c_void_p, c_dp, C.c_int64, C.c_int32, C.c_int32, c_dp, C.c_int32,
                                   c_i64p, c_dp, c_i32p, c_i32p, c_dp]),
@@ -40,6 +41,7 @@ _SIGNATURES = {
     "b200_shepmod_predict": (C.c_int, [C.c_void_p, c_dp, C.c_int64, C.c_int32, c_i64p, c_dp, c_i32p,
                                        c_i32p, c_dp, C.c_int32, c_dp]),
     "b200_lshep_fit": (C.c_int, [C.c_void_p, c_dp, C.c_int32, c_dp, c_dp, c_i32p]),
+    "b200_lshep_fit_robust": (C.c_int, [C.c_void_p, c_dp, c_dp, c_dp, c_i32p]),
     "b200_lshep_predict": (C.c_int, [C.c_void_p, C.c_double, c_dp, C.c_int64, c_dp, c_i32p]),
     "b200_knn_dev": (C.c_int, [C.c_void_p, C.c_void_p, C.c_int64, C.c_int32, C.c_int64, C.c_void_p,
                                C.c_void_p, C.c_void_p]),
@@ -128,6 +130,21 @@ class Model:
         check(lib().b200_get_stat(self._h, key.encode(), C.byref(v)))
         return v.value
 
+    def set_values(self, y):
+        """Keep the response values (n,) or (n,r) on the device; predict calls made with y=True use them."""
+        y = f64(y).reshape(self.n, -1)
+        check(lib().b200_set_values(self._h, ptr(y), y.shape[1]))
+        self.values_r = y.shape[1]
+
+    def _y_args(self, y, q):
+        """(host y or None, r, out): y=True selects the values left on the device by set_values()."""
+        if y is None:
+            return None, 0, None
+        if y is True:
+            return None, self.values_r, np.empty((q, self.values_r))
+        y = f64(y).reshape(self.n, -1)
+        return y, y.shape[1], np.empty((q, y.shape[1]))
+
     def knn(self, z, k, self_offset=-1, want_d2=True):
         z = f64(z)
         q = z.shape[0]
@@ -146,12 +163,7 @@ class Model:
             wts = np.empty((q, k), dtype=np.float64)
         cnt = np.empty(q, dtype=np.int32)
         err = np.empty(q, dtype=np.int32)
-        out = None
-        r = 0
-        if y is not None:
-            y = f64(y).reshape(self.n, -1)
-            r = y.shape[1]
-            out = np.empty((q, r), dtype=np.float64)
+        y, r, out = self._y_args(y, q)
         check(lib().b200_nn_predict(self._h, ptr(z), q, k, method, ptr(y), r, ptr(ids, c_i64p), ptr(wts),
                                     ptr(cnt, c_i32p), ptr(err, c_i32p), ptr(out)))
         return ids, wts, cnt, err, out
@@ -169,12 +181,7 @@ class Model:
         z = f64(z)
         q = z.shape[0]
         wts = np.empty((q, self.n)) if want_weights else None
-        out = None
-        r = 0
-        if y is not None:
-            y = f64(y).reshape(self.n, -1)
-            r = y.shape[1]
-            out = np.empty((q, r))
+        y, r, out = self._y_args(y, q)
         check(lib().b200_shepard_predict(self._h, ptr(z), q, ptr(y), r, ptr(wts), ptr(out)))
         return wts, out
 
@@ -189,14 +196,10 @@ class Model:
         on the device (returned ids/wts are then None, `cap` still grows until the longest list fits)."""
         z = f64(z)
         q = z.shape[0]
-        r = 0
-        out = None
-        if y is not None:
-            y = f64(y).reshape(self.n, -1)
-            r = y.shape[1]
-            out = np.empty((q, r))
+        want_sums = y is not None
+        y, r, out = self._y_args(y, q)
         while True:
-            keep = want_weights or y is None
+            keep = want_weights or not want_sums
             ids = np.empty((q, cap), dtype=np.int64) if keep else None
             wts = np.empty((q, cap)) if keep else None
             cnt = np.empty(q, dtype=np.int32)
@@ -214,12 +217,7 @@ class Model:
         index) and weights; the list capacity grows until the longest fits."""
         z = f64(z)
         q = z.shape[0]
-        r = 0
-        out = None
-        if y is not None:
-            y = f64(y).reshape(self.n, -1)
-            r = y.shape[1]
-            out = np.empty((q, r))
+        y, r, out = self._y_args(y, q)
         cap = max(1, min(cap, self.n))
         while True:
             ids = np.empty((q, cap), dtype=np.int64)
@@ -233,13 +231,18 @@ class Model:
                 return ids, wts, cnt, err, out
             cap = min(self.n, max(2 * cap, mx))
 
-    def lshep_fit(self, f):
+    def lshep_fit(self, f, robust=False):
         f = f64(f).reshape(self.n, -1)
         r = f.shape[1]
         a = np.empty((r, self.n, self.d))
         rw = np.empty(self.n)
         ier = C.c_int32(0)
-        check(lib().b200_lshep_fit(self._h, ptr(f), r, ptr(a), ptr(rw), C.byref(ier)))
+        if robust:
+            if r != 1:
+                raise ValueError("the robust LSHEP fit takes one response column (its radii depend on the response)")
+            check(lib().b200_lshep_fit_robust(self._h, ptr(f), ptr(a), ptr(rw), C.byref(ier)))
+        else:
+            check(lib().b200_lshep_fit(self._h, ptr(f), r, ptr(a), ptr(rw), C.byref(ier)))
         return a, rw, ier.value
 
     def lshep_predict(self, z, radius, r):

@@ -116,7 +116,12 @@ class WeightedApproximator(Approximator):
             if (not self.classifier) and isinstance(y, np.ndarray) and y.ndim == 1 \
                and y.dtype == np.float64 and len(y) == len(x):
                 self._y_numeric = y
-        return self._fit(x.copy(), **kwargs)
+        result = self._fit(x.copy(), **kwargs)
+        # numeric responses go to the device once, here, not with every predict call
+        model = getattr(self, "model", None)
+        if self._y_numeric is not None and model is not None and hasattr(model, "set_values"):
+            model.set_values(self._y_numeric)
+        return result
 
     def _predict_values(self, x, *args, **kwargs):
         """GPU weighted sums for numeric y; None when the subclass has no fused path."""

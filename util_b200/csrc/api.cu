@@ -78,6 +78,25 @@ int upload_y(b200_model* m, const double* y, int r) {
   }
   B200_TRY(m->y.reserve((size_t)m->n * r * 8));
   B200_CUDA(cudaMemcpy(m->y.p, y, (size_t)m->n * r * 8, cudaMemcpyHostToDevice));
+  m->y_r = r;
+  return 0;
+}
+
+// Response values of a predict call: the caller's y (uploaded now), or -- y == NULL with an output
+// buffer -- the values left on the device by b200_set_values.  *have: weighted sums are wanted.
+int resolve_y(b200_model* m, const double* y, int32_t* r, bool want_out, bool* have) {
+  *have = false;
+  if (y) {
+    B200_TRY(upload_y(m, y, *r));
+    *have = true;
+  } else if (want_out) {
+    if (m->y_r < 1) {
+      set_error("no response values: pass y or call b200_set_values first");
+      return 1;
+    }
+    *r = m->y_r;
+    *have = true;
+  }
   return 0;
 }
 
@@ -139,26 +158,31 @@ int b200_create(const double* x, int64_t n, int32_t d, int32_t device, b200_mode
     return 1;
   }
   B200_CUDA(cudaSetDevice(device));
+  cudaDeviceProp prop;
+  B200_CUDA(cudaGetDeviceProperties(&prop, device));
+  if (prop.major != 10) {
+    set_error("device %d is sm_%d%d; this library is built for sm_100a only", device, prop.major, prop.minor);
+    return 2;
+  }
   b200_model* m = new b200_model();
   m->device = device;
   m->n = n;
   m->d = d;
-  cudaDeviceProp prop;
-  B200_CUDA(cudaGetDeviceProperties(&prop, device));
   m->sm_count = prop.multiProcessorCount;
-  if (prop.major != 10) {
-    set_error("device %d is sm_%d%d; this library is built for sm_100a only", device, prop.major, prop.minor);
-    delete m;
+  // any failure from here on releases what was created (b200_destroy copes with a partly built model)
+  cudaError_t ce = cudaMalloc(&m->x, (size_t)n * d * 8);
+  if (ce == cudaSuccess) ce = cudaMemcpy(m->x, x, (size_t)n * d * 8, cudaMemcpyHostToDevice);
+  if (ce == cudaSuccess) ce = cudaEventCreate(&m->ev0);
+  if (ce == cudaSuccess) ce = cudaEventCreate(&m->ev1);
+  if (ce == cudaSuccess) ce = cudaEventCreate(&m->ev2);
+  if (ce == cudaSuccess) ce = cudaEventCreate(&m->ev3);
+  if (ce == cudaSuccess) ce = cudaStreamCreateWithFlags(&m->copy_stream, cudaStreamNonBlocking);
+  if (ce == cudaSuccess) ce = cudaEventCreateWithFlags(&m->ev_copy, cudaEventDisableTiming);
+  if (ce != cudaSuccess) {
+    set_error("b200_create: %s", cudaGetErrorString(ce));
+    b200_destroy(m);
     return 2;
   }
-  B200_CUDA(cudaMalloc(&m->x, (size_t)n * d * 8));
-  B200_CUDA(cudaMemcpy(m->x, x, (size_t)n * d * 8, cudaMemcpyHostToDevice));
-  B200_CUDA(cudaEventCreate(&m->ev0));
-  B200_CUDA(cudaEventCreate(&m->ev1));
-  B200_CUDA(cudaEventCreate(&m->ev2));
-  B200_CUDA(cudaEventCreate(&m->ev3));
-  B200_CUDA(cudaStreamCreateWithFlags(&m->copy_stream, cudaStreamNonBlocking));
-  B200_CUDA(cudaEventCreateWithFlags(&m->ev_copy, cudaEventDisableTiming));
   *out = m;
   return 0;
 }
@@ -237,11 +261,20 @@ int b200_get_stat(b200_model* m, const char* key, double* value) {
   return 0;
 }
 
+int b200_set_values(b200_model* m, const double* y, int32_t r) {
+  B200_TRY(use(m));
+  if (!y) {
+    m->y_r = 0;
+    return 0;
+  }
+  return upload_y(m, y, r);
+}
+
 int b200_knn(b200_model* m, const double* z, int64_t q, int32_t k, int64_t self_offset,
              int64_t* idx, double* d2) {
   B200_TRY(use(m));
-  if (q < 0 || !idx) {
-    set_error("b200_knn: bad arguments");
+  if (q < 0 || !idx || k < 1) {
+    set_error("b200_knn: bad arguments (q=%lld k=%d)", (long long)q, k);
     return 1;
   }
   if (q == 0) return 0;
@@ -260,19 +293,20 @@ int b200_nn_predict(b200_model* m, const double* z, int64_t q, int32_t k, int32_
                     const double* y, int32_t r, int64_t* ids, double* wts, int32_t* cnt,
                     int32_t* err, double* out) {
   B200_TRY(use(m));
-  if (q < 0 || (y && !out)) {
-    set_error("b200_nn_predict: bad arguments");
+  if (q < 0 || (y && !out) || k < 1) {
+    set_error("b200_nn_predict: bad arguments (q=%lld k=%d)", (long long)q, k);
     return 1;
   }
   if (q == 0) return 0;
-  B200_TRY(upload_y(m, y, r));
+  bool have_y = false;
+  B200_TRY(resolve_y(m, y, &r, out != nullptr, &have_y));
   B200_TRY(m->zq.reserve((size_t)q * m->d * 8 + 8));
   B200_TRY(m->idx32.reserve((size_t)q * k * 4));
   B200_TRY(m->d2.reserve((size_t)q * k * 8));
   B200_TRY(m->wts.reserve((size_t)q * k * 8));
   B200_TRY(m->cnt.reserve((size_t)q * 4));
   B200_TRY(m->err.reserve((size_t)q * 4));
-  if (y) B200_TRY(m->out.reserve((size_t)q * r * 8));
+  if (have_y) B200_TRY(m->out.reserve((size_t)q * r * 8));
   // Large batches from page-locked host memory go up in chunks on a copy stream, each chunk's
   // transfer under the previous chunk's kernels.  Chunks are whole waves of the tensor kernel's
   // persistent grid (sm_count blocks of 256 queries), a short first one so the kernels start early.
@@ -312,9 +346,9 @@ int b200_nn_predict(b200_model* m, const double* z, int64_t q, int32_t k, int32_
     }
     {
       Timer t(m, 0, &m->st.ms_weights);
-      B200_TRY(nn_weights(m, zc, hi - lo, k, method, ic, dc, y ? m->y.as<double>() : nullptr, r,
+      B200_TRY(nn_weights(m, zc, hi - lo, k, method, ic, dc, have_y ? m->y.as<double>() : nullptr, r,
                           m->wts.as<double>() + (size_t)lo * k, m->cnt.as<int32_t>() + lo, m->err.as<int32_t>() + lo,
-                          y ? m->out.as<double>() + (size_t)lo * r : nullptr, 0));
+                          have_y ? m->out.as<double>() + (size_t)lo * r : nullptr, 0));
     }
     done = hi;
   }
@@ -332,9 +366,9 @@ int b200_nn_predict(b200_model* m, const double* z, int64_t q, int32_t k, int32_
     }
     for (int32_t i : m->deferred) {
       B200_TRY(nn_weights(m, m->zq.as<double>() + (size_t)i * m->d, 1, k, method, m->idx32.as<int32_t>() + (size_t)i * k,
-                          m->d2.as<double>() + (size_t)i * k, y ? m->y.as<double>() : nullptr, r,
+                          m->d2.as<double>() + (size_t)i * k, have_y ? m->y.as<double>() : nullptr, r,
                           m->wts.as<double>() + (size_t)i * k, m->cnt.as<int32_t>() + i, m->err.as<int32_t>() + i,
-                          y ? m->out.as<double>() + (size_t)i * r : nullptr, 0));
+                          have_y ? m->out.as<double>() + (size_t)i * r : nullptr, 0));
     }
     m->deferred.clear();
   }
@@ -345,7 +379,7 @@ int b200_nn_predict(b200_model* m, const double* z, int64_t q, int32_t k, int32_
   if (wts) B200_CUDA(cudaMemcpy(wts, m->wts.p, (size_t)q * k * 8, cudaMemcpyDeviceToHost));
   if (cnt) B200_CUDA(cudaMemcpy(cnt, m->cnt.p, (size_t)q * 4, cudaMemcpyDeviceToHost));
   if (err) B200_CUDA(cudaMemcpy(err, m->err.p, (size_t)q * 4, cudaMemcpyDeviceToHost));
-  if (y) B200_CUDA(cudaMemcpy(out, m->out.p, (size_t)q * r * 8, cudaMemcpyDeviceToHost));
+  if (have_y) B200_CUDA(cudaMemcpy(out, m->out.p, (size_t)q * r * 8, cudaMemcpyDeviceToHost));
   B200_CUDA(cudaDeviceSynchronize());
   return 0;
 }
@@ -353,6 +387,10 @@ int b200_nn_predict(b200_model* m, const double* z, int64_t q, int32_t k, int32_
 int b200_knn_dev(b200_model* m, const double* z_dev, int64_t q, int32_t k, int64_t self_offset,
                  int32_t* idx_dev, double* d2_dev, void* stream) {
   B200_TRY(use(m));
+  if (q < 0 || k < 1 || !idx_dev) {
+    set_error("b200_knn_dev: bad arguments (q=%lld k=%d)", (long long)q, k);
+    return 1;
+  }
   if (q == 0) return 0;
   double* d2 = d2_dev;
   if (!d2) {
@@ -419,22 +457,23 @@ int b200_merge_topk_dev(int32_t device, const double* d2_parts, const int32_t* i
 int b200_shepard_predict(b200_model* m, const double* z, int64_t q, const double* y, int32_t r, double* wts,
                          double* out) {
   B200_TRY(use(m));
-  if (q < 0 || (y && !out) || (!y && !wts)) {
+  if (q < 0 || (y && !out) || (!out && !wts)) {
     set_error("b200_shepard_predict: bad arguments");
     return 1;
   }
   if (q == 0) return 0;
   B200_TRY(upload_queries(m, z, q));
-  B200_TRY(upload_y(m, y, r));
-  if (y) B200_TRY(m->out.reserve((size_t)q * r * 8));
+  bool have_y = false;
+  B200_TRY(resolve_y(m, y, &r, out != nullptr, &have_y));
+  if (have_y) B200_TRY(m->out.reserve((size_t)q * r * 8));
   if (wts) B200_TRY(m->wts.reserve((size_t)q * m->n * 8));
   {
     Timer t(m, 0, &m->st.ms_weights);
-    B200_TRY(shepard_all(m, m->zq.as<double>(), q, y ? m->y.as<double>() : nullptr, r,
-                         wts ? m->wts.as<double>() : nullptr, y ? m->out.as<double>() : nullptr, 0));
+    B200_TRY(shepard_all(m, m->zq.as<double>(), q, have_y ? m->y.as<double>() : nullptr, r,
+                         wts ? m->wts.as<double>() : nullptr, have_y ? m->out.as<double>() : nullptr, 0));
   }
   if (wts) B200_CUDA(cudaMemcpy(wts, m->wts.p, (size_t)q * m->n * 8, cudaMemcpyDeviceToHost));
-  if (y) B200_CUDA(cudaMemcpy(out, m->out.p, (size_t)q * r * 8, cudaMemcpyDeviceToHost));
+  if (have_y) B200_CUDA(cudaMemcpy(out, m->out.p, (size_t)q * r * 8, cudaMemcpyDeviceToHost));
   B200_CUDA(cudaDeviceSynchronize());
   return 0;
 }
@@ -487,23 +526,24 @@ int b200_voronoi_predict(b200_model* m, const double* z, int64_t q, int32_t cap,
   }
   if (q == 0) return 0;
   B200_TRY(upload_queries(m, z, q));
-  B200_TRY(upload_y(m, y, r));
+  bool have_y = false;
+  B200_TRY(resolve_y(m, y, &r, out != nullptr, &have_y));
   B200_TRY(m->idx32.reserve((size_t)q * cap * 4));
   B200_TRY(m->wts.reserve((size_t)q * cap * 8));
   B200_TRY(m->cnt.reserve((size_t)q * 4));
   B200_TRY(m->err.reserve((size_t)q * 4));
-  if (y) B200_TRY(m->out.reserve((size_t)q * r * 8));
+  if (have_y) B200_TRY(m->out.reserve((size_t)q * r * 8));
   {
     Timer t(m, 0, &m->st.ms_weights);
-    B200_TRY(voronoi_all(m, m->zq.as<double>(), q, cap, y ? m->y.as<double>() : nullptr, r, m->idx32.as<int32_t>(),
+    B200_TRY(voronoi_all(m, m->zq.as<double>(), q, cap, have_y ? m->y.as<double>() : nullptr, r, m->idx32.as<int32_t>(),
                          m->wts.as<double>(), m->cnt.as<int32_t>(), m->err.as<int32_t>(),
-                         y ? m->out.as<double>() : nullptr, 0));
+                         have_y ? m->out.as<double>() : nullptr, 0));
   }
   if (ids) B200_TRY(fetch_idx64(m, m->idx32.as<int32_t>(), q * cap, ids));
   if (wts) B200_CUDA(cudaMemcpy(wts, m->wts.p, (size_t)q * cap * 8, cudaMemcpyDeviceToHost));
   if (cnt) B200_CUDA(cudaMemcpy(cnt, m->cnt.p, (size_t)q * 4, cudaMemcpyDeviceToHost));
   if (err) B200_CUDA(cudaMemcpy(err, m->err.p, (size_t)q * 4, cudaMemcpyDeviceToHost));
-  if (y) B200_CUDA(cudaMemcpy(out, m->out.p, (size_t)q * r * 8, cudaMemcpyDeviceToHost));
+  if (have_y) B200_CUDA(cudaMemcpy(out, m->out.p, (size_t)q * r * 8, cudaMemcpyDeviceToHost));
   B200_CUDA(cudaDeviceSynchronize());
   return 0;
 }
@@ -512,34 +552,35 @@ int b200_shepmod_predict(b200_model* m, const double* z, int64_t q, int32_t cap,
                          double* wts, int32_t* cnt, int32_t* ier, const double* y, int32_t r,
                          double* out) {
   B200_TRY(use(m));
-  if (q < 0 || (y && !out)) {
-    set_error("b200_shepmod_predict: bad arguments");
+  if (q < 0 || (y && !out) || cap < 1) {
+    set_error("b200_shepmod_predict: bad arguments (q=%lld cap=%d)", (long long)q, cap);
     return 1;
   }
   if (q == 0) return 0;
   B200_TRY(upload_queries(m, z, q));
-  B200_TRY(upload_y(m, y, r));
+  bool have_y = false;
+  B200_TRY(resolve_y(m, y, &r, out != nullptr, &have_y));
   B200_TRY(m->idx32.reserve((size_t)q * cap * 4));
   B200_TRY(m->wts.reserve((size_t)q * cap * 8));
   B200_TRY(m->cnt.reserve((size_t)q * 4));
   B200_TRY(m->err.reserve((size_t)q * 4));
-  if (y) B200_TRY(m->out.reserve((size_t)q * r * 8));
+  if (have_y) B200_TRY(m->out.reserve((size_t)q * r * 8));
   {
     Timer t(m, 0, &m->st.ms_weights);
     B200_TRY(shepmod_predict(m, m->zq.as<double>(), q, cap, m->idx32.as<int32_t>(), m->wts.as<double>(),
-                             m->cnt.as<int32_t>(), m->err.as<int32_t>(), y ? m->y.as<double>() : nullptr,
-                             r, y ? m->out.as<double>() : nullptr, 0));
+                             m->cnt.as<int32_t>(), m->err.as<int32_t>(), have_y ? m->y.as<double>() : nullptr,
+                             r, have_y ? m->out.as<double>() : nullptr, 0));
   }
   if (ids) B200_TRY(fetch_idx64(m, m->idx32.as<int32_t>(), q * cap, ids));
   if (wts) B200_CUDA(cudaMemcpy(wts, m->wts.p, (size_t)q * cap * 8, cudaMemcpyDeviceToHost));
   if (cnt) B200_CUDA(cudaMemcpy(cnt, m->cnt.p, (size_t)q * 4, cudaMemcpyDeviceToHost));
   if (ier) B200_CUDA(cudaMemcpy(ier, m->err.p, (size_t)q * 4, cudaMemcpyDeviceToHost));
-  if (y) B200_CUDA(cudaMemcpy(out, m->out.p, (size_t)q * r * 8, cudaMemcpyDeviceToHost));
+  if (have_y) B200_CUDA(cudaMemcpy(out, m->out.p, (size_t)q * r * 8, cudaMemcpyDeviceToHost));
   B200_CUDA(cudaDeviceSynchronize());
   return 0;
 }
 
-int b200_lshep_fit(b200_model* m, const double* f, int32_t r, double* a, double* rw, int32_t* ier) {
+static int lshep_fit_host(b200_model* m, const double* f, int32_t r, double* a, double* rw, int32_t* ier, bool robust) {
   B200_TRY(use(m));
   if (!f || r < 1) {
     set_error("b200_lshep_fit: bad arguments");
@@ -552,7 +593,7 @@ int b200_lshep_fit(b200_model* m, const double* f, int32_t r, double* a, double*
   B200_TRY(m->out.reserve((size_t)r * n * 8));
   B200_CUDA(cudaMemcpy(m->out.p, ft.data(), (size_t)r * n * 8, cudaMemcpyHostToDevice));
   int e = 0;
-  B200_TRY(lshep_fit(m, m->out.as<double>(), r, 0, &e));
+  B200_TRY(lshep_fit(m, m->out.as<double>(), r, 0, &e, robust));
   if (ier) *ier = e;
   if (e != 1) {
     if (a) B200_CUDA(cudaMemcpy(a, m->la.p, (size_t)r * n * m->d * 8, cudaMemcpyDeviceToHost));
@@ -560,6 +601,14 @@ int b200_lshep_fit(b200_model* m, const double* f, int32_t r, double* a, double*
   }
   B200_CUDA(cudaDeviceSynchronize());
   return 0;
+}
+
+int b200_lshep_fit(b200_model* m, const double* f, int32_t r, double* a, double* rw, int32_t* ier) {
+  return lshep_fit_host(m, f, r, a, rw, ier, false);
+}
+
+int b200_lshep_fit_robust(b200_model* m, const double* f, double* a, double* rw, int32_t* ier) {
+  return lshep_fit_host(m, f, 1, a, rw, ier, true);
 }
 
 int b200_lshep_predict(b200_model* m, double radius, const double* z, int64_t q, double* out,

@@ -97,6 +97,7 @@ struct b200_model {
   bool shepmod_ready = false, lshep_ready = false;
   // cached response values for fused weighted sums
   b200::DevBuf y;
+  int y_r = 0;  // columns of the response values currently on the device (0: none)
   // scratch
   b200::DevBuf zq, idx32, d2, wts, cnt, err, out, part_d2, part_idx, cand, cand_meta, zimg,
       flags, misc, ids64;
@@ -164,7 +165,7 @@ int shepmod_predict(b200_model* m, const double* z_dev, int64_t q, int cap, int3
                     double* wts_dev, int32_t* cnt_dev, int32_t* ier_dev, const double* y_dev, int r,
                     double* out_dev, cudaStream_t st);
 // lshep.cu
-int lshep_fit(b200_model* m, const double* f_dev, int r, cudaStream_t st, int* ier);
+int lshep_fit(b200_model* m, const double* f_dev, int r, cudaStream_t st, int* ier, bool robust = false);
 int lshep_predict(b200_model* m, double radius, const double* z_dev, int64_t q, double* out_dev,
                   int32_t* ier_dev, cudaStream_t st);
 

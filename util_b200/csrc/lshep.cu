@@ -7,9 +7,11 @@
 //             reference calls LAPACK DGELSS (SVD, minimum norm); here it is a
 //             batched Householder QR with column pivoting, one thread per node,
 //             the systems stored [element][node] in scratch so loads coalesce.
-//             Full-rank systems agree with DGELSS to rounding; a node whose
-//             pivot falls below NP*eps*|R11| is flagged (IER=2) and gets the
-//             basic solution of its leading full-rank block.
+//             Full-rank systems agree with DGELSS to rounding.  A node whose pivots
+//             fall (near) the rank threshold is solved again the way DGELSS does it:
+//             a one-sided Jacobi SVD (one warp per such node), singular values
+//             <= NP*eps*sigma_max dropped, minimum-norm solution, IER=2 when the
+//             rank is short (:132-135, delaunay/lapack.f:2390-2420).
 //          3. DIAM = max pairwise squared distance (:114) only enters through
 //             RW = min(sqrt(DIAM)/2, RW) (:177).  A lower bound L <= DIAM from two
 //             farthest-point sweeps proves the clamp inactive when
@@ -51,10 +53,12 @@ __global__ void lshep_build_kernel(const double* __restrict__ x, int64_t n, int 
 
 // Householder QR with column pivoting, one thread per node, in place on W.
 // a (n,d) gets the solution; rank (n) the numerical rank.
+// Nodes whose smallest pivot is within 1e-7 of the first one are appended to `sus` and solved
+// again by lshep_svd_kernel (which also decides their rank the way DGELSS does).
 template <int DMAX>
 __global__ void lshep_qr_kernel(double* __restrict__ W, int64_t n, int d, int np,
                                 double* __restrict__ a, int32_t* __restrict__ rank_out,
-                                int32_t* __restrict__ flag) {
+                                int32_t* __restrict__ sus, int32_t* __restrict__ sus_cnt) {
   const int64_t k = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
   if (k >= n) return;
 #define A_(i, j) W[((size_t)(j) * np + (i)) * n + k]
@@ -67,7 +71,7 @@ __global__ void lshep_qr_kernel(double* __restrict__ W, int64_t n, int d, int np
     cn[j] = s;
   }
   int rank = d;
-  double r00 = 0.0;
+  double r00 = 0.0, rmin = CUDART_INF;
   const double tol = (double)np * 2.220446049250313e-16;  // RCOND, :100
   for (int c = 0; c < d; ++c) {
     // pivot: remaining column with the largest norm (recomputed for accuracy)
@@ -85,6 +89,7 @@ __global__ void lshep_qr_kernel(double* __restrict__ W, int64_t n, int d, int np
     }
     const double nrm = sqrt(best);
     if (c == 0) r00 = nrm;
+    rmin = fmin(rmin, nrm);
     if (!(nrm > tol * r00) || nrm == 0.0) { rank = c; break; }
     const double a0 = A_(c, c);
     const double alpha = a0 >= 0 ? -nrm : nrm;
@@ -112,8 +117,267 @@ __global__ void lshep_qr_kernel(double* __restrict__ W, int64_t n, int d, int np
   }
   for (int j = 0; j < d; ++j) a[k * d + perm[j]] = sol[j];  // :134
   if (rank_out) rank_out[k] = rank;
-  if (rank < d) atomicMax(flag, 2);  // :135
+  if (rank < d || !(rmin > 1e-7 * r00)) sus[atomicAdd(sus_cnt, 1)] = (int32_t)k;
 #undef A_
+}
+
+// Minimum-norm least squares the way DGELSS defines it, by one warp on a system in shared memory:
+// A = [d+1][np] (column j at A + j*np, column d the right-hand side; destroyed), V = [d][d] work,
+// wk = [2d] work.  One-sided Jacobi rotations orthogonalise the columns (A V = U S); then
+// x = sum_j (a_j . b / s_j^2) v_j over the singular values s_j > NP*eps*s_max (RCOND = NP*eps,
+// linear_shepard.f95:100; the cut of delaunay/lapack.f:2390-2400).  sol[d] receives x; returns the rank.
+__device__ int warp_gelss(double* A, double* V, double* wk, double* sol, int np, int d, int lane) {
+  for (int e = lane; e < d * d; e += 32) V[e] = (e / d == e % d) ? 1.0 : 0.0;
+  __syncwarp();
+  for (int sweep = 0; sweep < 40; ++sweep) {
+    int rotated = 0;
+    for (int p = 0; p + 1 < d; ++p)
+      for (int q = p + 1; q < d; ++q) {
+        double al = 0.0, be = 0.0, ga = 0.0;
+        for (int i = lane; i < np; i += 32) {
+          const double ap = A[(size_t)p * np + i], aq = A[(size_t)q * np + i];
+          al = fma(ap, ap, al);
+          be = fma(aq, aq, be);
+          ga = fma(ap, aq, ga);
+        }
+        for (int o = 16; o > 0; o >>= 1) {
+          al += __shfl_xor_sync(0xffffffffu, al, o);
+          be += __shfl_xor_sync(0xffffffffu, be, o);
+          ga += __shfl_xor_sync(0xffffffffu, ga, o);
+        }
+        if (!(fabs(ga) > 1e-15 * sqrt(al * be)) || ga == 0.0) continue;  // already orthogonal (warp-uniform)
+        ++rotated;
+        const double zeta = (be - al) / (2.0 * ga);
+        const double t = (zeta >= 0 ? 1.0 : -1.0) / (fabs(zeta) + sqrt(1.0 + zeta * zeta));
+        const double c = 1.0 / sqrt(1.0 + t * t), sn = c * t;
+        for (int i = lane; i < np; i += 32) {
+          const double ap = A[(size_t)p * np + i], aq = A[(size_t)q * np + i];
+          A[(size_t)p * np + i] = c * ap - sn * aq;
+          A[(size_t)q * np + i] = sn * ap + c * aq;
+        }
+        for (int i = lane; i < d; i += 32) {
+          const double vp = V[(size_t)p * d + i], vq = V[(size_t)q * d + i];
+          V[(size_t)p * d + i] = c * vp - sn * vq;
+          V[(size_t)q * d + i] = sn * vp + c * vq;
+        }
+        __syncwarp();
+      }
+    if (!rotated) break;
+  }
+  double* coef = wk;       // [d] a_j . b
+  double* sig2 = wk + d;   // [d] s_j^2
+  for (int j = 0; j < d; ++j) {
+    double s2 = 0.0, ab = 0.0;
+    for (int i = lane; i < np; i += 32) {
+      const double aj = A[(size_t)j * np + i];
+      s2 = fma(aj, aj, s2);
+      ab = fma(aj, A[(size_t)d * np + i], ab);
+    }
+    for (int o = 16; o > 0; o >>= 1) {
+      s2 += __shfl_xor_sync(0xffffffffu, s2, o);
+      ab += __shfl_xor_sync(0xffffffffu, ab, o);
+    }
+    if (lane == 0) {
+      sig2[j] = s2;
+      coef[j] = ab;
+    }
+  }
+  __syncwarp();
+  double smax2 = 0.0;
+  for (int j = 0; j < d; ++j) smax2 = fmax(smax2, sig2[j]);
+  const double rcond = (double)np * 2.220446049250313e-16;
+  const double thr = fmax(rcond * sqrt(smax2), 2.2250738585072014e-308);  // max(RCOND*S(1), SFMIN)
+  int rank = 0;
+  for (int j = 0; j < d; ++j) rank += sqrt(sig2[j]) > thr ? 1 : 0;
+  for (int i = lane; i < d; i += 32) {
+    double xi = 0.0;
+    for (int j = 0; j < d; ++j)
+      if (sqrt(sig2[j]) > thr) xi = fma(coef[j] / sig2[j], V[(size_t)j * d + i], xi);
+    sol[i] = xi;
+  }
+  __syncwarp();
+  return rank;
+}
+
+// DGELSS semantics for the nodes listed in `sus`: one warp per node.  The node's weighted system is
+// rebuilt in shared memory and solved by warp_gelss.  Rank short of d raises the fit's IER to 2 (:135).
+__global__ void __launch_bounds__(32)
+lshep_svd_kernel(const double* __restrict__ x, int64_t n, int d, int np, const int32_t* __restrict__ idx,
+                 const double* __restrict__ d2, const double* __restrict__ f, const int32_t* __restrict__ sus,
+                 double* __restrict__ a, int32_t* __restrict__ flag) {
+  extern __shared__ double sm[];
+  double* A = sm;                         // [d+1][np]
+  double* V = sm + (size_t)(d + 1) * np;  // [d][d]
+  double* wk = V + (size_t)d * d;         // [2d]
+  double* sol = wk + 2 * d;               // [d]
+  const int lane = threadIdx.x;
+  const int64_t k = sus[blockIdx.x];
+  const double rk = sqrt(d2[k * np + np - 1]);
+  const double rp = __dmul_rn(1.1, rk);
+  const double fk = f[k];
+  for (int i = lane; i < np; i += 32) {  // the same arithmetic as lshep_build_kernel
+    const int nb = idx[k * np + i];
+    const double dist = sqrt(d2[k * np + i]);
+    const double om = __ddiv_rn(__dsub_rn(rp, dist), __dmul_rn(rp, dist));
+    for (int j = 0; j < d; ++j) A[(size_t)j * np + i] = __dmul_rn(om, __dsub_rn(x[(int64_t)nb * d + j], x[k * d + j]));
+    A[(size_t)d * np + i] = __dmul_rn(om, __dsub_rn(f[nb], fk));
+  }
+  __syncwarp();
+  const int rank = warp_gelss(A, V, wk, sol, np, d, lane);
+  for (int i = lane; i < d; i += 32) a[k * d + i] = sol[i];
+  if (lane == 0 && rank < d) atomicMax(flag, 2);  // :135
+}
+
+// ---- robust fit (LSHEP with RLSHEP present, linear_shepard.f95:136-175; IRLS :181-282, MAD :284-308,
+// QUANTILE :310-335).  One warp per node, everything in shared memory.
+// k-th smallest (1-based) of v[0..n): the value with #(< it) < k <= #(<= it) -- what QUANTILE's
+// recursion returns.
+__device__ double warp_kth(const double* v, int n, int k, int lane) {
+  double found = 0.0;
+  int have = 0;
+  for (int i = lane; i < n; i += 32) {
+    const double x = v[i];
+    int lt = 0, le = 0;
+    for (int j = 0; j < n; ++j) {
+      lt += v[j] < x;
+      le += v[j] <= x;
+    }
+    if (lt < k && k <= le) {
+      found = x;
+      have = 1;
+    }
+  }
+  // every lane that found it holds the same value: take the lowest such lane
+  const unsigned m = __ballot_sync(0xffffffffu, have);
+  return __shfl_sync(0xffffffffu, found, __ffs(m) - 1);
+}
+__device__ double warp_mad(const double* res, double* tmp, int np, int lane) {
+  const double factor = __ddiv_rn(1.0, 0.6745);  // :297
+  const int nmid = np / 2;
+  double med;
+  if (np % 2 == 0) med = __ddiv_rn(__dadd_rn(warp_kth(res, np, nmid, lane), warp_kth(res, np, nmid + 1, lane)), 2.0);
+  else med = warp_kth(res, np, nmid + 1, lane);
+  for (int i = lane; i < np; i += 32) tmp[i] = fabs(__dsub_rn(res[i], med));
+  __syncwarp();
+  double r;
+  if (np % 2 == 0)
+    r = __ddiv_rn(__dmul_rn(factor, __dadd_rn(warp_kth(tmp, np, nmid, lane), warp_kth(tmp, np, nmid + 1, lane))), 2.0);
+  else
+    r = __dmul_rn(factor, warp_kth(tmp, np, nmid + 1, lane));
+  __syncwarp();
+  return r;
+}
+// residuals RES = ALPHA_IN . sol - BETA_IN (:137, :272), row by row in dimension order
+__device__ void warp_residuals(const double* Ain, const double* bin, const double* sol, double* res, int np, int d,
+                               int lane) {
+  for (int i = lane; i < np; i += 32) {
+    double v = 0.0;
+    for (int j = 0; j < d; ++j) v = __dadd_rn(v, __dmul_rn(Ain[(size_t)j * np + i], sol[j]));
+    res[i] = __dsub_rn(v, bin[i]);
+  }
+  __syncwarp();
+}
+__device__ double warp_bisq_objective(const double* res, double s, int np) {  // :243, :275 (sequential SUM)
+  double e = 0.0;
+  for (int j = 0; j < np; ++j) {
+    const double t = __ddiv_rn(res[j], s);
+    const double w = fmax(0.0, __dsub_rn(1.0, __dmul_rn(t, t)));
+    e = __dadd_rn(e, __dsub_rn(1.0, __dmul_rn(__dmul_rn(w, w), w)));
+  }
+  return e;
+}
+// IRLS (:181-282): returns IER 0 / 1 / 2; sol and res updated, omega = final weights, *s scaled (:237).
+__device__ int warp_irls(double* A, double* V, double* wk, double* sol, const double* Ain, const double* bin,
+                         double* res, double* omega, double* s, int func, int np, int d, int lane) {
+  *s = __dmul_rn(func == 1 ? 1.0 : 3.0, *s);  // :231, :237
+  double err_old = 0.0;
+  if (func == 2) err_old = warp_bisq_objective(res, *s, np);
+  for (int it = 0; it < 5; ++it) {
+    for (int j = lane; j < np; j += 32) {
+      double w;
+      if (func == 1) w = res[j] == 0.0 ? 1.0 : sqrt(fmin(1.0, __ddiv_rn(*s, fabs(res[j]))));  // :249-256
+      else {
+        const double t = __ddiv_rn(res[j], *s);
+        w = fmax(0.0, __dsub_rn(1.0, __dmul_rn(t, t)));  // :258-259
+      }
+      omega[j] = w;
+      for (int c = 0; c < d; ++c) A[(size_t)c * np + j] = __dmul_rn(w, Ain[(size_t)c * np + j]);  // :262-265
+      A[(size_t)d * np + j] = __dmul_rn(w, bin[j]);
+    }
+    __syncwarp();
+    const int rank = warp_gelss(A, V, wk, sol, np, d, lane);  // :266-267
+    if (rank < d) return 1;                                   // :268-271
+    warp_residuals(Ain, bin, sol, res, np, d, lane);          // :272
+  }
+  if (func == 2 && warp_bisq_objective(res, *s, np) > err_old) return 2;  // :274-280
+  return 0;
+}
+
+__global__ void __launch_bounds__(32)
+lshep_robust_kernel(const double* __restrict__ x, int64_t n, int d, int np, const int32_t* __restrict__ idx,
+                    const double* __restrict__ d2, const double* __restrict__ f, double* __restrict__ a,
+                    double* __restrict__ rw, unsigned long long* __restrict__ last_ier) {
+  extern __shared__ double sm[];
+  double* A = sm;                              // [d+1][np] weighted system (work)
+  double* V = A + (size_t)(d + 1) * np;        // [d][d]
+  double* wk = V + (size_t)d * d;              // [2d]
+  double* sol = wk + 2 * d;                    // [d]
+  double* Ain = sol + d;                       // [d][np] ALPHA_IN
+  double* bin = Ain + (size_t)d * np;          // [np] BETA_IN
+  double* res = bin + np;                      // [np]
+  double* omega = res + np;                    // [np]
+  double* dist = omega + np;                   // [np]
+  double* tmp = dist + np;                     // [np]
+  const int lane = threadIdx.x;
+  const int64_t k = blockIdx.x;
+  const double fk = f[k];
+  for (int i = lane; i < np; i += 32) {
+    const int nb = idx[k * np + i];
+    dist[i] = sqrt(d2[k * np + i]);                                                    // :116
+    bin[i] = __dsub_rn(f[nb], fk);                                                     // :117
+    for (int j = 0; j < d; ++j) {
+      const double v = __dsub_rn(x[(int64_t)nb * d + j], x[k * d + j]);                // :118-120
+      Ain[(size_t)j * np + i] = v;
+      A[(size_t)j * np + i] = v;                                                       // OMEGA = 1 (:122-123)
+    }
+    A[(size_t)d * np + i] = bin[i];
+    omega[i] = 1.0;
+  }
+  __syncwarp();
+  double rk = dist[np - 1];                                                            // :121
+  int rank = warp_gelss(A, V, wk, sol, np, d, lane);                                   // :132
+  for (int j = lane; j < d; j += 32) a[k * d + j] = sol[j];                            // :134
+  // IER is a plain scalar the node loop overwrites (:135, :145, :157): the code set by the highest node wins
+  if (lane == 0 && rank < d) atomicMax(last_ier, ((unsigned long long)(k + 1) << 2) | 2ull);
+  warp_residuals(Ain, bin, sol, res, np, d, lane);                                     // :137
+  double mar = warp_mad(res, tmp, np, lane);                                           // :138
+  bool failed = false;
+  if (mar > 2.220446049250313e-16) {                                                   // :139
+    int e1 = warp_irls(A, V, wk, sol, Ain, bin, res, omega, &mar, 1, np, d, lane);     // :140-143
+    if (e1 != 0) {
+      failed = true;                                                                   // :144-146
+    } else {
+      for (int j = lane; j < d; j += 32) a[k * d + j] = sol[j];                        // :148
+      mar = warp_mad(res, tmp, np, lane);                                              // :150
+      if (mar > 2.220446049250313e-16) {                                               // :151
+        e1 = warp_irls(A, V, wk, sol, Ain, bin, res, omega, &mar, 2, np, d, lane);     // :152-155
+        if (e1 != 0) failed = true;                                                    // :156-158
+        else
+          for (int j = lane; j < d; j += 32) a[k * d + j] = sol[j];                    // :160
+      }
+    }
+  }
+  if (failed) {
+    if (lane == 0) atomicMax(last_ier, ((unsigned long long)(k + 1) << 2) | 3ull);
+  } else {
+    for (int i = 0; i < np; ++i) {                                                     // :164-174
+      if (omega[i] < 0.8) {
+        rk = i == 0 ? __ddiv_rn(dist[0], 2.0) : __ddiv_rn(__dadd_rn(dist[i - 1], dist[i]), 2.0);
+        break;
+      }
+    }
+  }
+  if (lane == 0) rw[k] = rk;
 }
 
 // squared distance of every node to one anchor row; block max -> atomic max (as ordered uint64)
@@ -462,7 +726,7 @@ lshep_eval_kernel(const double* __restrict__ x, const float* __restrict__ x32, c
 
 }  // namespace
 
-int lshep_fit(b200_model* m, const double* f_dev, int r, cudaStream_t st, int* ier) {
+int lshep_fit(b200_model* m, const double* f_dev, int r, cudaStream_t st, int* ier, bool robust) {
   const int64_t n = m->n;
   const int d = m->d;
   *ier = 0;
@@ -482,18 +746,47 @@ int lshep_fit(b200_model* m, const double* f_dev, int r, cudaStream_t st, int* i
   B200_TRY(m->la.reserve((size_t)r * n * (2 * d + 1) * 8));  // a (r,n,d) then unit normals (r,n,d+1)
   B200_TRY(m->misc.reserve((size_t)np * (d + 1) * n * 8 + 64));
   B200_TRY(m->flags.reserve(256));
+  B200_TRY(m->cnt.reserve((size_t)n * 4 + 64));  // nodes to be solved again by the SVD kernel
   B200_CUDA(cudaMemcpyAsync(m->lf.p, f_dev, (size_t)r * n * 8, cudaMemcpyDeviceToDevice, st));
   B200_TRY(knn_dispatch(m, m->x, n, np, 0, m->idx32.as<int32_t>(), m->d2.as<double>(), st));
   B200_CUDA(cudaMemsetAsync(m->flags.p, 0, 256, st));
   int32_t* flag = m->flags.as<int32_t>();
   const unsigned gb = (unsigned)((n + 127) / 128);
+  unsigned long long* last_ier = reinterpret_cast<unsigned long long*>(m->flags.as<char>() + 32);
   for (int c = 0; c < r; ++c) {
     double* ac = m->la.as<double>() + (size_t)c * n * d;
+    if (robust) {
+      // RW depends on the response through the final IRLS weights; with several columns the last one stays,
+      // as in the wrapper's per-column loop (linear_shepard/__init__.py:47-55 keeps one rw per column: the
+      // caller reads it back after each column through b200_lshep_fit_robust's rw argument)
+      const size_t smem = ((size_t)(2 * d + 1) * np + (size_t)d * d + 3 * (size_t)d + 5 * (size_t)np) * 8;
+      B200_CUDA(cudaFuncSetAttribute(lshep_robust_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+      lshep_robust_kernel<<<(unsigned)n, 32, smem, st>>>(m->x, n, d, np, m->idx32.as<int32_t>(), m->d2.as<double>(),
+                                                         m->lf.as<double>() + (size_t)c * n, ac, m->rw.as<double>(),
+                                                         last_ier);
+      unit_slope_kernel<<<gb, 128, 0, st>>>(ac, n, d, m->la.as<double>() + (size_t)r * n * d + (size_t)c * n * (d + 1));
+      B200_CUDA(cudaGetLastError());
+      m->st.launches += 2;
+      continue;
+    }
     lshep_build_kernel<<<gb, 128, 0, st>>>(m->x, n, d, np, m->idx32.as<int32_t>(), m->d2.as<double>(),
                                            m->lf.as<double>() + (size_t)c * n, m->misc.as<double>(),
                                            m->rw.as<double>());
-    if (d <= 16) lshep_qr_kernel<16><<<gb, 128, 0, st>>>(m->misc.as<double>(), n, d, np, ac, nullptr, flag);
-    else lshep_qr_kernel<64><<<gb, 128, 0, st>>>(m->misc.as<double>(), n, d, np, ac, nullptr, flag);
+    int32_t* sus = m->cnt.as<int32_t>();
+    int32_t* sus_cnt = flag + 4;
+    B200_CUDA(cudaMemsetAsync(sus_cnt, 0, 4, st));
+    if (d <= 16) lshep_qr_kernel<16><<<gb, 128, 0, st>>>(m->misc.as<double>(), n, d, np, ac, nullptr, sus, sus_cnt);
+    else lshep_qr_kernel<64><<<gb, 128, 0, st>>>(m->misc.as<double>(), n, d, np, ac, nullptr, sus, sus_cnt);
+    int h_sus = 0;
+    B200_CUDA(cudaMemcpyAsync(&h_sus, sus_cnt, 4, cudaMemcpyDeviceToHost, st));
+    B200_CUDA(cudaStreamSynchronize(st));
+    if (h_sus > 0) {
+      const size_t smem = ((size_t)(d + 1) * np + (size_t)d * d + 3 * (size_t)d) * 8;
+      B200_CUDA(cudaFuncSetAttribute(lshep_svd_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+      lshep_svd_kernel<<<(unsigned)h_sus, 32, smem, st>>>(m->x, n, d, np, m->idx32.as<int32_t>(), m->d2.as<double>(),
+                                                          m->lf.as<double>() + (size_t)c * n, sus, ac, flag);
+      m->st.launches += 1;
+    }
     unit_slope_kernel<<<gb, 128, 0, st>>>(ac, n, d, m->la.as<double>() + (size_t)r * n * d + (size_t)c * n * (d + 1));
     B200_CUDA(cudaGetLastError());
     m->st.launches += 3;
@@ -542,6 +835,11 @@ int lshep_fit(b200_model* m, const double* f_dev, int r, cudaStream_t st, int* i
     clamp_rw_kernel<<<gb, 128, 0, st>>>(m->rw.as<double>(), n, sqrt(diam) / 2.0);
     B200_CUDA(cudaGetLastError());
     m->st.launches += 2;
+  }
+  if (robust) {
+    unsigned long long h_last = 0;
+    B200_CUDA(cudaMemcpy(&h_last, last_ier, 8, cudaMemcpyDeviceToHost));
+    h_flag = (int)(h_last & 3ull);
   }
   *ier = h_flag;
   m->lshep_r = r;

@@ -44,7 +44,7 @@ class ShepMod(WeightedApproximator):
                 [wts[i, :cnt[i]] for i in range(len(ids))])
 
     def _predict_values(self, x):
-        return self._run(x, y=self._y_numeric)[3][:, 0]
+        return self._run(x, y=True)[3][:, 0]
 
     def errors(self):
         print("%i normal returns." % self.ierrors.get(0, 0))

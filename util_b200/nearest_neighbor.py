@@ -52,19 +52,23 @@ class NearestNeighbor(WeightedApproximator):
         if self.model is not None: self.model.close()
         self.model = _lib.Model(self.points, device=self.device)
         self.tree = self.model  # attribute name users of the reference read
-        # nearest_neighbor/__init__.py:42-55: automatic k
         if self.num_neighbors is None:
-            if self.y is not None:
-                self.auto_kwargs.update(kwargs)
-                if "mean" not in self.auto_kwargs:
-                    self.auto_kwargs["mean"] = not self.classifier
-                end = ("\n" if display else "\r")
-                print("Nearest neighbor, estimating best value for 'k'..", end=end, flush=True)
-                self.num_neighbors = auto(self.points, self.y, **self.auto_kwargs)
-                print(f"  chose k = {self.num_neighbors}", end=end, flush=True)
-                print("                                                 ", end=end, flush=True)
-            else:
-                self.num_neighbors = 1
+            self.num_neighbors = self._choose_k(display, kwargs)
+
+    def _choose_k(self, display, overrides):
+        """k=None (nearest_neighbor/__init__.py:42-55): without responses k = 1, otherwise auto() with the
+        constructor's keyword arguments, those of this fit() call on top, and `mean` defaulting to
+        "not a classifier".  Progress lines as the reference prints them."""
+        if self.y is None:
+            return 1
+        self.auto_kwargs.update(overrides)
+        self.auto_kwargs.setdefault("mean", not self.classifier)
+        end = "\n" if display else "\r"
+        print("Nearest neighbor, estimating best value for 'k'..", end=end, flush=True)
+        k = auto(self.points, self.y, **self.auto_kwargs)
+        print(f"  chose k = {k}", end=end, flush=True)
+        print(" " * 49, end=end, flush=True)
+        return k
 
     def _check(self):
         if self.model is None:
@@ -94,7 +98,7 @@ class NearestNeighbor(WeightedApproximator):
     def _predict_values(self, points, max_size=2**20, display=True):
         k = self._check()
         code = _method_code(self.method)
-        _, _, _, err, out = self.model.nn_predict(points, k, code, y=self._y_numeric, want_weights=False)
+        _, _, _, err, out = self.model.nn_predict(points, k, code, y=True, want_weights=False)
         self._raise_submodel_errors(code, err)
         return out[:, 0]
 
@@ -115,41 +119,48 @@ class NearestNeighbor(WeightedApproximator):
         return (np.sqrt(d2), idx) if return_distance else idx
 
 
+def _default_sample(n, count):
+    """Row sample of the reference's auto(): util.random.random_range(n, count=count) draws
+    random.sample(range(n), count) whenever n <= 2**15 (util/random/random.py:55-58), so with the
+    same `random` seed this picks the same rows there; for larger n the reference walks a linear
+    congruential generator, which a caller who needs the identical rows can pass in as `indices`."""
+    import random
+    return random.sample(range(n), min(count, n))
+
+
 def auto(points, values, metric=abs_diff, max_k=None, samples=100, mean=True, k_step=1,
-         model=NearestNeighbor, display=False):
-    """nearest_neighbor/__init__.py:93-132: pick the power-of-two k minimising the mean
-    (or mean-min) response difference to the k nearest neighbours of sampled points."""
-    from math import floor, log2
-    from random import sample
+         model=None, display=False, indices=None):
+    """Choice of k as in nearest_neighbor/__init__.py:93-132: for a sample of the fitted rows, the
+    mean (or mean of the minimum) response difference to their k nearest other rows, over
+    k = 1, 2, 4, ... <= max_k; the k with the lowest value wins (the smallest on ties).
+
+    One batched kNN call (k = max_k + 1, first column dropped as in :107) replaces the reference's
+    per-point loop.  `indices` (optional) fixes the sampled rows; `model` is accepted for signature
+    compatibility (the reference ignores it as well, :104)."""
+    n = len(points)
     if max_k is None:
-        max_k = 2 ** floor(log2(len(points) // 2))
-        # the CUDA kNN keeps at most 1024 neighbours per query; the reference's default (half the data
-        # set) is capped accordingly -- the error curve is flat long before that in practice
-        max_k = min(max_k, 512)
-    model = NearestNeighbor(k=max_k + 1)
-    model.fit(points)
-    # util.random.random_range(len(points), count=samples) (:104)
-    indices = sample(range(len(points)), min(samples, len(points)))
-    neighbors = model.neighbors(points[indices])[:, 1:]
-    differences = np.array([[metric(values[i1], values[i2]) for i2 in neighbors[i]]
-                            for i, i1 in enumerate(indices)])
-    k_values = {}
-    for k_pow in range(0, int(log2(max_k)) + 1, k_step):
-        k = 2 ** k_pow
-        if mean: k_values[k] = np.mean(differences[:, :k])
-        else: k_values[k] = np.mean(np.min(differences[:, :k], axis=1))
-    if 2 ** k_pow != max_k:
-        k = 2 ** int(log2(max_k))
-        if mean: k_values[k] = np.mean(differences[:, :k])
-        else: k_values[k] = np.mean(np.min(differences[:, :k], axis=1))
-    best_k = min(k_values.items(), key=lambda i: i[1])[0]
+        max_k = 1 << ((n // 2).bit_length() - 1)  # largest power of two <= n/2  (:98-100)
+    rows = np.asarray(list(indices) if indices is not None else _default_sample(n, samples), dtype=np.int64)
+    knn = NearestNeighbor(k=max_k + 1)
+    knn.fit(points)
+    nbrs = knn.neighbors(points[rows], k=max_k + 1)[:, 1:]
+    knn.model.close()
+    if metric is abs_diff and isinstance(values, np.ndarray) and values.ndim == 1 and values.dtype.kind in "fiu":
+        diffs = np.abs(values[rows, None] - values[nbrs])
+    else:  # any pairwise metric over arbitrary response objects
+        diffs = np.array([[metric(values[i], values[j]) for j in nbrs[r]] for r, i in enumerate(rows)])
+    top = max_k.bit_length() - 1  # int(log2(max_k))
+    ks = [1 << e for e in range(0, top + 1, k_step)]
+    if ks[-1] != max_k and (1 << top) not in ks:
+        ks.append(1 << top)  # (:118-121) the largest power of two is always a candidate
+    score = (lambda k: np.mean(diffs[:, :k])) if mean else (lambda k: np.mean(np.min(diffs[:, :k], axis=1)))
+    table = {k: score(k) for k in ks}
+    best_k = min(table.items(), key=lambda kv: kv[1])[0]
     if display:
-        name = "mean" if mean else "minimum"
-        from math import log10, ceil
-        print('-' * 52)
-        print(" Estimated " + name + " error for various choices of 'k':")
-        for k in sorted(k_values):
-            extra = "  <-- chosen 'k'" if k == best_k else ""
-            print(f"  k = {k:{ceil(log10(max_k))}d} ~ {k_values[k]:.4e}" + extra)
-        print('-' * 52)
+        width = len(str(max_k - 1)) if max_k > 1 else 0
+        print("-" * 52)
+        print(f" Estimated {'mean' if mean else 'minimum'} error for various choices of 'k':")
+        for k in sorted(table):
+            print(f"  k = {k:{width}d} ~ {table[k]:.4e}" + ("  <-- chosen 'k'" if k == best_k else ""))
+        print("-" * 52)
     return best_k

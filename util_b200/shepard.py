@@ -33,4 +33,4 @@ class Shepard(WeightedApproximator):
         return indices, weights
 
     def _predict_values(self, points, display_wait_sec=3.):
-        return self.model.shepard_predict(points, y=self._y_numeric)[1][:, 0]
+        return self.model.shepard_predict(points, y=True)[1][:, 0]

@@ -45,7 +45,7 @@ class Voronoi(WeightedApproximator):
         return ([ids[i, :cnt[i]] for i in range(len(ids))], [wts[i, :cnt[i]] for i in range(len(ids))])
 
     def _predict_values(self, points, **kw):
-        _, _, _, err, out = self.model.voronoi_predict(points, y=self._y_numeric)
+        _, _, _, err, out = self.model.voronoi_predict(points, y=True)
         if (err == 1).any():
             raise OverflowError("The scale of the data caused a squared float to overflow, consider normalizing data.")
         if (err == 2).any():
