@@ -1,17 +1,27 @@
 #!/usr/bin/env python
-"""bench.py -- query points/sec of the kNN + Shepard predict hot path.
+"""bench.py -- query points/sec of util.approximate's distance-based predict hot path on B200.
 
-    python bench.py --gpus N --steps K --warmup W            # this repo's CUDA path
-    python bench.py --impl reference --gpus N --steps K ...  # the reference's CPU algorithm (oracle port)
+    python bench.py --gpus N --steps K --warmup W            # this repo's CUDA path, headline config C5
+    python bench.py --config c1|c2|c3|c4                     # the other BASELINE.json configs (one GPU)
+    python bench.py --impl reference --gpus N --steps K ...  # the reference's CPU algorithm on the host cores
 
-Workload (BASELINE.json configs[4], SURVEY.md 8d "C5"): X 1,000,000 x 64 uniform
-[0,1) (seed 0), Z 1,000,000 x 64 (seed 1), k = 16, NearestNeighbor(method=Shepard),
-y = 3x0 + .5cos(8x0) + sin(5x_{d-1}).  One step = one pass of the hot path over
-the whole query batch.  `value` is timed on the device with the inputs resident
-in HBM; `e2e` goes through the host-buffer C-ABI call (pinned host memory in,
-host results out, copies inside the timed region).  For N > 1 the data set is
-sharded over the ranks (local top-k, NCCL all-to-all of the partial lists,
-on-device merge): total work is fixed, so scaling is "strong".
+Headline workload (BASELINE.json configs[4], SURVEY.md 8d "C5"): X 1,000,000 x 64 uniform [0,1) (seed 0),
+Z 1,000,000 x 64 (seed 1), k = 16, NearestNeighbor(method=Shepard), y = 3x0 + .5cos(8x0) + sin(5x_{d-1}).
+One step = one pass of the hot path over the whole query batch.  `value` is timed on the device with the
+inputs resident in HBM; `e2e` goes through the host-buffer C-ABI call (pinned host memory in, host results
+out, copies inside the timed region).  For N > 1 the default (`--shard auto`) gives every rank all fitted
+points and a slice of the queries -- the data set fits one GPU, which is the case north_star assigns to
+query sharding; `--shard data` splits the fitted points instead (local top-k, NCCL all-to-all of the
+partial lists, on-device merge).  Total work is fixed either way, so scaling is "strong".
+
+C1-C4 go through the drop-in classes: fit and predict are timed separately, `value` is the predict rate
+from the library's own kernel timers (inputs resident), `e2e` the class call with host arrays, and every
+stage gets a roofline entry: tensor peak where the stage is a contraction, HBM bytes for the weighting
+stages, and the measured fp64 / fp32 FMA rate of the CUDA cores (b200_debug_fma_peak) for the dense scans.
+
+cpu_baseline: the oracle port (OpenMP, all host cores) on a bounded sample; when the unmodified reference
+is installed under baseline/_ref (pip --target) the real util.approximate.NearestNeighbor
+(pure Python + sklearn BallTree, one thread) is timed too and reported as `reference_class`.
 """
 import argparse
 import ctypes as C
@@ -32,8 +42,14 @@ CONFIGS = {
     # name: (n, q, d, k)
     "c5": (1_000_000, 1_000_000, 64, 16),
     "c5small": (200_000, 100_000, 64, 16),
-    "c1": (10_000, 1_000, 8, 1),
     "c5q": (1_000_000, 37_888, 64, 16),   # one 256-query block per SM: quick kernel experiments
+}
+# the other BASELINE.json configs, run through the drop-in classes: (n, q, d, k, model)
+CLASS_CONFIGS = {
+    "c1": (10_000, 1_000, 8, 1, "NearestNeighbor(k=1)"),
+    "c2": (100_000, 100_000, 16, None, "ShepMod()"),
+    "c3": (200_000, 200_000, 10, None, "LSHEP(radius=2)"),
+    "c4": (50_000, 50_000, 32, 64, "NearestNeighbor(k=64, method=Voronoi)"),
 }
 
 
@@ -102,6 +118,152 @@ def cpu_port(x, y, z, k, seconds=15.0, threads=None):
     return s / dt, s, dt, cores, (ids, out)
 
 
+def reference_class_rate(x, y, z, k, seconds=25.0, queries=None):
+    """The unmodified reference, when it is installed under baseline/_ref: the real
+    util.approximate.NearestNeighbor (pure Python + sklearn BallTree; its Fortran sub-models cannot be
+    built here, so method=Average) on a bounded query sample, one thread.  None if not installed."""
+    ref = os.path.join(ROOT, "baseline", "_ref")
+    if not os.path.isdir(os.path.join(ref, "util")):
+        return None
+    import types
+    import tempfile
+    stub = types.ModuleType("fmodpy")  # the reference imports fmodpy at package import; nothing is compiled
+    stub.config = types.SimpleNamespace(load_config=lambda *a, **kw: None)
+
+    def fimport(*a, **kw):
+        raise ImportError("fmodpy stub: no Fortran toolchain in this image")
+    stub.fimport = fimport
+    sys.modules.setdefault("fmodpy", stub)
+    sys.path.insert(0, ref)
+    cwd = os.getcwd()
+    os.chdir(tempfile.mkdtemp())
+    try:
+        import util.approximate as ua
+    except Exception as e:  # e.g. sklearn missing
+        os.chdir(cwd)
+        return {"unavailable": repr(e)[:200]}
+    os.chdir(cwd)
+    m = ua.NearestNeighbor(k=k)
+    t0 = time.perf_counter()
+    m.fit(x, y)
+    t_fit = time.perf_counter() - t0
+    s = 4
+    t0 = time.perf_counter()
+    m.predict(z[:s], display=False)
+    per = (time.perf_counter() - t0) / s
+    s = int(queries or max(8, min(len(z), seconds / max(per, 1e-9))))
+    t0 = time.perf_counter()
+    pred = m.predict(z[:s], display=False)
+    dt = time.perf_counter() - t0
+    return {"value": s / dt, "unit": "queries/s", "cores": 1, "kind": "reference",
+            "sample": f"first {s} queries, util.approximate.NearestNeighbor(k={k}) from baseline/_ref "
+                      f"(method=Average: the Fortran sub-models cannot be built), BallTree build {t_fit:.1f} s not included",
+            "fit_s": t_fit, "pred": np.asarray(pred, dtype=float)}
+
+
+def run_class_config(args, name):
+    """C1-C4 through the drop-in classes on one GPU: fit and predict timed separately."""
+    import util_b200 as ub
+    from util_b200 import _lib
+    from oracle import harness as H
+    n, q, d, k, label = CLASS_CONFIGS[name]
+    x = np.random.default_rng(0).random((n, d))
+    z = np.random.default_rng(1).random((q, d))
+    y = fun(x)
+    pk = peaks()
+    f64 = C.c_double()
+    f32 = C.c_double()
+    _lib.check(_lib.lib().b200_debug_fma_peak(0, C.byref(f64), C.byref(f32)))
+    make = {"c1": lambda: ub.NearestNeighbor(k=1), "c2": lambda: ub.ShepMod(), "c3": lambda: ub.LSHEP(radius=2),
+            "c4": lambda: ub.NearestNeighbor(k=64, method=ub.Voronoi)}[name]
+    m = make()
+    m.fit(x, y)  # warm-up fit (operand images, allocations)
+    t0 = time.perf_counter()
+    m.fit(x, y)
+    fit_s = time.perf_counter() - t0
+    fit_stats = {s: m.model.stat(s) for s in ("ms_prep", "ms_stage1", "ms_rerank", "ms_exact", "ms_weights")}
+    sampler = ClockSampler(0)
+    sampler.start()
+    for _ in range(max(args.warmup, 3)):
+        m.predict(z)
+    m.model.set_option("reset_stats", 1)
+    t0 = time.perf_counter()
+    for _ in range(args.steps):
+        pred = m.predict(z)
+    dt = (time.perf_counter() - t0) / args.steps
+    sampler.stop_flag = True
+    st = {s: m.model.stat(s) / args.steps for s in
+          ("ms_prep", "ms_stage1", "ms_rerank", "ms_exact", "ms_weights", "launches", "uncertified")}
+    ms_dev = st["ms_prep"] + st["ms_stage1"] + st["ms_rerank"] + st["ms_exact"] + st["ms_weights"]
+    pred = np.asarray(pred, dtype=float).reshape(q)
+    # ---- roofline of the dominant predict kernel
+    if name in ("c2", "c3"):
+        # dense scan of every node by every query: fp32 prefilter (2 q n d flops) in front of the fp64 arithmetic;
+        # SURVEY 8d counts C2 as a contraction against the tensor peak and C3 as (5M+12) q n fp64 flops
+        if name == "c2":
+            flops, peak, unit_peak = 2.0 * q * n * d, pk["tensor"], "dense bf16 tensor peak (north_star assigns this stage to the tensor pipe)"
+            kern = "shepmod_eval_kernel"
+        else:
+            flops, peak, unit_peak = (5.0 * d + 12.0) * q * n, f64.value, "measured fp64 FMA rate (b200_debug_fma_peak)"
+            kern = "lshep_eval_kernel"
+        ach = flops / (st["ms_weights"] * 1e-3) / 1e12
+        roof = {"bound": "tensor" if name == "c2" else "fp64", "kernel": kern, "achieved": ach, "peak": peak,
+                "unit": "TFLOP/s", "frac": ach / peak, "traffic": None, "peak_source": unit_peak,
+                "ms_per_launch": st["ms_weights"], "algorithmic_flops_per_launch": flops,
+                "fp32_fma_peak_tflops": f32.value, "fp64_fma_peak_tflops": f64.value}
+    else:
+        flops = 2.0 * q * n * d
+        ms_knn = st["ms_stage1"] if st["ms_stage1"] > 0 else st["ms_exact"]
+        ach = flops / (max(ms_knn, 1e-9) * 1e-3) / 1e12
+        roof = {"bound": "tensor", "kernel": "knn_tc_kernel" if st["ms_stage1"] > 0 else "knn_exact_kernel (fp64 CUDA cores)",
+                "achieved": ach, "peak": pk["tensor"], "unit": "TFLOP/s", "frac": ach / pk["tensor"], "traffic": None,
+                "peak_source": pk["src"] + " bf16_tflops_sustained", "ms_per_launch": ms_knn,
+                "algorithmic_flops_per_launch": flops}
+    stages = {"weights": {"bound": "hbm", "ms": st["ms_weights"]}}
+    if name == "c4":
+        byts = q * (k * d * 8 + d * 8 + k * 4 + k * 12)  # k neighbour rows + query + ids in, ids/weights out
+        stages["weights"].update(bytes=byts, achieved=byts / 1e9 / (st["ms_weights"] * 1e-3), peak=pk["hbm"], unit="GB/s")
+    # ---- CPU baseline: the oracle port on a bounded sample, parity on that sample
+    H.set_threads(os.cpu_count() or 1)
+    s = {"c1": q, "c2": 400, "c3": 200, "c4": 300}[name]
+    t0 = time.perf_counter()
+    if name == "c1":
+        ids, w, cnt, _ = H.nn_predict(x, z[:s], 1, "average")
+        ref = H.weighted_sum(ids, w, cnt, y)
+    elif name == "c2":
+        oi, ow, oc, _ = H.shepmod_predict(x, m.rw, z[:s], cap=256)
+        ref = H.weighted_sum(oi, ow, oc, y)
+    elif name == "c3":
+        ref, _ = H.lshep_predict(x, y, m.a[0].T, m.rw[0], z[:s])
+    else:
+        ids, w, cnt, _ = H.nn_predict(x, z[:s], k, "voronoi")
+        ref = H.weighted_sum(ids, w, cnt, y)
+    t_cpu = time.perf_counter() - t0
+    rel = float(np.max(np.abs(pred[:s] - ref) / np.maximum(np.abs(ref), 1e-3 * max(1.0, np.abs(ref).max()))))
+    line = {"metric": "query points/sec (%s predict)" % label, "value": q / (ms_dev * 1e-3), "unit": "queries/s",
+            "n_gpus": 1, "steps": args.steps, "warmup": max(args.warmup, 3), "ms_per_step": ms_dev,
+            "higher_is_better": True, "scaling": "strong", "vs_baseline": None,
+            "dtype": "f64 (f16 tensor filter / f32 prefilter in front)", "data": "synthetic",
+            "config": {"workload": f"{label} fit + predict, {n}x{d} data, {q} queries", "n": n, "q": q, "d": d, "k": k,
+                       "parallelism": "single", "l2": "results of the previous step are overwritten; inputs re-uploaded every step"},
+            "fit_s": fit_s, "fit_stages_ms": fit_stats,
+            "roofline": roof, "stages_ms": {kk: vv for kk, vv in st.items() if kk.startswith("ms_")},
+            "roofline_stages": stages, "gpu_launches": int(round(st["launches"] * args.steps)),
+            "e2e": {"value": q / dt, "unit": "queries/s", "h2d_bytes_per_step": int(z.nbytes),
+                    "d2h_bytes_per_step": int(q * 8), "ms_per_step": dt * 1e3},
+            "clocks": sampler.summary(),
+            "cpu_baseline": {"value": s / t_cpu, "unit": "queries/s", "cores": os.cpu_count(), "kind": "port",
+                             "sample": f"first {s} of {q} queries against all {n} points in {t_cpu:.1f} s, OpenMP over queries"},
+            "parity_on_sample": {"max_rel_err": rel}}
+    if name == "c1" and not args.no_ref_class:
+        rc = reference_class_rate(x, y, z, 1, seconds=args.ref_seconds)
+        if rc and "pred" in rc:
+            p_ref = rc.pop("pred")
+            rc["predictions_equal"] = bool(np.array_equal(p_ref, pred[:len(p_ref)]))
+        line["reference_class"] = rc
+    print(json.dumps(line), flush=True)
+
+
 def run_reference(args, n, q, d, k):
     rank = int(os.environ.get("RANK", "0"))
     if rank != 0:
@@ -142,6 +304,11 @@ def run_reference(args, n, q, d, k):
             "cpu_baseline": {"value": val, "unit": "queries/s", "cores": cores, "kind": "port",
                              "sample": f"{s} of {q} queries per step against all {n} points, OpenMP over queries"},
             "e2e": {"value": val, "unit": "queries/s", "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0}}
+    if not args.no_ref_class:
+        rc = reference_class_rate(x, y, z, k, seconds=args.ref_seconds, queries=args.ref_queries or None)
+        if rc:
+            rc.pop("pred", None)
+        line["reference_class"] = rc
     print(json.dumps(line), flush=True)
 
 
@@ -157,6 +324,9 @@ def main():
                          "queries when the data set fits one GPU's HBM (north_star), else data")
     ap.add_argument("--cpu-seconds", type=float, default=15.0)
     ap.add_argument("--no-cpu", action="store_true")
+    ap.add_argument("--no-ref-class", action="store_true", help="skip timing the real reference class from baseline/_ref")
+    ap.add_argument("--ref-seconds", type=float, default=25.0)
+    ap.add_argument("--ref-queries", type=int, default=0, help="fixed query sample for the reference class (0: by time)")
     ap.add_argument("--no-e2e", action="store_true", help="kernel experiments only: skip the host-buffer leg")
     ap.add_argument("--path", type=int, default=0, help="0 auto, 1 exact, 2 tensor")
     ap.add_argument("--margin", type=int, default=-1)
@@ -166,6 +336,11 @@ def main():
     ap.add_argument("--tc-stats", type=int, default=0, help="instrumented stage-1 kernel: event / stall counters")
     ap.add_argument("--tc-mode", type=int, default=0, help="ceilings: 1 no selection, 2 no epilogue")
     args = ap.parse_args()
+    if args.config in CLASS_CONFIGS:
+        if args.impl == "reference":
+            n, q, d, k, _ = CLASS_CONFIGS[args.config]
+            return run_reference(args, n, q, d, k or 16)
+        return run_class_config(args, args.config)
     n, q, d, k = CONFIGS[args.config]
     if args.shard == "auto":
         args.shard = "query" if n * d * 8 < 60e9 else "data"
@@ -376,6 +551,14 @@ def main():
             go = last["out"][:s].cpu().numpy()
             line["parity_on_sample"] = {"indices_equal": bool(np.array_equal(gi, cids)),
                                         "max_rel_err": float(np.max(np.abs(go - cout) / np.maximum(np.abs(cout), 1e-3)))}
+            if not args.no_ref_class:
+                # the reference's own class (one thread, method=Average); its neighbours must be ours
+                rc = reference_class_rate(x, y, z, k, seconds=args.ref_seconds, queries=args.ref_queries or None)
+                if rc and "pred" in rc:
+                    p_ref = rc.pop("pred")
+                    mine = y[last["idx"][:len(p_ref)].cpu().numpy().astype(np.int64)].mean(axis=1)
+                    rc["max_rel_err_vs_ours"] = float(np.max(np.abs(mine - p_ref) / np.maximum(np.abs(p_ref), 1e-3)))
+                line["reference_class"] = rc
         print(json.dumps(line), flush=True)
     if G > 1:
         dist.destroy_process_group()

@@ -16,6 +16,10 @@ extern "C" {
 int b200_tc_debug_scores(b200_model* m, const double* z, int64_t q, int32_t k, float* scores,
                          int64_t cols);
 
+/* Measured FMA rates of the CUDA cores (independent chains on every SM), the roofline denominators
+ * bench.py uses for the dense fp64 / fp32 scans: TFLOP/s, 2 flops per FMA. */
+int b200_debug_fma_peak(int32_t device, double* fp64_tflops, double* fp32_tflops);
+
 #ifdef __cplusplus
 }
 #endif

@@ -112,7 +112,14 @@ def gen_wrappers():
     rows = b(zu)
     s = Split(standins.linear(Approximator), k=4, seed=5)
     s.fit(xs, ys)
-    np.savez(os.path.join(HERE, "wrappers.npz"), unique_values=with_values,
+    from util.approximate.wrappers import condition
+    cond = {}
+    for tag, kw in (("a", {}), ("b", dict(dim=2)), ("c", dict(scale=False))):
+        c = condition(standins.linear(Approximator), method="PCA", **kw)()
+        c.fit(xs, ys)
+        cond[f"cond_{tag}_matrix"] = c.conditioner
+        cond[f"cond_{tag}_pred"] = c(zs)
+    np.savez(os.path.join(HERE, "wrappers.npz"), **cond, unique_values=with_values,
              unique_ids=np.array([list(r[0]) + [-1] * (40 - len(r[0])) for r in rows]),
              unique_wts=np.array([list(r[1]) + [0.0] * (40 - len(r[1])) for r in rows]),
              unique_indices=b.unique_indices, split=s(zs))

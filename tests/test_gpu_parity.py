@@ -334,6 +334,23 @@ def test_standalone_voronoi_all_points(ub, oracle):
         md(z[:2])
 
 
+def test_nn_with_any_weighted_submodel(ub, oracle):
+    """NearestNeighbor(method=cls) instantiates whatever WeightedApproximator class it is given
+    (nearest_neighbor/__init__.py:78-83; SURVEY.md 3.1 lists ShepMod, which needs k >= d + 2)."""
+    x, z = synth(600, 40, 3)
+    y = fun(x)
+    k = 8
+    m = ub.NearestNeighbor(k=k, method=ub.ShepMod)
+    m.fit(x, y)
+    pred = np.array(m(z))
+    ids, w, cnt, _ = oracle.nn_predict(x, z, k, "shepmod")
+    ref = oracle.weighted_sum(ids, w, cnt, y)
+    assert relerr(pred, ref) < RTOL
+    gi, gw = m._predict(z)
+    for r in range(len(z)):
+        assert np.array_equal(gi[r], ids[r, :cnt[r]])
+
+
 def test_auto_k_selection(ub):
     """nearest_neighbor.auto (nearest_neighbor/__init__.py:93-132): k=None picks a power of two from the
     neighbours of 100 sampled points; a response that only depends on the nearest point wants k = 1."""

@@ -61,7 +61,7 @@ def test_condition_applies_the_map_on_both_sides():
     rng = np.random.default_rng(1)
     x, z = rng.random((30, 4)), rng.random((6, 4))
     A = np.diag([1., 0., 3., 0.])[:, [0, 2]]  # keep and scale two coordinates
-    C = condition(NearestOne, A)
+    C = condition(NearestOne, conditioner=A)
     m = C()
     m.fit(x)
     assert m.x.shape == (30, 2)
@@ -92,3 +92,21 @@ def test_wrappers_match_the_reference_golden():
     s = Split(standins.linear(Approximator), k=4, seed=5)
     s.fit(xs, ys)
     assert np.array_equal(s(zs), g["split"])
+
+
+def test_condition_pca_matches_the_reference_golden():
+    """tests/golden/wrappers.npz `cond_*`: the reference's condition(method="PCA") (wrappers.py:117-184 with
+    util.stats.pca / normalize_error) around the stand-in linear model."""
+    import os, sys
+    here = os.path.join(os.path.dirname(os.path.abspath(__file__)), "golden")
+    sys.path.insert(0, here)
+    import standins
+    g = np.load(os.path.join(here, "wrappers.npz"))
+    xu, yu, zu, xs, ys, zs = standins.wrapper_inputs()
+    for tag, kw in (("a", {}), ("b", dict(dim=2)), ("c", dict(scale=False))):
+        m = condition(standins.linear(Approximator), method="PCA", **kw)()
+        m.fit(xs, ys)
+        assert np.allclose(m.conditioner, g[f"cond_{tag}_matrix"], rtol=1e-12, atol=1e-14)
+        assert np.allclose(m(zs), g[f"cond_{tag}_pred"], rtol=1e-10, atol=1e-12)
+    with pytest.raises(NotImplementedError):
+        condition(standins.linear(Approximator))

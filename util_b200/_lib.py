@@ -52,6 +52,7 @@ _SIGNATURES = {
                                          C.c_void_p, C.c_void_p, C.c_void_p]),
     "b200_tc_debug_scores": (C.c_int, [C.c_void_p, c_dp, C.c_int64, C.c_int32, C.POINTER(C.c_float),
                                        C.c_int64]),
+    "b200_debug_fma_peak": (C.c_int, [C.c_int32, c_dp, c_dp]),
     "b200_merge_topk_dev": (C.c_int, [C.c_int32, C.c_void_p, C.c_void_p, C.c_int32, C.c_int64,
                                       C.c_int32, C.c_void_p, C.c_void_p, C.c_void_p]),
 }

@@ -4,7 +4,7 @@ import shutil
 import subprocess
 
 CSRC = os.path.join(os.path.dirname(os.path.abspath(__file__)), "csrc")
-SOURCES = ["api.cu", "knn_exact.cu", "knn_tc.cu", "weights.cu", "shepard_all.cu", "voronoi_all.cu", "shepmod.cu", "lshep.cu"]
+SOURCES = ["api.cu", "knn_exact.cu", "knn_tc.cu", "weights.cu", "shepard_all.cu", "voronoi_all.cu", "shepmod.cu", "lshep.cu", "microbench.cu"]
 LIB = os.path.join(CSRC, "libb200approx.so")
 NVCC_FLAGS = ["-gencode", "arch=compute_100a,code=sm_100a", "-lineinfo", "-O3", "-std=c++17",
               "-Xcompiler", "-fPIC", "-shared", "-ccbin", "g++"]

@@ -29,12 +29,8 @@ class Average(WeightedApproximator):
 
 
 def _method_code(method):
-    code = getattr(method, "_b200_method", None)
-    if code is None:
-        raise NotImplementedError(
-            f"NearestNeighbor(method={getattr(method, '__name__', method)}): only Average, Shepard "
-            "and Voronoi sub-models have a CUDA kernel")
-    return code
+    """Average / Shepard / Voronoi sub-models have a fused CUDA kernel; None for any other class."""
+    return getattr(method, "_b200_method", None)
 
 
 class NearestNeighbor(WeightedApproximator):
@@ -88,6 +84,8 @@ class NearestNeighbor(WeightedApproximator):
         """
         k = self._check()
         code = _method_code(self.method)
+        if code is None:
+            return self._predict_any_submodel(points, k)
         ids, wts, cnt, err, _ = self.model.nn_predict(points, k, code)
         self._raise_submodel_errors(code, err)
         if code == _lib.VORONOI:
@@ -95,9 +93,25 @@ class NearestNeighbor(WeightedApproximator):
                     [wts[i, :cnt[i]] for i in range(len(ids))])
         return ids, wts
 
+    def _predict_any_submodel(self, points, k):
+        """Any other WeightedApproximator class as `method` (nearest_neighbor/__init__.py:78-83): the k
+        neighbours of all queries come from one batched GPU call; the sub-model is then constructed,
+        fitted on each query's neighbours and evaluated there, as the reference does per point."""
+        closest = self.model.knn(points, k, want_d2=False)
+        pts, wts = [], []
+        for nbrs, pt in zip(closest, points):
+            sub = self.method()
+            sub.fit(self.points[nbrs])
+            guess_pts, guess_wts = sub.predict(pt)
+            pts.append(nbrs[np.asarray(guess_pts, dtype=np.int64)])
+            wts.append(np.asarray(guess_wts))
+        return pts, wts
+
     def _predict_values(self, points, max_size=2**20, display=True):
         k = self._check()
         code = _method_code(self.method)
+        if code is None:
+            return None  # no fused path: base.predict forms the sums from (ids, wts)
         _, _, _, err, out = self.model.nn_predict(points, k, code, y=True, want_weights=False)
         self._raise_submodel_errors(code, err)
         return out[:, 0]

@@ -1,11 +1,10 @@
 """Model combinators with the interface of util/approximate/wrappers.py.
 
 `Split` (:13-36) and `unique` (:42-116) are host-side glue around any model of this
-package; the distance work underneath stays on the GPU.  `condition` (:122-184) with an
-explicit linear map: the reference derives its map from PLRM / util.stats.pca / mpca,
-which are outside this package's scope, so here the caller supplies the
-d x d' matrix (the "PCA"/"MPCA" branch's `self.conditioner`, :170) and the wrapper applies
-it before fit and predict exactly as :172,183 do.
+package; the distance work underneath stays on the GPU.  `condition` (:117-184) keeps the
+reference's signature: method="PCA" builds the linear map on the host (sklearn PCA + the
+per-axis error scaling of util.stats.normalize_error), an explicit `conditioner=` matrix is
+accepted as well, and the map is applied before fit and predict exactly as :172,183 do.
 """
 import numpy as np
 
@@ -89,18 +88,63 @@ def unique(weighted_approximator):
     return UniquePointsApproximator
 
 
-def condition(approximator, conditioner):
-    """wrappers.py:122-184 for a given linear map: the model is fitted on, and evaluated
-    at, `x @ conditioner` (:172,183).  `conditioner` is the (d, d') matrix
-    `(diag(values) @ components).T` of :170."""
-    conditioner = np.asarray(conditioner, dtype=float)
-    if conditioner.ndim != 2:
-        raise UnexpectedType("conditioner should be a 2D (d, d') array.")
+def _axis_slopes_to_scale(points, values, metric):
+    """util.stats.normalize_error (stats/metric_pca.py:23-49): per axis the total metric variation between
+    neighbours along that axis, divided by their spacing; the axes are then scaled by slope^-2,
+    normalised by the median and to unit geometric mean."""
+    n, d = points.shape
+    slope = np.zeros(d)
+    for axis in range(d):
+        order = np.argsort(points[:, axis])
+        for lo, hi in zip(order[:-1], order[1:]):
+            gap = points[hi, axis] - points[lo, axis]
+            if gap > 0:
+                slope[axis] += metric(values[lo], values[hi]) / (gap * d)
+    if slope.min() <= 0.0:  # axes without any slope are the only ones needed
+        slope = np.where(slope == 0, 1., float("inf"))
+    fix = slope ** (-2)
+    fix /= np.median(fix)
+    return fix / np.prod(fix) ** (1 / d)
+
+
+def condition(approximator, metric=None, method="PLR", dim=None, samples=None, scale=True,
+              display=False, seed=None, conditioner=None, **cond_kwargs):
+    """wrappers.py:117-184: the model is fitted on, and evaluated at, `x @ conditioner` (:172,183).
+
+    method="PCA" (:145-149): the principal axes of x (sklearn PCA, as the reference's util.stats.pca
+    calls it) scaled by `normalize_error` so that the response has unit metric slope along each axis.
+    `conditioner=` (an extension) supplies the (d, d') matrix `(diag(values) @ components).T` of :170
+    directly.  The reference's default "PLR" trains its PLRM network and "MPCA" samples random point
+    pairs through util.random; both lie outside this package and raise."""
+    from .base import abs_diff
+    if metric is None:
+        metric = abs_diff
+    if conditioner is not None:
+        conditioner = np.asarray(conditioner, dtype=float)
+        if conditioner.ndim != 2:
+            raise UnexpectedType("conditioner should be a 2D (d, d') array.")
+    elif method != "PCA":
+        raise NotImplementedError(
+            f"condition(method={method!r}): only method='PCA' and an explicit conditioner= matrix are "
+            "available; the reference's PLR / MPCA conditioners need its PLRM network / random pair sampler")
 
     class ConditionedApproximator(approximator):
-        def _fit(self, x, *args, **kwargs):
-            self.conditioner = conditioner
-            return super()._fit(np.matmul(x, conditioner), *args, **kwargs)
+        def _fit(self, x, *args, num_comps=None, **kwargs):
+            if conditioner is not None:
+                self.conditioner = conditioner
+            else:
+                y = args[0] if args else getattr(self, "y", None)
+                if y is None:
+                    raise UnexpectedType("condition(method='PCA') needs response values to scale the axes.")
+                if num_comps is None: num_comps = min(x.shape + (16,))   # :128
+                if dim is not None: num_comps = min(dim, num_comps)       # :129
+                from sklearn.decomposition import PCA
+                num_comps = min(num_comps, *x.shape)
+                components = PCA(n_components=num_comps).fit(x).components_    # :146, stats/metric_pca.py:82-94
+                values = _axis_slopes_to_scale(np.matmul(x, components.T), y, metric)   # :148
+                if not scale: values[:] = 1.                                           # :157
+                self.conditioner = np.matmul(np.diag(values), components).T           # :170
+            return super()._fit(np.matmul(x, self.conditioner), *args, **kwargs)
 
         def _predict(self, x, *args, **kwargs):
             return super()._predict(np.matmul(x, self.conditioner), *args, **kwargs)
