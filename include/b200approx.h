@@ -100,7 +100,7 @@ int b200_eval_mesh(int32_t device, const double* int_prods, int32_t n, const dou
 /* Stand-alone Voronoi() over ALL fitted points (Voronoi._predict,
  * voronoi/__init__.py:41-62: PREDICT, voronoi/voronoi.f90:57-155, once per query
  * against the n x n inner-product cache of _fit, :32-38).  The cache is built on
- * the first call (n <= 4096).  Per query the points with positive weight in
+ * the first call (kept in HBM while it fits 40 GB; larger sets recompute the products).  Per query the points with positive weight in
  * ascending index order: ids/wts (q,cap), cnt (q) = their number (> cap: the
  * row was truncated, call again with a larger cap), err (q) 0 / 1 overflow /
  * 2 duplicated fit points; optional y (n,r) -> out (q,r). */

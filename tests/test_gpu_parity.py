@@ -334,6 +334,28 @@ def test_standalone_voronoi_all_points(ub, oracle):
         md(z[:2])
 
 
+@pytest.mark.parametrize("n,d,qs", [(5000, 6, 24), (20000, 4, 12)])
+def test_standalone_voronoi_beyond_4096_points(ub, oracle, n, d, qs):
+    """Voronoi() over all n fitted points for n beyond one block's shared memory (persistent blocks, Gram
+    cache in HBM): supports, weights and predictions against PREDICT (voronoi.f90:57-155) as the oracle
+    restates it; SURVEY.md 8d asks for the N = 5 000 point."""
+    x, z = synth(n, qs, d)
+    y = fun(x)
+    m = ub.Voronoi()
+    m.fit(x, y)
+    pred = np.array(m(z))
+    gi, gw = m._predict(z)
+    ref = []
+    for r, p in enumerate(z):
+        w, e = oracle.voronoi_predict(x, p)
+        assert e == 0
+        sup = np.nonzero(w > 0)[0]
+        assert np.array_equal(gi[r], sup)
+        assert np.max(np.abs(gw[r] - w[sup])) < 1e-12
+        ref.append(sum(y[i] * w[i] for i in sup))
+    assert relerr(pred, np.array(ref)) < RTOL
+
+
 def test_nn_with_any_weighted_submodel(ub, oracle):
     """NearestNeighbor(method=cls) instantiates whatever WeightedApproximator class it is given
     (nearest_neighbor/__init__.py:78-83; SURVEY.md 3.1 lists ShepMod, which needs k >= d + 2)."""
@@ -461,7 +483,7 @@ def test_wrappers_around_gpu_models(ub, oracle):
     assert relerr(np.array(m(x[:100])), y[:100] + 1.0) < RTOL
     # condition with an explicit map: neighbours are found in the mapped space (:172,183)
     A = np.diag([2.0, 1.0, 0.5, 0.0])
-    C = ub.condition(ub.NearestNeighbor, A)
+    C = ub.condition(ub.NearestNeighbor, conditioner=A)
     c = C(k=5)
     c.fit(x, y)
     ids, w, cnt, _ = oracle.nn_predict(x @ A, z @ A, 5, "average")

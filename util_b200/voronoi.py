@@ -3,9 +3,10 @@
 As `NearestNeighbor(k, method=Voronoi)` (BASELINE.json config 4, "candidate-pruned
 by kNN") the weights on the k neighbours come from voronoi_kernel (PREDICT,
 voronoi/voronoi.f90:57-155).  Stand-alone `Voronoi()` over all n fitted points uses
-voronoi_all_kernel against the n x n inner-product matrix (the reference's `dots`
-cache, :32-38), built once on the device: n <= 4096 (128 MiB; the reference's cache
-is 20 GB at n = 50 000 -- beyond that use the kNN-pruned form, as BASELINE does).
+the n x n inner-product matrix (the reference's `dots` cache, :32-38) built once on the
+device: up to n = 4096 one block per query keeps its row buffers in shared memory; beyond
+that persistent blocks keep them in global scratch and the cache stays in HBM while it
+fits (20 GB at n = 50 000), else the inner products are recomputed on the fly.
 """
 import numpy as np
 
@@ -18,7 +19,6 @@ class DuplicateInterpolationPoints(Exception): pass
 
 class Voronoi(WeightedApproximator):
     _b200_method = _lib.VORONOI
-    _MAX_N = 4096
     points = None
     dots = None  # the reference's lazily filled n x n cache; results never depended on it
     model = None
@@ -28,10 +28,6 @@ class Voronoi(WeightedApproximator):
 
     def _fit(self, points):
         self.points = points.copy().T
-        if points.shape[0] > self._MAX_N:
-            raise NotImplementedError(
-                f"stand-alone Voronoi over n={points.shape[0]} > {self._MAX_N} points is not built; "
-                "use NearestNeighbor(k, method=Voronoi)")
         if self.model is not None: self.model.close()
         self.model = _lib.Model(points, device=self.device)
 
