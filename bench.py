@@ -440,6 +440,12 @@ def main():
     stats = {s: model.stat(s) / args.steps for s in
              ("ms_prep", "ms_stage1", "ms_rerank", "ms_exact", "launches", "uncertified")}
     stats["ms_weights"] = sum(a.elapsed_time(b) for a, b in wev) / max(len(wev), 1)
+    if data_sharded:
+        sh.ms_collective = sh.ms_merge = 0.0
+        sh._timed = sh._timed[-args.steps:]
+        sh.collect_times()
+        stats["ms_collective"] = sh.ms_collective / args.steps
+        stats["ms_merge"] = sh.ms_merge / args.steps
     if G > 1:
         t = torch.tensor([ms], device=dev)
         dist.all_reduce(t, op=dist.ReduceOp.MAX)

@@ -150,6 +150,25 @@ int b200_merge_topk_dev(int32_t device, const double* d2_parts, const int32_t* i
                         int32_t parts, int64_t q, int32_t k, double* d2_out, int32_t* idx_out,
                         void* stream);
 
+/* ---- one fitted model over several GPUs of one box, driven from one process.  No counterpart in the
+ * reference (single-threaded, no devices); this is BASELINE.json configs[4] behind the C-ABI.
+ * shard_data = 0: every device holds all fitted points and takes a contiguous slice of the queries (no
+ * exchange; the choice when the data set fits one GPU).  shard_data = 1: device g holds rows
+ * [g n/G, (g+1) n/G), finds its exact local top-k of all queries, the partial lists travel in one
+ * all-to-all (grouped ncclSend/ncclRecv; libnccl.so.2 is opened with dlopen at create time), and each
+ * device merges and weights its slice of the queries -- bit-identical to the single-GPU result.
+ * Host buffers in and out as for b200_nn_predict; Average / Shepard weighting under data sharding.
+ * Stats: the devices' counters summed, plus "ms_collective", "ms_merge", "ms_local" (max over devices). */
+typedef struct b200_multi b200_multi;
+int b200_multi_create(const double* x, int64_t n, int32_t d, int32_t n_dev, const int32_t* devs, int32_t shard_data,
+                      b200_multi** out);
+int b200_multi_destroy(b200_multi* mm);
+int b200_multi_set_option(b200_multi* mm, const char* key, double value);
+int b200_multi_get_stat(b200_multi* mm, const char* key, double* value);
+int b200_multi_set_values(b200_multi* mm, const double* y, int32_t r);
+int b200_multi_nn_predict(b200_multi* mm, const double* z, int64_t q, int32_t k, int32_t method, int64_t* ids,
+                          double* wts, double* out);
+
 /* Exact kNN that allocates nothing.  It has no counterpart in the reference, which owns
  * no device memory.  Meant for callers that cannot let a library allocate while they
  * run: serving loops for which the implicit device-wide synchronisation of

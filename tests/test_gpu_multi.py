@@ -49,3 +49,29 @@ def test_data_sharded_two_gpus(tmp_path):
                         "--master-addr", "127.0.0.1", "--master-port", str(port), str(f)],
                        capture_output=True, text=True, timeout=600, env=env)
     assert "SHARDED_OK" in r.stdout, r.stdout[-2000:] + r.stderr[-2000:]
+
+
+def test_one_process_handle_over_two_gpus(oracle):
+    """b200_multi_*: NearestNeighbor(devices=[0, 1]) from one process, no torch -- queries sharded, and the
+    fitted points sharded with the NCCL exchange + on-device merge.  Both must reproduce the oracle's
+    neighbours bit for bit and the single-GPU predictions exactly."""
+    from util_b200 import _lib
+    import util_b200 as ub
+    if _lib.lib().b200_device_count() < 2:
+        pytest.skip("needs >= 2 GPUs")
+    n, q, d, k = 60000, 5001, 16, 8   # q not a multiple of the device count: padded slices
+    x = np.random.default_rng(0).random((n, d)); z = np.random.default_rng(1).random((q, d))
+    y = 3 * x[:, 0] + .5 * np.cos(8 * x[:, 0]) + np.sin(5 * x[:, -1])
+    oi, od = oracle.knn(x, z[:300], k)
+    one = ub.NearestNeighbor(k=k, method=ub.Shepard)
+    one.fit(x, y)
+    ref = np.array(one(z))
+    for shard in ("query", "data"):
+        m = ub.NearestNeighbor(k=k, method=ub.Shepard, devices=[0, 1], shard=shard)
+        m.fit(x, y)
+        pred = np.array(m(z))
+        assert np.array_equal(pred, ref), shard
+        ids, wts = m._predict(z[:300])
+        assert np.array_equal(ids, oi), shard
+        if shard == "data":
+            assert m.model.stat("ms_collective") > 0 and m.model.stat("ms_merge") > 0

@@ -52,6 +52,12 @@ _SIGNATURES = {
                                          C.c_void_p, C.c_void_p, C.c_void_p]),
     "b200_tc_debug_scores": (C.c_int, [C.c_void_p, c_dp, C.c_int64, C.c_int32, C.POINTER(C.c_float),
                                        C.c_int64]),
+    "b200_multi_create": (C.c_int, [c_dp, C.c_int64, C.c_int32, C.c_int32, c_i32p, C.c_int32, C.POINTER(C.c_void_p)]),
+    "b200_multi_destroy": (C.c_int, [C.c_void_p]),
+    "b200_multi_set_option": (C.c_int, [C.c_void_p, C.c_char_p, C.c_double]),
+    "b200_multi_get_stat": (C.c_int, [C.c_void_p, C.c_char_p, c_dp]),
+    "b200_multi_set_values": (C.c_int, [C.c_void_p, c_dp, C.c_int32]),
+    "b200_multi_nn_predict": (C.c_int, [C.c_void_p, c_dp, C.c_int64, C.c_int32, C.c_int32, c_i64p, c_dp, c_dp]),
     "b200_debug_fma_peak": (C.c_int, [C.c_int32, c_dp, c_dp]),
     "b200_merge_topk_dev": (C.c_int, [C.c_int32, C.c_void_p, C.c_void_p, C.c_int32, C.c_int64,
                                       C.c_int32, C.c_void_p, C.c_void_p, C.c_void_p]),
@@ -92,6 +98,69 @@ def f64(a):
 
 def ptr(a, t=c_dp):
     return None if a is None else a.ctypes.data_as(t)
+
+
+class MultiModel:
+    """Owner of one `b200_multi` handle: the fitted points on several GPUs of this box, driven from this
+    process (queries sharded, or the fitted points sharded with an NCCL exchange of the partial lists)."""
+
+    def __init__(self, x, devices, shard="query"):
+        x = f64(x)
+        if shard not in ("query", "data"):
+            raise ValueError("shard must be 'query' or 'data'")
+        self.n, self.d = x.shape
+        self.devices = [int(v) for v in devices]
+        self.shard = shard
+        devs = np.asarray(self.devices, dtype=np.int32)
+        self._h = C.c_void_p()
+        check(lib().b200_multi_create(ptr(x), self.n, self.d, len(devs), ptr(devs, c_i32p), int(shard == "data"),
+                                      C.byref(self._h)))
+        self.values_r = 0
+
+    def close(self):
+        if getattr(self, "_h", None) is not None and self._h:
+            lib().b200_multi_destroy(self._h)
+            self._h = C.c_void_p()
+
+    def __del__(self):
+        try:
+            self.close()
+        except Exception:
+            pass
+
+    def set_option(self, key, value):
+        check(lib().b200_multi_set_option(self._h, key.encode(), float(value)))
+
+    def stat(self, key):
+        v = C.c_double()
+        check(lib().b200_multi_get_stat(self._h, key.encode(), C.byref(v)))
+        return v.value
+
+    def set_values(self, y):
+        y = f64(y).reshape(self.n, -1)
+        check(lib().b200_multi_set_values(self._h, ptr(y), y.shape[1]))
+        self.values_r = y.shape[1]
+
+    def knn(self, z, k, self_offset=-1, want_d2=False):
+        """Neighbour indices (q,k) ascending by (distance, index); distances are not exchanged."""
+        if self_offset != -1 or want_d2:
+            raise NotImplementedError("MultiModel.knn returns indices only")
+        return self.nn_predict(z, k, AVERAGE)[0]
+
+    def nn_predict(self, z, k, method, y=None, want_weights=True):
+        """Same return convention as Model.nn_predict: (ids, wts, cnt, err, out); y=True uses set_values()."""
+        z = f64(z)
+        q = z.shape[0]
+        ids = wts = out = None
+        if want_weights:
+            ids = np.empty((q, k), dtype=np.int64)
+            wts = np.empty((q, k), dtype=np.float64)
+        if y is not None:
+            if y is not True:
+                self.set_values(y)
+            out = np.empty((q, self.values_r))
+        check(lib().b200_multi_nn_predict(self._h, ptr(z), q, k, method, ptr(ids, c_i64p), ptr(wts), ptr(out)))
+        return ids, wts, np.full(q, k, dtype=np.int32), np.zeros(q, dtype=np.int32), out
 
 
 class Model:

@@ -4,7 +4,7 @@ import shutil
 import subprocess
 
 CSRC = os.path.join(os.path.dirname(os.path.abspath(__file__)), "csrc")
-SOURCES = ["api.cu", "knn_exact.cu", "knn_tc.cu", "weights.cu", "shepard_all.cu", "voronoi_all.cu", "shepmod.cu", "lshep.cu", "microbench.cu"]
+SOURCES = ["api.cu", "knn_exact.cu", "knn_tc.cu", "weights.cu", "shepard_all.cu", "voronoi_all.cu", "shepmod.cu", "lshep.cu", "microbench.cu", "multi.cu"]
 LIB = os.path.join(CSRC, "libb200approx.so")
 NVCC_FLAGS = ["-gencode", "arch=compute_100a,code=sm_100a", "-lineinfo", "-O3", "-std=c++17",
               "-Xcompiler", "-fPIC", "-shared", "-ccbin", "g++"]
@@ -23,7 +23,7 @@ def build(force=False, verbose=False):
     if not force and not needs_build():
         return LIB
     nvcc = shutil.which("nvcc") or "/usr/local/cuda/bin/nvcc"
-    cmd = [nvcc] + NVCC_FLAGS + (["-Xptxas", "-v"] if verbose else []) + ["-o", LIB] + SOURCES + ["-lcuda"]
+    cmd = [nvcc] + NVCC_FLAGS + (["-Xptxas", "-v"] if verbose else []) + ["-o", LIB] + SOURCES + ["-lcuda", "-ldl"]
     subprocess.check_call(cmd, cwd=CSRC)
     return LIB
 

@@ -34,19 +34,30 @@ def _method_code(method):
 
 
 class NearestNeighbor(WeightedApproximator):
-    def __init__(self, k=1, method=Average, device=None, **auto_kwargs):
+    def __init__(self, k=1, method=Average, device=None, devices=None, shard="query", **auto_kwargs):
+        """`device` / `devices` / `shard` are additions to the reference's constructor: one GPU ordinal, or
+        a list of ordinals over which the queries (shard="query", the default: every GPU holds all fitted
+        points) or the fitted points (shard="data": local top-k, NCCL exchange, on-device merge) are split."""
         self.points = None
         self.method = method
         self.num_neighbors = k
         self.auto_kwargs = auto_kwargs
         self.device = device
+        self.devices = list(devices) if devices is not None else None
+        self.shard = shard
         self.model = None  # _lib.Model: the device-resident points (stands in for self.tree)
 
     def _fit(self, control_points, k=None, display=True, **kwargs):
         if k is not None: self.num_neighbors = k
         self.points = control_points.copy()
         if self.model is not None: self.model.close()
-        self.model = _lib.Model(self.points, device=self.device)
+        if self.devices is not None and len(self.devices) > 1:
+            if _method_code(self.method) not in (_lib.AVERAGE, _lib.SHEPARD):
+                raise NotImplementedError("several devices: Average and Shepard sub-models")
+            self.model = _lib.MultiModel(self.points, self.devices, shard=self.shard)
+        else:
+            dev = self.devices[0] if self.devices else self.device
+            self.model = _lib.Model(self.points, device=dev)
         self.tree = self.model  # attribute name users of the reference read
         if self.num_neighbors is None:
             self.num_neighbors = self._choose_k(display, kwargs)

@@ -68,6 +68,8 @@ class DataShardedKNN:
         self.device_index = device_index
         self.model = _lib.Model(np.ascontiguousarray(x_full[self.lo:self.hi]), device=device_index)
         self.torch = torch
+        self.ms_collective = self.ms_merge = 0.0  # accumulated CUDA-event times of the exchange and the merge
+        self._timed = []
 
     def knn(self, z_dev, k, stream=None):
         """-> merged (d2, idx) for this rank's query slice: tensors (q/world, k)."""
@@ -79,13 +81,27 @@ class DataShardedKNN:
         self._lib.check(lib.b200_knn_dev(self.model.handle, z_dev.data_ptr(), q, k, -1, idx.data_ptr(),
                                          d2.data_ptr(), st))
         idx.add_(self.lo)  # local -> global row ids
+        e = [torch.cuda.Event(enable_timing=True) for _ in range(3)]
+        e[0].record()
         rd2, ridx = exchange_partials(d2, idx, self.group)
+        e[1].record()
         qm = q // self.world
         md2 = torch.empty((qm, k), dtype=torch.float64, device=z_dev.device)
         midx = torch.empty((qm, k), dtype=torch.int32, device=z_dev.device)
         self._lib.check(lib.b200_merge_topk_dev(self.device_index, rd2.data_ptr(), ridx.data_ptr(), self.world,
                                                 qm, k, md2.data_ptr(), midx.data_ptr(), st))
+        e[2].record()
+        self._timed.append(e)
         return md2, midx
+
+    def collect_times(self):
+        """Fold the recorded CUDA events into ms_collective / ms_merge (call after a synchronize)."""
+        for e in self._timed:
+            self.ms_collective += e[0].elapsed_time(e[1])
+            self.ms_merge += e[1].elapsed_time(e[2])
+        n = len(self._timed)
+        self._timed = []
+        return n
 
     def predict(self, z_dev, k, method, y_dev, stream=None):
         """Weighted prediction for this rank's query slice (y_dev: all n responses, replicated)."""
