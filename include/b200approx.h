@@ -129,6 +129,11 @@ int b200_lshep_fit(b200_model* m, const double* f, int32_t r, double* a, double*
  * neighbour whose final weight is below 0.8.  One response column f (n); a (n,d), rw (n); *ier 0/1/2/3.
  * b200_lshep_predict then evaluates this fit. */
 int b200_lshep_fit_robust(b200_model* m, const double* f, double* a, double* rw, int32_t* ier);
+/* RIPPLE (linear_shepard.f95:474-665; exported by the Fortran module, not reachable from the shipped
+ * wrapper): least-median-style start from the best (M+1)-point subset of the neighbour chains, then the
+ * two IRLS stages.  One response column f (n), d <= 16; a (n,d), rw (n); *ier 0/1/2.
+ * b200_lshep_predict then evaluates this fit. */
+int b200_ripple_fit(b200_model* m, const double* f, double* a, double* rw, int32_t* ier);
 /* LSHEPVAL over a batch (linear_shepard.f95:365-472) with the radii scaled by
  * `radius`: out (q,r), ier (q,r) 0/1/2. */
 int b200_lshep_predict(b200_model* m, double radius, const double* z, int64_t q, double* out,

@@ -153,6 +153,16 @@ def lshep_fit_robust(x, f):
     return a, rw, ier, om
 
 
+def ripple(x, f):
+    """RIPPLE (linear_shepard.f95:474-665): (a (n,d), rw (n), ier)."""
+    x, f = _f64(x), _f64(f)
+    n, d = x.shape
+    a = np.ones((n, d))
+    rw = np.ones(n)
+    ier = lib().orc_ripple(_p(x), C.c_int64(n), d, _p(f), _p(a), _p(rw), C.c_void_p(_dgelss_ptr()))
+    return a, rw, ier
+
+
 def lshep_predict(x, f, a, rw, z):
     """LSHEPVAL over a batch: (values (q), ier (q))."""
     x, f, a, rw, z = _f64(x), _f64(f), _f64(a), _f64(rw), _f64(z)

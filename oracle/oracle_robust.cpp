@@ -205,4 +205,189 @@ int orc_lshep_fit_robust(const double* x, int64_t n, int d, const double* f, dou
   return ier;
 }
 
+// MAD as RIPPLE calls it (f95:602): MAD(RES(1:M+1), NP) -- the order statistics are taken at NP/2 (+1)
+// of an array that holds only M+1 values (QUANTILE works on the array it is handed, MAD's NMID on NP).
+static double mad_np(const double* res, int len, int np_) {
+  const double factor = 1.0 / 0.6745;
+  const int nmid = np_ / 2;
+  std::vector<double> dev(len);
+  if (np_ % 2 == 0) {
+    const double med = (orc_quantile(res, len, nmid) + orc_quantile(res, len, nmid + 1)) / 2.0;
+    for (int i = 0; i < len; ++i) dev[i] = std::fabs(res[i] - med);
+    return factor * (orc_quantile(dev.data(), len, nmid) + orc_quantile(dev.data(), len, nmid + 1)) / 2.0;
+  }
+  const double med = orc_quantile(res, len, nmid + 1);
+  for (int i = 0; i < len; ++i) dev[i] = std::fabs(res[i] - med);
+  return factor * orc_quantile(dev.data(), len, nmid + 1);
+}
+
+// RIPPLE (f95:474-665).  x (n,d) row-major, a (n,d) row-major, rw (n).  Returns IER 0 / 1 / 2.
+// The least-median-style start: for each of the NP chains of M+3 points grown through the neighbour
+// lists, every way of leaving out two of its points (never the first) gives an (M+1) x M system; the
+// one with the smallest residual component wins, then two IRLS stages on the neighbour set.
+int orc_ripple(const double* x, int64_t n, int d, const double* f, double* a, double* rw, dgelss_fn dgelss) {
+  if (d < 1 || n <= d + 3) return 1;                                             // :520-523
+  const int np2 = (int)std::min<int64_t>(n - 1, (3 * d + 5) / 2);               // :525
+  const int np0 = (int)std::min<int64_t>(n - 1, (3 * d + 1) / 2);               // :539
+  const int mc = d + 3;                                                          // chain length
+  std::vector<int64_t> S((size_t)n * np2);
+  double diam = 0.0;
+#pragma omp parallel
+  {
+    std::vector<Cand> c(np2);
+    double ldiam = 0.0;
+#pragma omp for schedule(dynamic, 16)
+    for (int64_t k = 0; k < n; ++k) {                                            // :526-537
+      double mx;
+      knn_one(x, n, d, x + k * d, np2, k, c.data(), &mx);
+      ldiam = std::max(ldiam, mx);
+      for (int i = 0; i < np2; ++i) S[(size_t)k * np2 + i] = c[i].i;
+    }
+#pragma omp critical
+    diam = std::max(diam, ldiam);
+  }
+  int ier = 0;
+  int64_t ier_k = -1;
+#pragma omp parallel
+  {
+    const int npmax = np0 + d + 1;
+    std::vector<int64_t> D((size_t)np0 * mc), keep(d + 1), best(d + 1);
+    std::vector<double> alpha_in((size_t)npmax * d), beta_in(npmax), alpha((size_t)(d + 1) * d), beta(d + 1), sigma(d),
+        res(npmax), omega(npmax), sol(d), dist(d + 1), rows((size_t)mc * d), rb(mc);
+    int lwork = 5 * d + 2 + 64 * (2 * d + 2);
+    std::vector<double> work(lwork);
+    int lier = 0;
+    int64_t lier_k = -1;
+#pragma omp for schedule(dynamic, 8)
+    for (int64_t k = 0; k < n; ++k) {
+      for (int i = 0; i < np0; ++i) D[(size_t)i * mc] = S[(size_t)k * np2 + i];  // :540
+      for (int j = 1; j < mc; ++j)                                               // :541-548 (J = j+1)
+        for (int i = 0; i < np0; ++i) {
+          const int64_t prev = D[(size_t)i * mc + j - 1];
+          for (int l = 0; l <= j; ++l) {                                         // L = 1..J: the last admissible L stays
+            const int64_t cand = S[(size_t)prev * np2 + l];
+            bool fresh = cand != k;
+            for (int t = 0; t < j && fresh; ++t) fresh = D[(size_t)i * mc + t] != cand;
+            if (fresh) D[(size_t)i * mc + j] = cand;
+          }
+        }
+      double lse = std::numeric_limits<double>::max();                           // :549
+      for (int j = 0; j < np0; ++j) {                                            // :550
+        for (int i = 0; i < mc; ++i) {                                           // :551-554
+          const int64_t p = D[(size_t)j * mc + i];
+          rb[i] = f[p] - f[k];
+          for (int t = 0; t < d; ++t) rows[(size_t)i * d + t] = x[p * d + t] - x[k * d + t];
+        }
+        for (int i = 2; i < mc; ++i)                                             // I = 3..M+3
+          for (int l = 1; l < i; ++l) {                                          // L = 2..I-1
+            int r = 0;
+            for (int t = 0; t < mc; ++t) {                                       // :559-564: rows L and I left out
+              if (t == l || t == i) continue;
+              keep[r] = D[(size_t)j * mc + t];
+              beta[r] = rb[t];
+              for (int cdim = 0; cdim < d; ++cdim) alpha[(size_t)cdim * (d + 1) + r] = rows[(size_t)t * d + cdim];
+              ++r;
+            }
+            int m_ = d + 1, n_ = d, nrhs = 1, lda = d + 1, ldb = d + 1, rank = 0, info = 0;
+            double rc = (d + 1) * DBL_EPSILON;                                   // :555
+            dgelss(&m_, &n_, &nrhs, alpha.data(), &lda, beta.data(), &ldb, sigma.data(), &rc, &rank, work.data(),
+                   &lwork, &info);                                               // :565-566
+            if (std::fabs(beta[d]) < lse) {                                      // :567-573
+              lse = std::fabs(beta[d]);
+              for (int t = 0; t < d; ++t) a[k * d + t] = beta[t];
+              best = keep;
+            }
+          }
+      }
+      // :577-583 the winning M+1 points, their squared distances and residuals
+      for (int i = 0; i <= d; ++i) {
+        const int64_t p = best[i];
+        beta_in[i] = f[p] - f[k];
+        double s2 = 0.0;
+        for (int t = 0; t < d; ++t) {
+          const double v = x[p * d + t] - x[k * d + t];
+          alpha_in[(size_t)t * npmax + i] = v;
+          s2 += v * v;
+        }
+        dist[i] = s2;
+      }
+      for (int i = 0; i <= d; ++i) {
+        double v = 0.0;
+        for (int t = 0; t < d; ++t) v += alpha_in[(size_t)t * npmax + i] * a[k * d + t];
+        res[i] = v - beta_in[i];
+      }
+      double mar = std::max(mad_np(res.data(), d + 1, np0), 1.0e-6);             // :584
+      int np_ = np0;
+      for (int i = 0; i < np0; ++i) {                                            // :585-588
+        const int64_t p = S[(size_t)k * np2 + i];
+        beta_in[i] = f[p] - f[k];
+        for (int t = 0; t < d; ++t) alpha_in[(size_t)t * npmax + i] = x[p * d + t] - x[k * d + t];
+      }
+      double rwk = 0.0;                                                          // :589
+      for (int t = 0; t < d; ++t) rwk += alpha_in[(size_t)t * npmax + np0 - 1] * alpha_in[(size_t)t * npmax + np0 - 1];
+      {  // :590 SORT(DIST, IDIST, M+1, M+1): stable insertion, ties keep the earlier entry
+        std::vector<int> ord(d + 1);
+        std::iota(ord.begin(), ord.end(), 0);
+        std::stable_sort(ord.begin(), ord.end(), [&](int p, int q) { return dist[p] < dist[q]; });
+        std::vector<double> ds(d + 1);
+        std::vector<int64_t> is(d + 1);
+        for (int i = 0; i <= d; ++i) {
+          ds[i] = dist[ord[i]];
+          is[i] = best[ord[i]];
+        }
+        for (int i = 0; i <= d; ++i) {                                           // :591-598
+          bool among = false;
+          for (int t = 0; t < np0; ++t) among = among || S[(size_t)k * np2 + t] == is[i];
+          if (ds[i] > rwk || (ds[i] == rwk && !among)) {
+            beta_in[np_] = f[is[i]] - f[k];
+            for (int t = 0; t < d; ++t) alpha_in[(size_t)t * npmax + np_] = x[is[i] * d + t] - x[k * d + t];
+            ++np_;
+          }
+        }
+      }
+      rw[k] = std::sqrt(rwk);                                                    // :599
+      // IRLS wants leading dimension = row count: compact the columns to np_ rows
+      std::vector<double> ain((size_t)np_ * d);
+      for (int t = 0; t < d; ++t)
+        for (int i = 0; i < np_; ++i) ain[(size_t)t * np_ + i] = alpha_in[(size_t)t * npmax + i];
+      for (int i = 0; i < np_; ++i) {                                            // :600
+        double v = 0.0;
+        for (int t = 0; t < d; ++t) v += ain[(size_t)t * np_ + i] * a[k * d + t];
+        res[i] = v - beta_in[i];
+      }
+      int e1 = orc_irls(d, np_, &mar, 5, 1, omega.data(), sol.data(), beta_in.data(), ain.data(), res.data(), dgelss);  // :601-604
+      if (e1 != 0) {
+        if (k >= lier_k) { lier = 2; lier_k = k; }                               // :605-607
+        continue;
+      }
+      for (int t = 0; t < d; ++t) a[k * d + t] = sol[t];                         // :609
+      e1 = orc_irls(d, np_, &mar, 5, 2, omega.data(), sol.data(), beta_in.data(), ain.data(), res.data(), dgelss);      // :611-614
+      if (e1 != 0) {
+        if (k >= lier_k) { lier = 2; lier_k = k; }                               // :615-617
+        continue;
+      }
+      for (int t = 0; t < d; ++t) a[k * d + t] = sol[t];                         // :619
+      for (int i = 0; i < np_; ++i) {                                            // :621-634
+        if (omega[i] < 0.8) {
+          auto len = [&](int r) {
+            double s2 = 0.0;
+            for (int t = 0; t < d; ++t) s2 += ain[(size_t)t * np_ + r] * ain[(size_t)t * np_ + r];
+            return std::sqrt(s2);
+          };
+          rw[k] = i == 0 ? len(0) / 2.0 : (len(i - 1) + len(i)) / 2.0;
+          break;
+        }
+      }
+    }
+#pragma omp critical
+    if (lier_k > ier_k) {
+      ier = lier;
+      ier_k = lier_k;
+    }
+  }
+  const double half = std::sqrt(diam) / 2.0;                                     // :636
+  for (int64_t k = 0; k < n; ++k) rw[k] = std::min(half, rw[k]);
+  return ier;
+}
+
 }  // extern "C"

@@ -286,6 +286,29 @@ def test_lshep_robust_fit_vs_oracle(ub, oracle, n, d):
     assert relerr(out, o_out) < RTOL
 
 
+@pytest.mark.parametrize("n,d", [(1500, 2), (2500, 5)])
+def test_ripple_fit_vs_oracle(ub, oracle, n, d):
+    """LSHEP(ripple=True): RIPPLE (linear_shepard.f95:474-665) against the oracle's restatement.  The start
+    is the argmin over ~NP (M+1)(M+2)/2 small least-squares residuals (QR here, DGELSS there) followed by ten
+    IRLS solves with discrete decisions; nodes whose choice sits on a rounding tie may pick another
+    subset, so all but a small fraction must agree to 1e-9 in the gradients and exactly in RW."""
+    x, z = synth(n, 200, d)
+    rng = np.random.default_rng(4)
+    f = fun(x) + 0.02 * rng.standard_normal(n)
+    f[::19] += 2.0
+    m = ub.LSHEP(ripple=True)
+    m.fit(x, f)
+    a_o, rw_o, ier_o = oracle.ripple(x, f)
+    got = m.a[0].T
+    scale = np.maximum(np.abs(a_o).max(axis=1, keepdims=True), 1e-3 * np.abs(a_o).max())
+    err = (np.abs(got - a_o) / scale).max(axis=1)
+    bad = (err > 1e-9) | (m.rw[0] != rw_o * 2)
+    assert bad.mean() < 0.01, (bad.sum(), err.max())
+    out = m(z)
+    o_out, _ = oracle.lshep_predict(x, f, got, m.rw[0], z)
+    assert relerr(out, o_out) < RTOL
+
+
 def test_standalone_shepard_voronoi_demo_sizes(ub, oracle):
     # the reference's own demos: test_plot(model, N=20) (shepard/__init__.py:53, voronoi/__init__.py:68)
     x, z = synth(20, 60, 2)

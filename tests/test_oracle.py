@@ -167,3 +167,23 @@ def test_oracle_robust_lshep_invariants(oracle):
     assert off(a0) > 0.15                                               # the plain fit is pulled by outlier neighbours
     assert off(a) < 0.75 * off(a0)                                      # the robust fit less often (NP = 5 leaves little redundancy)
     assert np.all(rw <= rw0 + 1e-15) and (rw < rw0).mean() > 0.1        # RW is cut at down-weighted neighbours
+
+
+def test_oracle_ripple_invariants(oracle):
+    """RIPPLE (linear_shepard.f95:474-665), parity unpinned: a noise-free plane is reproduced, gross outliers
+    pull far fewer nodes than the plain LSHEP fit, radii only shrink."""
+    rng = np.random.default_rng(0)
+    x = rng.random((800, 3))
+    g = np.array([1.0, 2.0, -3.0])
+    f = x @ g + 0.5
+    a, rw, ier = oracle.ripple(x, f)
+    assert np.abs(a - g).max() < 1e-10
+    f2 = f.copy()
+    f2[::13] += 4.0
+    a2, rw2, _ = oracle.ripple(x, f2)
+    a0, rw0, _, _ = oracle.lshep_fit(x, f2)
+    clean = np.ones(800, dtype=bool)
+    clean[::13] = False
+    off = lambda grads: (np.abs(grads[clean] - g).max(axis=1) > 1e-6).mean()
+    assert off(a0) > 0.2 and off(a2) < 0.05
+    assert np.all(rw2 <= rw0 * (1 + 1e-15))

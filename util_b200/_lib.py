@@ -42,6 +42,7 @@ _SIGNATURES = {
                                        c_i32p, c_dp, C.c_int32, c_dp]),
     "b200_lshep_fit": (C.c_int, [C.c_void_p, c_dp, C.c_int32, c_dp, c_dp, c_i32p]),
     "b200_lshep_fit_robust": (C.c_int, [C.c_void_p, c_dp, c_dp, c_dp, c_i32p]),
+    "b200_ripple_fit": (C.c_int, [C.c_void_p, c_dp, c_dp, c_dp, c_i32p]),
     "b200_lshep_predict": (C.c_int, [C.c_void_p, C.c_double, c_dp, C.c_int64, c_dp, c_i32p]),
     "b200_knn_dev": (C.c_int, [C.c_void_p, C.c_void_p, C.c_int64, C.c_int32, C.c_int64, C.c_void_p,
                                C.c_void_p, C.c_void_p]),
@@ -300,6 +301,15 @@ class Model:
             if mx <= cap:
                 return ids, wts, cnt, err, out
             cap = min(self.n, max(2 * cap, mx))
+
+    def ripple_fit(self, f):
+        """RIPPLE (linear_shepard.f95:474-665) for one response column: (a (1,n,d), rw (n), ier)."""
+        f = f64(f).reshape(self.n)
+        a = np.empty((1, self.n, self.d))
+        rw = np.empty(self.n)
+        ier = C.c_int32(0)
+        check(lib().b200_ripple_fit(self._h, ptr(f), ptr(a), ptr(rw), C.byref(ier)))
+        return a, rw, ier.value
 
     def lshep_fit(self, f, robust=False):
         f = f64(f).reshape(self.n, -1)

@@ -580,7 +580,7 @@ int b200_shepmod_predict(b200_model* m, const double* z, int64_t q, int32_t cap,
   return 0;
 }
 
-static int lshep_fit_host(b200_model* m, const double* f, int32_t r, double* a, double* rw, int32_t* ier, bool robust) {
+static int lshep_fit_host(b200_model* m, const double* f, int32_t r, double* a, double* rw, int32_t* ier, int mode) {
   B200_TRY(use(m));
   if (!f || r < 1) {
     set_error("b200_lshep_fit: bad arguments");
@@ -593,7 +593,7 @@ static int lshep_fit_host(b200_model* m, const double* f, int32_t r, double* a, 
   B200_TRY(m->out.reserve((size_t)r * n * 8));
   B200_CUDA(cudaMemcpy(m->out.p, ft.data(), (size_t)r * n * 8, cudaMemcpyHostToDevice));
   int e = 0;
-  B200_TRY(lshep_fit(m, m->out.as<double>(), r, 0, &e, robust));
+  B200_TRY(lshep_fit(m, m->out.as<double>(), r, 0, &e, mode));
   if (ier) *ier = e;
   if (e != 1) {
     if (a) B200_CUDA(cudaMemcpy(a, m->la.p, (size_t)r * n * m->d * 8, cudaMemcpyDeviceToHost));
@@ -604,11 +604,15 @@ static int lshep_fit_host(b200_model* m, const double* f, int32_t r, double* a, 
 }
 
 int b200_lshep_fit(b200_model* m, const double* f, int32_t r, double* a, double* rw, int32_t* ier) {
-  return lshep_fit_host(m, f, r, a, rw, ier, false);
+  return lshep_fit_host(m, f, r, a, rw, ier, 0);
 }
 
 int b200_lshep_fit_robust(b200_model* m, const double* f, double* a, double* rw, int32_t* ier) {
-  return lshep_fit_host(m, f, 1, a, rw, ier, true);
+  return lshep_fit_host(m, f, 1, a, rw, ier, 1);
+}
+
+int b200_ripple_fit(b200_model* m, const double* f, double* a, double* rw, int32_t* ier) {
+  return lshep_fit_host(m, f, 1, a, rw, ier, 2);
 }
 
 int b200_lshep_predict(b200_model* m, double radius, const double* z, int64_t q, double* out,

@@ -165,7 +165,7 @@ int shepmod_predict(b200_model* m, const double* z_dev, int64_t q, int cap, int3
                     double* wts_dev, int32_t* cnt_dev, int32_t* ier_dev, const double* y_dev, int r,
                     double* out_dev, cudaStream_t st);
 // lshep.cu
-int lshep_fit(b200_model* m, const double* f_dev, int r, cudaStream_t st, int* ier, bool robust = false);
+int lshep_fit(b200_model* m, const double* f_dev, int r, cudaStream_t st, int* ier, int mode = 0);
 int lshep_predict(b200_model* m, double radius, const double* z_dev, int64_t q, double* out_dev,
                   int32_t* ier_dev, cudaStream_t st);
 

@@ -380,6 +380,273 @@ lshep_robust_kernel(const double* __restrict__ x, int64_t n, int d, int np, cons
   if (lane == 0) rw[k] = rk;
 }
 
+// ---- RIPPLE (linear_shepard.f95:474-665): one block per node.
+// MAD as RIPPLE calls it (:584): order statistics at NP/2 (+1) of an array of `len` = M+1 values.
+__device__ double warp_mad_np(const double* res, double* tmp, int len, int np, int lane) {
+  const double factor = __ddiv_rn(1.0, 0.6745);
+  const int nmid = np / 2;
+  double med;
+  if (np % 2 == 0) med = __ddiv_rn(__dadd_rn(warp_kth(res, len, nmid, lane), warp_kth(res, len, nmid + 1, lane)), 2.0);
+  else med = warp_kth(res, len, nmid + 1, lane);
+  for (int i = lane; i < len; i += 32) tmp[i] = fabs(__dsub_rn(res[i], med));
+  __syncwarp();
+  double r;
+  if (np % 2 == 0)
+    r = __ddiv_rn(__dmul_rn(factor, __dadd_rn(warp_kth(tmp, len, nmid, lane), warp_kth(tmp, len, nmid + 1, lane))), 2.0);
+  else
+    r = __dmul_rn(factor, warp_kth(tmp, len, nmid + 1, lane));
+  __syncwarp();
+  return r;
+}
+
+constexpr int RP_MMAX = 16;            // dimension limit of the RIPPLE kernel (thread-private (M+1)x(M+1) systems)
+constexpr int RP_THREADS = 128;
+
+// S (n, np2): the np2 nearest other nodes of every node, ascending (the self-kNN's output).
+__global__ void __launch_bounds__(RP_THREADS)
+ripple_kernel(const double* __restrict__ x, int64_t n, int d, int np0, int np2, const int32_t* __restrict__ S,
+              const double* __restrict__ f, double* __restrict__ a, double* __restrict__ rw,
+              unsigned long long* __restrict__ last_ier) {
+  extern __shared__ double sm[];
+  const int mc = d + 3, m1 = d + 1, npmax = np0 + d + 1;
+  double* A = sm;                                 // [d+1][npmax] weighted system (work of warp_gelss)
+  double* V = A + (size_t)(d + 1) * npmax;        // [d][d]
+  double* wk = V + (size_t)d * d;                 // [2d]
+  double* sol = wk + 2 * d;                       // [d]
+  double* Ain = sol + d;                          // [d][npmax]
+  double* bin = Ain + (size_t)d * npmax;          // [npmax]
+  double* res = bin + npmax;                      // [npmax]
+  double* omega = res + npmax;                    // [npmax]
+  double* tmp = omega + npmax;                    // [npmax]
+  double* dist = tmp + npmax;                     // [m1]
+  double* rbest = dist + m1;                      // [RP_THREADS] best residual of each thread
+  double* csol = rbest + RP_THREADS;              // [d] the winning start solution
+  int* D = reinterpret_cast<int*>(csol + d);      // [np0][mc] chains
+  int* tbest = D + np0 * mc;                      // [RP_THREADS] its task number
+  int* keep = tbest + RP_THREADS;                 // [m1] points of the winning subset (then sorted by distance)
+  int* keep2 = keep + m1;                         // [m1]
+  __shared__ int s_np, s_fail;
+  const int t = threadIdx.x, lane = t & 31;
+  const int64_t k = blockIdx.x;
+  const int32_t* Sk = S + k * np2;
+  // ---- chains through the neighbour lists (:540-548)
+  if (t < np0) {
+    int* ch = D + t * mc;
+    ch[0] = Sk[t];
+    for (int j = 1; j < mc; ++j) {
+      const int32_t* Sp = S + (int64_t)ch[j - 1] * np2;
+      for (int l = 0; l <= j; ++l) {  // L = 1..J: the last admissible entry stays
+        const int cand = Sp[l];
+        bool fresh = cand != (int)k;
+        for (int u = 0; u < j && fresh; ++u) fresh = ch[u] != cand;
+        if (fresh) ch[j] = cand;
+      }
+    }
+  }
+  __syncthreads();
+  // ---- every chain, every pair of left-out points (never the first): (M+1) x M least squares by
+  // Householder QR in thread-private memory; the residual is the last component of Q^T b (:550-575)
+  const int per_chain = (mc - 2) * (mc - 1) / 2;  // pairs (L, I), 2 <= L < I <= M+3
+  const int ntask = np0 * per_chain;
+  double my_res = CUDART_INF;
+  int my_task = 0x7fffffff;
+  double my_sol[RP_MMAX];
+  const double fk = f[k];
+  for (int task = t; task < ntask; task += RP_THREADS) {
+    const int j = task / per_chain;
+    int rem = task - j * per_chain, I = 2, L = 1;
+    while (rem >= I - 1) {  // I = 3.. (0-based 2..), L = 2..I-1 (0-based 1..I-1)
+      rem -= I - 1;
+      ++I;
+    }
+    L = 1 + rem;
+    double T[(RP_MMAX + 1) * (RP_MMAX + 1)];  // rows r, columns 0..d-1 and the right-hand side in column d
+    const int* ch = D + j * mc;
+    int r = 0;
+    for (int u = 0; u < mc; ++u) {
+      if (u == L || u == I) continue;
+      const int p = ch[u];
+      for (int c = 0; c < d; ++c) T[r * m1 + c] = __dsub_rn(x[(int64_t)p * d + c], x[k * d + c]);
+      T[r * m1 + d] = __dsub_rn(f[p], fk);
+      ++r;
+    }
+    bool singular = false;
+    double rmax = 0.0;
+    for (int c = 0; c < d; ++c) {
+      double nrm2 = 0.0;
+      for (int i = c; i < m1; ++i) nrm2 = fma(T[i * m1 + c], T[i * m1 + c], nrm2);
+      const double nrm = sqrt(nrm2);
+      rmax = fmax(rmax, nrm);
+      if (!(nrm > (double)m1 * 2.220446049250313e-16 * rmax) || nrm == 0.0) {
+        singular = true;  // DGELSS would drop a singular value here; such subsets are not taken as starts
+        break;
+      }
+      const double a0 = T[c * m1 + c];
+      const double alpha = a0 >= 0 ? -nrm : nrm;
+      const double v0 = a0 - alpha;
+      double vv = v0 * v0;
+      for (int i = c + 1; i < m1; ++i) vv = fma(T[i * m1 + c], T[i * m1 + c], vv);
+      const double beta = vv > 0 ? 2.0 / vv : 0.0;
+      for (int cc = c + 1; cc <= d; ++cc) {
+        double sdot = v0 * T[c * m1 + cc];
+        for (int i = c + 1; i < m1; ++i) sdot = fma(T[i * m1 + c], T[i * m1 + cc], sdot);
+        sdot *= beta;
+        T[c * m1 + cc] -= sdot * v0;
+        for (int i = c + 1; i < m1; ++i) T[i * m1 + cc] -= sdot * T[i * m1 + c];
+      }
+      T[c * m1 + c] = alpha;
+    }
+    if (singular) continue;
+    const double rr = fabs(T[d * m1 + d]);
+    if (rr < my_res) {  // tasks arrive in increasing order: strict < keeps the first minimum (:567)
+      my_res = rr;
+      my_task = task;
+      for (int c = d - 1; c >= 0; --c) {
+        double sdot = T[c * m1 + d];
+        for (int cc = c + 1; cc < d; ++cc) sdot -= T[c * m1 + cc] * my_sol[cc];
+        my_sol[c] = sdot / T[c * m1 + c];
+      }
+    }
+  }
+  rbest[t] = my_res;
+  tbest[t] = my_task;
+  __syncthreads();
+  for (int o = RP_THREADS / 2; o > 0; o >>= 1) {
+    if (t < o) {
+      const double r2 = rbest[t + o];
+      const int t2 = tbest[t + o];
+      if (r2 < rbest[t] || (r2 == rbest[t] && t2 < tbest[t])) {
+        rbest[t] = r2;
+        tbest[t] = t2;
+      }
+    }
+    __syncthreads();
+  }
+  const int win = tbest[0];
+  if (win == my_task && win != 0x7fffffff) {
+    for (int c = 0; c < d; ++c) csol[c] = my_sol[c];
+    const int j = win / per_chain;
+    int rem = win - j * per_chain, I = 2;
+    while (rem >= I - 1) {
+      rem -= I - 1;
+      ++I;
+    }
+    const int L = 1 + rem;
+    int r = 0;
+    for (int u = 0; u < mc; ++u)
+      if (u != L && u != I) keep[r++] = D[j * mc + u];
+  }
+  if (t == 0) {
+    s_fail = win == 0x7fffffff;
+    s_np = np0;
+  }
+  __syncthreads();
+  if (t >= 32) return;  // the rest is one warp's work
+  if (s_fail) {         // every subset singular: no start (the reference would carry a truncated-SVD solution)
+    if (lane == 0) {
+      atomicMax(last_ier, ((unsigned long long)(k + 1) << 2) | 2ull);
+      rw[k] = sqrt(sqdist_seq(x + (int64_t)Sk[np0 - 1] * d, x + k * d, d));
+      for (int c = 0; c < d; ++c) a[k * d + c] = 0.0;
+    }
+    return;
+  }
+  // ---- residuals of the winning subset and the scale MAR (:577-584)
+  for (int i = lane; i < m1; i += 32) {
+    const int p = keep[i];
+    bin[i] = __dsub_rn(f[p], fk);
+    double s2 = 0.0;
+    for (int c = 0; c < d; ++c) {
+      const double v = __dsub_rn(x[(int64_t)p * d + c], x[k * d + c]);
+      Ain[(size_t)c * npmax + i] = v;
+      s2 = __dadd_rn(s2, __dmul_rn(v, v));
+    }
+    dist[i] = s2;
+  }
+  __syncwarp();
+  for (int i = lane; i < m1; i += 32) {
+    double v = 0.0;
+    for (int c = 0; c < d; ++c) v = __dadd_rn(v, __dmul_rn(Ain[(size_t)c * npmax + i], csol[c]));
+    res[i] = __dsub_rn(v, bin[i]);
+  }
+  __syncwarp();
+  double mar = fmax(warp_mad_np(res, tmp, m1, np0, lane), 1.0e-6);
+  // ---- the NP nearest nodes, plus the subset's points beyond the NP-th neighbour (:585-598)
+  for (int i = lane; i < np0; i += 32) {
+    const int p = Sk[i];
+    bin[i] = __dsub_rn(f[p], fk);
+    for (int c = 0; c < d; ++c) Ain[(size_t)c * npmax + i] = __dsub_rn(x[(int64_t)p * d + c], x[k * d + c]);
+  }
+  __syncwarp();
+  double rwk = 0.0;
+  for (int c = 0; c < d; ++c) rwk = __dadd_rn(rwk, __dmul_rn(Ain[(size_t)c * npmax + np0 - 1], Ain[(size_t)c * npmax + np0 - 1]));
+  // stable sort of the subset by distance (SORT, :590): rank by counting
+  for (int i = lane; i < m1; i += 32) {
+    int rk = 0;
+    for (int j = 0; j < m1; ++j) rk += (dist[j] < dist[i] || (dist[j] == dist[i] && j < i)) ? 1 : 0;
+    keep2[rk] = keep[i];
+    tmp[rk] = dist[i];
+  }
+  __syncwarp();
+  if (lane == 0) {
+    int np = np0;
+    for (int i = 0; i < m1; ++i) {
+      const int p = keep2[i];
+      bool among = false;
+      for (int u = 0; u < np0; ++u) among = among || Sk[u] == p;
+      if (tmp[i] > rwk || (tmp[i] == rwk && !among)) {
+        bin[np] = __dsub_rn(f[p], fk);
+        for (int c = 0; c < d; ++c) Ain[(size_t)c * npmax + np] = __dsub_rn(x[(int64_t)p * d + c], x[k * d + c]);
+        ++np;
+      }
+    }
+    s_np = np;
+  }
+  __syncwarp();
+  const int np = s_np;
+  double rk_out = sqrt(rwk);  // :599
+  // the helpers index columns with the row count as leading dimension: compact [d][npmax] -> [d][np]
+  if (np != npmax) {
+    for (int c = 1; c < d; ++c) {
+      double v[2];
+      int cntv = 0;
+      for (int i = lane; i < np; i += 32) v[cntv++] = Ain[(size_t)c * npmax + i];
+      __syncwarp();
+      cntv = 0;
+      for (int i = lane; i < np; i += 32) Ain[(size_t)c * np + i] = v[cntv++];
+      __syncwarp();
+    }
+  }
+  for (int c = lane; c < d; c += 32) sol[c] = csol[c];
+  __syncwarp();
+  warp_residuals(Ain, bin, sol, res, np, d, lane);  // :600
+  for (int j = lane; j < d; j += 32) a[k * d + j] = csol[j];
+  int e1 = warp_irls(A, V, wk, sol, Ain, bin, res, omega, &mar, 1, np, d, lane);  // :601-604
+  bool failed = e1 != 0;
+  if (!failed) {
+    for (int j = lane; j < d; j += 32) a[k * d + j] = sol[j];                     // :609
+    e1 = warp_irls(A, V, wk, sol, Ain, bin, res, omega, &mar, 2, np, d, lane);    // :611-614
+    failed = e1 != 0;
+    if (!failed)
+      for (int j = lane; j < d; j += 32) a[k * d + j] = sol[j];                   // :619
+  }
+  if (failed) {
+    if (lane == 0) atomicMax(last_ier, ((unsigned long long)(k + 1) << 2) | 2ull);  // :605-607, :615-617
+  } else {
+    for (int i = 0; i < np; ++i) {                                                // :621-634
+      if (omega[i] < 0.8) {
+        double l1 = 0.0, l0 = 0.0;
+        for (int c = 0; c < d; ++c) {
+          l1 = __dadd_rn(l1, __dmul_rn(Ain[(size_t)c * np + i], Ain[(size_t)c * np + i]));
+          if (i > 0) l0 = __dadd_rn(l0, __dmul_rn(Ain[(size_t)c * np + i - 1], Ain[(size_t)c * np + i - 1]));
+        }
+        rk_out = i == 0 ? __ddiv_rn(sqrt(l1), 2.0) : __ddiv_rn(__dadd_rn(sqrt(l0), sqrt(l1)), 2.0);
+        break;
+      }
+    }
+  }
+  if (lane == 0) rw[k] = rk_out;
+}
+
 // squared distance of every node to one anchor row; block max -> atomic max (as ordered uint64)
 __global__ void far_from_kernel(const double* __restrict__ x, int64_t n, int d,
                                 const double* __restrict__ anchor, unsigned long long* __restrict__ best) {
@@ -726,19 +993,26 @@ lshep_eval_kernel(const double* __restrict__ x, const float* __restrict__ x32, c
 
 }  // namespace
 
-int lshep_fit(b200_model* m, const double* f_dev, int r, cudaStream_t st, int* ier, bool robust) {
+int lshep_fit(b200_model* m, const double* f_dev, int r, cudaStream_t st, int* ier, int mode) {
+  // mode 0: LSHEP; 1: LSHEP with RLSHEP present (robust); 2: RIPPLE
+  const bool robust = mode == 1, ripple = mode == 2;
   const int64_t n = m->n;
   const int d = m->d;
   *ier = 0;
-  if (d < 1 || n <= d + 1) {  // :91-94
+  if (d < 1 || n <= d + (ripple ? 3 : 1)) {  // :91-94, :520-523
     *ier = 1;
     return 0;
+  }
+  if (ripple && d > RP_MMAX) {
+    set_error("ripple: dimension %d > %d unsupported", d, RP_MMAX);
+    return 1;
   }
   if (d > 64) {
     set_error("lshep_fit: dimension %d > 64 unsupported", d);
     return 1;
   }
-  const int np = (int)imin64(n - 1, (3 * d + 1) / 2);  // :98
+  const int np0 = (int)imin64(n - 1, (3 * d + 1) / 2);  // :98
+  const int np = ripple ? (int)imin64(n - 1, (3 * d + 5) / 2) : np0;  // RIPPLE's neighbour lists are longer (:525)
   B200_TRY(m->idx32.reserve((size_t)n * np * 4));
   B200_TRY(m->d2.reserve((size_t)n * np * 8));
   B200_TRY(m->rw.reserve((size_t)n * 8));
@@ -755,6 +1029,18 @@ int lshep_fit(b200_model* m, const double* f_dev, int r, cudaStream_t st, int* i
   unsigned long long* last_ier = reinterpret_cast<unsigned long long*>(m->flags.as<char>() + 32);
   for (int c = 0; c < r; ++c) {
     double* ac = m->la.as<double>() + (size_t)c * n * d;
+    if (ripple) {
+      const int npmax = np0 + d + 1, m1 = d + 1, mc = d + 3;
+      const size_t smem = ((size_t)(2 * d + 1) * npmax + (size_t)d * d + 4 * (size_t)d + 4 * (size_t)npmax + m1 + RP_THREADS) * 8 +
+                          ((size_t)np0 * mc + RP_THREADS + 2 * m1) * 4 + 64;
+      B200_CUDA(cudaFuncSetAttribute(ripple_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+      ripple_kernel<<<(unsigned)n, RP_THREADS, smem, st>>>(m->x, n, d, np0, np, m->idx32.as<int32_t>(),
+                                                          m->lf.as<double>() + (size_t)c * n, ac, m->rw.as<double>(), last_ier);
+      unit_slope_kernel<<<gb, 128, 0, st>>>(ac, n, d, m->la.as<double>() + (size_t)r * n * d + (size_t)c * n * (d + 1));
+      B200_CUDA(cudaGetLastError());
+      m->st.launches += 2;
+      continue;
+    }
     if (robust) {
       // RW depends on the response through the final IRLS weights; with several columns the last one stays,
       // as in the wrapper's per-column loop (linear_shepard/__init__.py:47-55 keeps one rw per column: the
@@ -836,7 +1122,7 @@ int lshep_fit(b200_model* m, const double* f_dev, int r, cudaStream_t st, int* i
     B200_CUDA(cudaGetLastError());
     m->st.launches += 2;
   }
-  if (robust) {
+  if (robust || ripple) {
     unsigned long long h_last = 0;
     B200_CUDA(cudaMemcpy(&h_last, last_ier, 8, cudaMemcpyDeviceToHost));
     h_flag = (int)(h_last & 3ull);

@@ -12,12 +12,13 @@ from .modified_shepard import TooFewDataPoints
 
 
 class LSHEP(Approximator):
-    def __init__(self, radius=2, device=None, robust=False):
+    def __init__(self, radius=2, device=None, robust=False, ripple=False):
         """`robust=True` (not in the reference's wrapper, which never passes RLSHEP to the Fortran,
         linear_shepard/__init__.py:36,53) selects the module's robust fit: IRLS with Huber and bisquare
-        weights, linear_shepard.f95:136-175."""
+        weights, linear_shepard.f95:136-175.  `ripple=True` selects the module's RIPPLE fit (:474-665)."""
         self.ierrors = {}
         self.robust = robust
+        self.ripple = ripple
         self.radius = radius
         self.x = self.f = self.a = self.rw = None
         self.device = device
@@ -29,7 +30,12 @@ class LSHEP(Approximator):
             raise TooFewDataPoints(*self.x.shape)
         if self.model is not None: self.model.close()
         self.model = _lib.Model(control_points, device=self.device)
-        a, rw, ier = self.model.lshep_fit(values, robust=self.robust)
+        if self.ripple:
+            if values.shape[1] != 1:
+                raise ValueError("RIPPLE takes one response column")
+            a, rw, ier = self.model.ripple_fit(values[:, 0])
+        else:
+            a, rw, ier = self.model.lshep_fit(values, robust=self.robust)
         self.fit_ier = ier
         r = values.shape[1]
         # per-column lists like the reference (:43-55); a[i] is (M, N), rw[i] already * radius
