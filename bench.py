@@ -195,6 +195,8 @@ def run_class_config(args, name):
     st = {s: m.model.stat(s) / args.steps for s in
           ("ms_prep", "ms_stage1", "ms_rerank", "ms_exact", "ms_weights", "launches", "uncertified")}
     ms_dev = st["ms_prep"] + st["ms_stage1"] + st["ms_rerank"] + st["ms_exact"] + st["ms_weights"]
+    if name == "c2":
+        ms_dev = st["ms_weights"]  # ShepMod's stage timer spans the whole predict, radius filter (ms_stage1) included
     pred = np.asarray(pred, dtype=float).reshape(q)
     # ---- roofline of the dominant predict kernel
     if name in ("c2", "c3"):
@@ -202,7 +204,7 @@ def run_class_config(args, name):
         # SURVEY 8d counts C2 as a contraction against the tensor peak and C3 as (5M+12) q n fp64 flops
         if name == "c2":
             flops, peak, unit_peak = 2.0 * q * n * d, pk["tensor"], "dense bf16 tensor peak (north_star assigns this stage to the tensor pipe)"
-            kern = "shepmod_eval_kernel"
+            kern = "knn_tc_kernel<THR> radius filter + shepmod_cand_kernel" if st["ms_stage1"] > 0 else "shepmod_eval_kernel"
         else:
             flops, peak, unit_peak = (5.0 * d + 12.0) * q * n, f64.value, "measured fp64 FMA rate (b200_debug_fma_peak)"
             kern = "lshep_eval_kernel"

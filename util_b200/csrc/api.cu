@@ -192,7 +192,7 @@ int b200_destroy(b200_model* m) {
   cudaSetDevice(m->device);
   cudaDeviceSynchronize();
   if (m->x) cudaFree(m->x);
-  DevBuf* bufs[] = {&m->tc.mu, &m->tc.img, &m->tc.nlo, &m->tc.perm, &m->tc.xs, &m->vor_g, &m->x32, &m->rw, &m->lf, &m->la, &m->y, &m->zq, &m->idx32, &m->d2,
+  DevBuf* bufs[] = {&m->tc.mu, &m->tc.img, &m->tc.nlo, &m->tc.perm, &m->tc.xs, &m->tc_sm.mu, &m->tc_sm.img, &m->tc_sm.nlo, &m->tc_sm.perm, &m->vor_g, &m->x32, &m->rw, &m->lf, &m->la, &m->y, &m->zq, &m->idx32, &m->d2,
                     &m->wts, &m->cnt, &m->err, &m->out, &m->part_d2, &m->part_idx, &m->cand,
                     &m->cand_meta, &m->zimg, &m->flags, &m->misc, &m->ids64};
   for (DevBuf* b : bufs) b->release();

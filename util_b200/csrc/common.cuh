@@ -87,6 +87,7 @@ struct b200_model {
   int sm_count = 148;
   double* x = nullptr;  // (n,d) row-major fp64 on the device
   b200::TcData tc;
+  b200::TcData tc_sm;  // images of the ShepMod radius filter (ordered and bounded by s^2 rw^2 - ||y||^2)
   // ShepMod / LSHEP fitted state
   b200::DevBuf rw, lf, la;  // rw (n); lshep f (r,n), a (r,n,d)
   int lshep_r = 0;
@@ -143,6 +144,8 @@ int merge_topk(const double* d2_parts, const int32_t* idx_parts, int parts, int6
                double* d2_out, int32_t* idx_out, cudaStream_t st);
 // knn_tc.cu
 bool tc_supported(const b200_model* m, int k);
+int shepmod_filter(b200_model* m, const double* z_dev, int64_t q, int32_t* cand_rows, int32_t* cand_cnt,
+                   cudaStream_t st);
 int knn_tc(b200_model* m, const double* z_dev, int64_t q, int k, int64_t self_offset,
            int32_t* idx_dev, double* d2_dev, cudaStream_t st);
 // weights.cu

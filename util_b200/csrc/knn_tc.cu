@@ -93,8 +93,12 @@ __global__ void maxabs_kernel(const double* __restrict__ x, int64_t n, int d, co
 // are nearly equal, which is what lets the filter use one norm bound per chunk.  Any order gives
 // the same exact result.  Key: fp32 bits of the squared norm (non-negative, so unsigned order =
 // numeric order).
+// rw != NULL (the ShepMod radius filter): the order is by c = s^2 rw^2 - ||y||^2 instead, the quantity
+// whose spread inside a chunk decides how tight the per-chunk bound is there; c may be negative, so the
+// float bits are mapped to an order-preserving unsigned key.
 __global__ void norm_key_kernel(const double* __restrict__ x, int64_t n, int d, const double* __restrict__ mu,
-                                double scale, uint32_t* __restrict__ key, int32_t* __restrict__ val) {
+                                double scale, const double* __restrict__ rw, uint32_t* __restrict__ key,
+                                int32_t* __restrict__ val) {
   const int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
   if (i >= n) return;
   double n2 = 0.0;
@@ -102,7 +106,13 @@ __global__ void norm_key_kernel(const double* __restrict__ x, int64_t n, int d, 
     const double yc = (x[i * d + j] - mu[j]) * scale;
     n2 = fma(yc, yc, n2);
   }
-  key[i] = __float_as_uint((float)n2);
+  if (rw) {
+    const double r = rw[i] * scale;
+    const uint32_t b = __float_as_uint((float)(r * r - n2));
+    key[i] = (b & 0x80000000u) ? ~b : (b | 0x80000000u);
+  } else {
+    key[i] = __float_as_uint((float)n2);
+  }
   val[i] = (int32_t)i;
 }
 
@@ -127,8 +137,8 @@ __global__ void iota_kernel(int32_t* __restrict__ v, int64_t n) {
 // Padding positions hold zero rows; the selection warps drop them by their position.
 __global__ void __launch_bounds__(128)
 data_img_kernel(const double* __restrict__ x, int64_t n, int d, int K, const double* __restrict__ mu, double scale,
-                const int32_t* __restrict__ perm, __half* __restrict__ img, float* __restrict__ nlo, int64_t npad,
-                unsigned long long* __restrict__ ymax_bits) {
+                const int32_t* __restrict__ perm, const double* __restrict__ rw, __half* __restrict__ img,
+                float* __restrict__ nlo, int64_t npad, unsigned long long* __restrict__ ymax_bits) {
   const int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;  // image position (npad is a multiple of 128)
   double nm = 0.0;
   float lo = NLO_PAD;
@@ -159,6 +169,11 @@ data_img_kernel(const double* __restrict__ x, int64_t n, int d, int K, const dou
     nm = sqrt(fmax(n2, n2h));
     // rounded towards zero with room for the fp64 rounding of n2 itself
     if (i < n) lo = __double2float_rd(n2 * (1.0 - 1e-12));
+    if (i < n && rw) {  // radius filter: the chunk bound is -max c, c = s^2 rw^2 - ||y||^2, rounded away from the data
+      const double r = rw[src] * scale;
+      const double r2 = r * r;
+      lo = __double2float_rd(-(r2 - n2) - 1e-12 * (r2 + n2));
+    }
   }
   for (int o = 16; o > 0; o >>= 1) {
     nm = fmax(nm, __shfl_xor_sync(0xffffffffu, nm, o));
@@ -238,6 +253,7 @@ struct KParams {
   int32_t* cand_idx;     // [qpad][32*U]
   int32_t* cand_cnt;     // [qpad]
   float* cand_tau;       // [qpad]
+  const float* row_thr;  // THR kernels: [qpad] fixed threshold of every query row
   float* dbg;            // optional [qpad][ntiles*128] raw tensor dots (tests only)
   unsigned long long* stats;  // optional [16] counters of the instrumented build (tuning only): events, events with a
                               // survivor, survivors, rank-merges, selection busy clk, queue-full clk, ready-wait clk,
@@ -399,7 +415,12 @@ __device__ __forceinline__ float take_entry(float* ls, int* li, float s, bool ok
 //   [2E, 3E)    selection: warp 2E + c owns rows c*32 .. c*32+31 and drains the queues of epilogue
 //               warps c (columns 0-63) and E + c (columns 64-127)
 //   3E          producer (bulk copies);  3E+1, 3E+2  MMA issuers (issuer j = accumulator stage j)
-template <int U, int HALVES, bool DBG>
+// THR = true turns the selection into a fixed-threshold filter (ShepMod's radius test): the row's
+// threshold is a constant handed in through p.row_thr, the per-chunk bound p.nlo is -max_j c_j of the
+// chunk (c_j = s^2 RW_j^2 - ||y_j||^2), and the selection warp appends every column with
+// dot + nlo < threshold to the row's list (ids only, no order); a row with more than 32*U such columns is
+// marked overflowed (count 32*U + 1) and left to the dense scan.
+template <int U, int HALVES, bool DBG, bool THR = false>
 __global__ void __launch_bounds__((HALVES * 12 + 3) * 32, 1) knn_tc_kernel(const KParams p) {
   constexpr int ROWS = HALVES * TILE;
   constexpr int E = HALVES * 4;
@@ -637,7 +658,7 @@ __global__ void __launch_bounds__((HALVES * 12 + 3) * 32, 1) knn_tc_kernel(const
         _Pragma("unroll") for (int i = 0; i < 32; ++i) o[i] = v[i];                                  \
       }                                                                                              \
     }                                                                                                \
-    const bool fl_ = chunk_min(v) < (tau - (nlc)) + fmaf(nlc, 4.76837158e-7f, at);                   \
+    const bool fl_ = chunk_min(v) < (tau - (nlc)) + fmaf(fabsf(nlc), 4.76837158e-7f, at);            \
     const unsigned fa_ = (!DBG || (p.mode & 3) == 0) ? __ballot_sync(0xffffffffu, fl_) : 0u;         \
     if (fa_) {                                                                                       \
       if (QE >= 32) {                                                                                \
@@ -709,7 +730,13 @@ __global__ void __launch_bounds__((HALVES * 12 + 3) * 32, 1) knn_tc_kernel(const
         ls0[e] = CUDART_INF_F;
         li0[e] = -1;
       }
-      tau0[lane] = CUDART_INF_F;
+      int* cnt0 = reinterpret_cast<int*>(ls0);  // THR: entries per row (the score plane is unused there)
+      if (THR) {
+        cnt0[lane] = 0;
+        tau0[lane] = p.row_thr[((int64_t)qb * ROWS + c * 32) + lane];
+      } else {
+        tau0[lane] = CUDART_INF_F;
+      }
       __syncwarp();
       if (lane == 0) ptx::st_release_shared(c_ready, (uint32_t)(b + 1));
       uint32_t spins = 0, nap = 32;
@@ -760,6 +787,19 @@ __global__ void __launch_bounds__((HALVES * 12 + 3) * 32, 1) knn_tc_kernel(const
               st_bulk += __popc(m) >= 6;
             }
             if (m == 0) continue;
+            if (THR) {
+              const int have = cnt0[rl];
+              const int add = __popc(m);
+              __syncwarp();
+              if (have + add <= W) {
+                if (ok) li0[(size_t)rl * W + have + __popc(m & ((1u << lane) - 1u))] = base + lane;
+                if (lane == 0) cnt0[rl] = have + add;
+              } else if (lane == 0) {
+                cnt0[rl] = W + 1;  // overflow: stays (W + 1 + anything > W)
+              }
+              __syncwarp();
+              continue;
+            }
             const float nt = take_entry<U>(ls0 + (size_t)rl * W, li0 + (size_t)rl * W, s, ok, m, base, tau, keep, lane);
             if (lane == 0 && nt != tau) ptx::st_volatile_shared_f32(ptx::smem_u32(&tau0[rl]), nt);
             __syncwarp();
@@ -782,6 +822,7 @@ __global__ void __launch_bounds__((HALVES * 12 + 3) * 32, 1) knn_tc_kernel(const
         }
         if (lane == r) my_cnt = nv;
       }
+      if (THR) my_cnt = min(cnt0[lane], W + 1);
       p.cand_cnt[q0 + lane] = my_cnt;
       p.cand_tau[q0 + lane] = tau0[lane];
       __syncwarp();
@@ -905,8 +946,10 @@ rerank_kernel(const double* __restrict__ x, int64_t n, int d, const double* __re
 // ------------------------------------------------------------------ host side
 namespace {
 
-int tc_prepare(b200_model* m, cudaStream_t st) {
-  TcData& t = m->tc;
+// rw == NULL: the kNN images (m->tc).  rw != NULL: the images of the ShepMod radius filter (m->tc_sm),
+// ordered and bounded by c = s^2 rw^2 - ||y||^2.
+int tc_prepare(b200_model* m, cudaStream_t st, const double* rw = nullptr) {
+  TcData& t = rw ? m->tc_sm : m->tc;
   if (t.ready) return 0;
   const int64_t n = m->n;
   const int d = m->d;
@@ -954,7 +997,7 @@ int tc_prepare(b200_model* m, cudaStream_t st) {
     B200_TRY(vals.reserve((size_t)n * 4 + 64));
     uint32_t* k_in = keys.as<uint32_t>();
     uint32_t* k_out = k_in + n;
-    tc::norm_key_kernel<<<nb, 256, 0, st>>>(m->x, n, d, t.mu.as<double>(), t.scale, k_in, vals.as<int32_t>());
+    tc::norm_key_kernel<<<nb, 256, 0, st>>>(m->x, n, d, t.mu.as<double>(), t.scale, rw, k_in, vals.as<int32_t>());
     size_t tmp_bytes = 0;
     B200_CUDA(cub::DeviceRadixSort::SortPairs(nullptr, tmp_bytes, k_in, k_out, vals.as<int32_t>(), t.perm.as<int32_t>(),
                                               (int)n, 0, 32, st));
@@ -970,7 +1013,7 @@ int tc_prepare(b200_model* m, cudaStream_t st) {
   B200_CUDA(cudaGetLastError());
   // a copy of the rows in image order for the re-rank (skipped for very large sets: it doubles the data)
   t.xs.release();
-  if ((size_t)n * d * 8 <= ((size_t)16 << 30)) {
+  if (!rw && (size_t)n * d * 8 <= ((size_t)16 << 30)) {
     B200_TRY(t.xs.reserve((size_t)n * d * 8));
     const int64_t tot = n * d;
     tc::gather_rows_kernel<<<(unsigned)((tot + 255) / 256), 256, 0, st>>>(m->x, n, d, t.perm.as<int32_t>(), t.xs.as<double>());
@@ -979,7 +1022,7 @@ int tc_prepare(b200_model* m, cudaStream_t st) {
   }
   B200_CUDA(cudaMemsetAsync(bits, 0, 8, st));
   tc::data_img_kernel<<<(unsigned)(npad / 128), 128, 0, st>>>(m->x, n, d, t.K, t.mu.as<double>(), t.scale, t.perm.as<int32_t>(),
-                                                              t.img.as<__half>(), t.nlo.as<float>(), npad, bits);
+                                                              rw, t.img.as<__half>(), t.nlo.as<float>(), npad, bits);
   B200_CUDA(cudaGetLastError());
   B200_CUDA(cudaMemcpyAsync(hb, bits, 8, cudaMemcpyDeviceToHost, st));
   B200_CUDA(cudaStreamSynchronize(st));
@@ -1027,6 +1070,17 @@ bool tc_config(int d, int k, int margin, bool self, int force_halves, TcConfig* 
   return false;
 }
 
+template <int HALVES>
+int launch_thr(b200_model* m, const tc::KParams& kp, const TcConfig& cfg, cudaStream_t st) {
+  const int threads = (HALVES * 12 + 3) * 32;
+  const int grid = std::min(kp.qblocks, m->sm_count);
+  auto kern = tc::knn_tc_kernel<2, HALVES, false, true>;
+  B200_CUDA(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)cfg.smem));
+  kern<<<grid, threads, cfg.smem, st>>>(kp);
+  B200_CUDA(cudaGetLastError());
+  return 0;
+}
+
 template <int U, int HALVES>
 int launch_tc(b200_model* m, const tc::KParams& kp, const TcConfig& cfg, bool dbg, cudaStream_t st) {
   const int threads = (HALVES * 12 + 3) * 32;
@@ -1045,6 +1099,106 @@ int launch_tc(b200_model* m, const tc::KParams& kp, const TcConfig& cfg, bool db
 }
 
 }  // namespace
+
+namespace tc {
+// Fixed threshold of each query row for the radius filter: a node K can only contain the query in its
+// radius if  dot_K + (-c_K) < E - ||x||^2  in scaled units, with E the bound on the tensor dot's error;
+// widened by the fp64 rounding of the centred form, rounded up to float.  Queries the fp16 image cannot
+// hold get +inf (everything is flagged, the row overflows and goes to the dense scan); padding rows -inf.
+__global__ void row_thr_kernel(const QMeta* __restrict__ meta, int64_t q, int64_t qpad, int d, double scale,
+                               double data_cmax, float* __restrict__ thr) {
+  const int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
+  if (i >= qpad) return;
+  if (i >= q) {
+    thr[i] = -CUDART_INF_F;
+    return;
+  }
+  const QMeta mq = meta[i];
+  if (!(mq.err < CUDART_INF)) {
+    thr[i] = CUDART_INF_F;
+    return;
+  }
+  const double cm = fmax(data_cmax, mq.cmax) * scale;
+  const double slack = 1e-7 * (fabs(mq.qn2) + mq.err) + 1e-9 * (double)d * cm * cm;
+  thr[i] = __double2float_ru(mq.err - mq.qn2 + slack);
+}
+__global__ void cand_rows_kernel(const int32_t* __restrict__ cand_pos, const int32_t* __restrict__ cand_cnt,
+                                 const int32_t* __restrict__ perm, int64_t q, int W, int64_t n, int32_t* __restrict__ rows,
+                                 int32_t* __restrict__ cnt_out) {
+  const int64_t e = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
+  if (e >= q * W) return;
+  const int64_t p = e / W;
+  const int j = (int)(e - p * W);
+  const int c = cand_cnt[p];
+  if (j == 0) cnt_out[p] = c;
+  const int pos = (j < c && c <= W) ? cand_pos[e] : -1;
+  rows[e] = (pos >= 0 && pos < n) ? perm[pos] : -1;
+}
+}  // namespace tc
+
+// ShepMod's radius test as a tensor-core filter: for every query the positions (fitted rows, through
+// perm) of all nodes that may hold it inside their radius -- a superset of {K : dist < RW(K)} -- at most
+// 64 per query; cand_cnt = 65 marks a query with more (or one the filter cannot handle).
+// cand_rows (q, 64) int32 fitted-row numbers, cand_cnt (q).
+int shepmod_filter(b200_model* m, const double* z_dev, int64_t q, int32_t* cand_rows, int32_t* cand_cnt_out,
+                   cudaStream_t st) {
+  B200_TRY(tc_prepare(m, st, m->rw.as<double>()));
+  const TcData& t = m->tc_sm;
+  TcConfig cfg;
+  // shape as for a 64-entry list (u = 2); keep is not used by the threshold kernel
+  if (!tc_config(m->d, 40, 0, false, 0, &cfg)) {
+    set_error("radius filter unsupported for d=%d", m->d);
+    return 1;
+  }
+  const int rows = cfg.halves * tc::TILE, W = 64;
+  const int qblocks = (int)((q + rows - 1) / rows);
+  const int64_t qpad = (int64_t)qblocks * rows;
+  B200_TRY(m->zimg.reserve((size_t)qpad * t.K * 2));
+  B200_TRY(m->cand.reserve((size_t)qpad * W * 4));
+  B200_TRY(m->cand_meta.reserve((size_t)qpad * (12 + sizeof(tc::QMeta)) + 64));
+  int32_t* cand_cnt = m->cand_meta.as<int32_t>();
+  float* cand_tau = reinterpret_cast<float*>(cand_cnt + qpad);
+  float* row_thr = cand_tau + qpad;
+  tc::QMeta* meta = reinterpret_cast<tc::QMeta*>(row_thr + qpad);
+  cudaEventRecord(m->ev3, st);  // (ev0 / ev1 belong to the caller's stage timer)
+  tc::query_img_kernel<<<(unsigned)((qpad + 127) / 128), 128, 0, st>>>(z_dev, q, m->d, t.K, t.mu.as<double>(), t.scale, t.ymax,
+                                                                        m->zimg.as<__half>(), qpad, meta);
+  tc::row_thr_kernel<<<(unsigned)((qpad + 255) / 256), 256, 0, st>>>(meta, q, qpad, m->d, t.scale, t.cmax, row_thr);
+  B200_CUDA(cudaGetLastError());
+  tc::KParams kp;
+  kp.a_img = m->zimg.as<__half>();
+  kp.b_img = t.img.as<__half>();
+  kp.nlo = t.nlo.as<float>();
+  kp.K = t.K;
+  kp.ntiles = (int)t.tiles;
+  kp.ncols = (int)m->n;
+  kp.qblocks = qblocks;
+  kp.slots = cfg.slots;
+  kp.qent = cfg.qent;
+  kp.parts = 1;
+  kp.keep = W;
+  kp.mode = 0;
+  kp.cand_idx = m->cand.as<int32_t>();
+  kp.cand_cnt = cand_cnt;
+  kp.cand_tau = cand_tau;
+  kp.row_thr = row_thr;
+  kp.dbg = nullptr;
+  kp.stats = nullptr;
+  if (cfg.halves == 2) B200_TRY(launch_thr<2>(m, kp, cfg, st));
+  else B200_TRY(launch_thr<1>(m, kp, cfg, st));
+  // positions -> fitted rows, compacted to the caller's (q, 64) layout
+  tc::cand_rows_kernel<<<(unsigned)((q * W + 255) / 256), 256, 0, st>>>(kp.cand_idx, cand_cnt, t.perm.as<int32_t>(), q, W, m->n,
+                                                                        cand_rows, cand_cnt_out);
+  B200_CUDA(cudaGetLastError());
+  cudaEventRecord(m->ev2, st);
+  B200_CUDA(cudaEventSynchronize(m->ev2));
+  float ms1 = 0;
+  cudaEventElapsedTime(&ms1, m->ev3, m->ev2);
+  m->st.ms_stage1 += ms1;  // also inside the caller's ms_weights
+  m->st.launches += 4;
+  m->st.tc_queries += q;
+  return 0;
+}
 
 bool tc_supported(const b200_model* m, int k) {
   TcConfig c;

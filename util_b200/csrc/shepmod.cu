@@ -243,6 +243,303 @@ shepmod_eval_kernel(const double* __restrict__ x, const float* __restrict__ x32,
   }
 }
 
+// SHEPMODVAL on a candidate list (modified_shepard.f95:83-176): one warp per query.  cand (q, 64) holds
+// fitted-row numbers of a SUPERSET of the nodes whose radius contains the query (the tensor-core radius
+// filter, knn_tc.cu); the exact test DIST < RW(K), the exact-hit rule (lowest K wins, :136-140), the
+// weights (:143) and their sums run on those rows in ascending node order, which is the order the
+// reference's scan meets them in -- nodes outside the list contribute nothing to any of it.  A query with
+// no node inside a radius (IER = 1: the M+1 nearest nodes take over, :147-170) or with an overflowed list
+// is appended to `redo` for the dense scan.
+__global__ void __launch_bounds__(256)
+shepmod_cand_kernel(const double* __restrict__ x, const double* __restrict__ rw, int d, const double* __restrict__ z,
+                    int64_t q, const int32_t* __restrict__ cand, const int32_t* __restrict__ cand_cnt, int cap,
+                    int32_t* __restrict__ ids, double* __restrict__ wts, int32_t* __restrict__ cnt,
+                    int32_t* __restrict__ ier, const double* __restrict__ y, int r, double* __restrict__ out,
+                    int32_t* __restrict__ redo, int32_t* __restrict__ redo_cnt) {
+  constexpr int W = 64;
+  __shared__ int s_row[8][W];
+  __shared__ double s_w[8][W];
+  const int w = threadIdx.x >> 5, lane = threadIdx.x & 31;
+  const int64_t p = (int64_t)blockIdx.x * 8 + w;
+  if (p >= q) return;
+  const int nc = cand_cnt[p];
+  if (nc > W || nc <= 0) {  // overflow, or certainly no radius contains the query
+    if (lane == 0) redo[atomicAdd(redo_cnt, 1)] = (int32_t)p;
+    return;
+  }
+  // rank the candidate rows ascending (each lane owns entries lane and lane + 32)
+  int mine[2];
+#pragma unroll
+  for (int u = 0; u < 2; ++u) {
+    const int j = lane + 32 * u;
+    mine[u] = j < nc ? cand[p * W + j] : 0x7fffffff;
+  }
+  int rank[2] = {0, 0};
+  for (int i = 0; i < nc; ++i) {
+    const int v = __shfl_sync(0xffffffffu, i < 32 ? mine[0] : mine[1], i & 31);
+#pragma unroll
+    for (int u = 0; u < 2; ++u) rank[u] += v < mine[u] ? 1 : 0;
+  }
+#pragma unroll
+  for (int u = 0; u < 2; ++u)
+    if (lane + 32 * u < nc) s_row[w][rank[u]] = mine[u];
+  __syncwarp();
+  // exact distances and weights, two sorted entries per lane
+  const double* zp = z + p * d;
+  int hit = 0x7fffffff;
+#pragma unroll
+  for (int u = 0; u < 2; ++u) {
+    const int j = lane + 32 * u;
+    double wv = -1.0;  // not inside the node's radius
+    if (j < nc) {
+      const int node = s_row[w][j];
+      const double a = sqdist_seq(zp, x + (int64_t)node * d, d);
+      const double dist = sqrt(a);  // :132
+      const double rk = rw[node];
+      if (dist < rk) {  // :134
+        if (__dsub_rn(rk, dist) == rk) hit = min(hit, node);  // :136
+        const double t = __ddiv_rn(__dsub_rn(rk, dist), __dmul_rn(rk, dist));  // :143
+        wv = __dmul_rn(t, t);
+      }
+    }
+    if (j < W) s_w[w][j] = wv;
+  }
+  for (int o = 16; o > 0; o >>= 1) hit = min(hit, __shfl_xor_sync(0xffffffffu, hit, o));
+  __syncwarp();
+  // An exact hit returns one-hot -- but only if the scan reaches it before... it always does: the scan
+  // stops at the FIRST node (lowest index) that is an exact hit, whatever came before (:137-139).
+  if (lane == 0) {
+    int c = 0;
+    int e = 0;
+    bool fallback = false;
+    int32_t* myid = ids ? ids + p * cap : nullptr;
+    double* myw = wts ? wts + p * cap : nullptr;
+    double acc_w[8];
+    int acc_id[8];
+    (void)acc_w;
+    (void)acc_id;
+    if (hit != 0x7fffffff) {
+      if (myid) myid[0] = hit;
+      if (myw) myw[0] = 1.0;
+      c = 1;
+      if (out)
+        for (int col = 0; col < r; ++col) out[p * r + col] = __dadd_rn(0.0, __dmul_rn(y[(int64_t)hit * r + col], 1.0));
+    } else {
+      double s = 0.0;  // SUM(WTS) in node order (:172)
+      int hits = 0;
+      for (int j = 0; j < nc; ++j)
+        if (s_w[w][j] >= 0.0) {
+          s = __dadd_rn(s, s_w[w][j]);
+          ++hits;
+        }
+      if (hits == 0) {
+        fallback = true;
+      } else {
+        for (int col = 0; out && col < r; ++col) out[p * r + col] = 0.0;
+        for (int j = 0; j < nc; ++j) {
+          if (s_w[w][j] < 0.0) continue;
+          const double wn = __ddiv_rn(s_w[w][j], s);
+          if (wn > 0) {  // a weight can underflow to zero; the wrapper drops those
+            const int node = s_row[w][j];
+            if (c < cap) {
+              if (myid) myid[c] = node;
+              if (myw) myw[c] = wn;
+            }
+            if (out && c < cap)
+              for (int col = 0; col < r; ++col)
+                out[p * r + col] = __dadd_rn(out[p * r + col], __dmul_rn(y[(int64_t)node * r + col], wn));  // base.py:169
+            ++c;
+          }
+        }
+      }
+    }
+    if (fallback) {
+      redo[atomicAdd(redo_cnt, 1)] = (int32_t)p;
+    } else {
+      cnt[p] = c;
+      ier[p] = e;
+    }
+  }
+}
+
+// The complete SHEPMODVAL for the queries listed in `sel`, one block per query: 256 nodes per step in
+// ascending order, every thread one node; the sequential parts -- hit list and SUM(WTS) in node order, the
+// replacement of the fallback slots by MINLOC (:147-158), the stop at the first exact hit -- are carried
+// out by thread 0 on the few nodes the step flags.  Used for the queries the radius filter hands back (no
+// node inside a radius, or more than 64 candidates), where a thread-per-query scan would leave the GPU
+// empty.  Square roots and divisions only where a test on the squared distance cannot decide.
+constexpr int SM_BT = 256;
+__global__ void __launch_bounds__(SM_BT)
+shepmod_block_kernel(const double* __restrict__ x, const double* __restrict__ rw, int64_t n, int d,
+                     const double* __restrict__ z, const int32_t* __restrict__ sel, int cap,
+                     int32_t* __restrict__ ids, double* __restrict__ wts, int32_t* __restrict__ cnt,
+                     int32_t* __restrict__ ier, const double* __restrict__ y, int r, double* __restrict__ out) {
+  __shared__ double s_z[SM_FB], s_D[SM_FB], s_a[SM_BT], s_rk[SM_BT];
+  __shared__ int s_DI[SM_FB];
+  __shared__ unsigned s_in[SM_BT / 32], s_cd[SM_BT / 32];
+  __shared__ int s_c, s_hit, s_J;
+  __shared__ double s_temp, s_sum;
+  const int t = threadIdx.x, lane = t & 31, wid = t >> 5;
+  const int64_t p = sel[blockIdx.x];
+  const int m1 = d + 1;
+  for (int j = t; j < d; j += SM_BT) s_z[j] = z[p * d + j];
+  for (int i = t; i < m1; i += SM_BT) {
+    s_D[i] = 0.0;   // :124-125
+    s_DI[i] = -1;
+  }
+  if (t == 0) {
+    s_c = 0;
+    s_hit = -1;
+    s_J = 0;
+    s_temp = 0.0;  // :126
+    s_sum = 0.0;
+  }
+  __syncthreads();
+  int32_t* myid = ids + p * cap;
+  double* myw = wts + p * cap;
+  for (int64_t base = 0; base < n; base += SM_BT) {
+    const int64_t k = base + t;
+    const int c0 = s_c;
+    const double temp0 = s_temp;
+    if (s_hit >= 0) break;  // uniform: written before the last barrier
+    double a = CUDART_INF, rk = 0.0;
+    if (k < n) {
+      a = sqdist_seq(s_z, x + k * d, d);
+      rk = rw[k];
+    }
+    const double r2 = rk * rk;
+    bool inside = false;
+    if (k < n && a < r2 * (1.0 + 1e-14)) inside = a < r2 * (1.0 - 1e-14) ? true : sqrt(a) < rk;  // :134
+    const double lim2 = temp0 > 0.0 ? (1.0 / temp0) * (1.0 / temp0) * (1.0 + 1e-12) : CUDART_INF;
+    const bool maybe = c0 == 0 && k < n && !inside && a < lim2;  // may enter the fallback slots: 1/dist > temp
+    const unsigned mi = __ballot_sync(0xffffffffu, inside), mc = __ballot_sync(0xffffffffu, maybe);
+    if (lane == 0) {
+      s_in[wid] = mi;
+      s_cd[wid] = mc;
+    }
+    s_a[t] = a;
+    s_rk[t] = rk;
+    if (!__syncthreads_or(inside || maybe)) continue;
+    if (t == 0) {
+      int c = s_c, J = s_J, hit = -1;
+      double temp = s_temp, sum = s_sum;
+      for (int wq = 0; wq < SM_BT / 32 && hit < 0; ++wq) {
+        unsigned both = s_in[wq] | s_cd[wq];
+        while (both) {
+          const int b = __ffs(both) - 1;
+          both &= both - 1;
+          const int i = wq * 32 + b;
+          const double dist = sqrt(s_a[i]);  // :132
+          const double rki = s_rk[i];
+          if ((s_in[wq] >> b) & 1u) {
+            if (__dsub_rn(rki, dist) == rki) {  // :136-140
+              hit = (int)(base + i);
+              break;
+            }
+            const double u = __ddiv_rn(__dsub_rn(rki, dist), __dmul_rn(rki, dist));  // :143
+            const double wv = __dmul_rn(u, u);
+            if (c < cap) {
+              myid[c] = (int)(base + i);
+              myw[c] = wv;
+            }
+            sum = __dadd_rn(sum, wv);
+            ++c;
+          } else if (c == 0) {
+            const double wv = __ddiv_rn(1.0, dist);  // :150
+            if (wv > temp) {                         // :152-158
+              s_D[J] = wv;
+              s_DI[J] = (int)(base + i);
+              int jm = 0;
+              double dm = s_D[0];
+              for (int u2 = 1; u2 < m1; ++u2)
+                if (s_D[u2] < dm) { dm = s_D[u2]; jm = u2; }  // MINLOC: first minimum
+              J = jm;
+              temp = dm;
+            }
+          }
+        }
+      }
+      s_c = c;
+      s_J = J;
+      s_temp = temp;
+      s_sum = sum;
+      s_hit = hit;
+    }
+    __syncthreads();
+  }
+  __syncthreads();
+  if (t != 0) return;
+  int c = s_c;
+  const int hit = s_hit;
+  const double s = s_sum;
+  int e = 0;
+  if (hit >= 0) {  // one-hot (:137-139)
+    myid[0] = hit;
+    myw[0] = 1.0;
+    c = 1;
+  } else if (c == 0) {  // :163-170 original Shepard on the M+1 kept nodes
+    e = 1;
+    double sd = 0.0;
+    for (int i = 0; i < m1; ++i) s_D[i] = __dmul_rn(s_D[i], s_D[i]);
+    for (int i = 0; i < m1; ++i) sd = __dadd_rn(sd, s_D[i]);
+    for (int i = 1; i < m1; ++i) {  // ascending node index, as `base[wts > 0]` returns them
+      const double dv = s_D[i];
+      const int iv = s_DI[i];
+      int j = i;
+      while (j > 0 && s_DI[j - 1] > iv) { s_D[j] = s_D[j - 1]; s_DI[j] = s_DI[j - 1]; --j; }
+      s_D[j] = dv;
+      s_DI[j] = iv;
+    }
+    for (int i = 0; i < m1; ++i) {
+      if (s_DI[i] < 0) continue;
+      const double wn = __ddiv_rn(s_D[i], sd);
+      if (wn > 0) {
+        if (c < cap) { myid[c] = s_DI[i]; myw[c] = wn; }
+        ++c;
+      }
+    }
+  } else {  // :172
+    const int lim = c < cap ? c : cap;
+    int kept = 0;
+    for (int i = 0; i < lim; ++i) {
+      const double wn = __ddiv_rn(myw[i], s);
+      if (wn > 0) {
+        myid[kept] = myid[i];
+        myw[kept] = wn;
+        ++kept;
+      }
+    }
+    if (c <= cap) c = kept;
+  }
+  cnt[p] = c;
+  ier[p] = e;
+  if (out) {
+    const int lim = c < cap ? c : cap;
+    for (int col = 0; col < r; ++col) {
+      double acc = 0.0;  // base.py:169
+      for (int i = 0; i < lim; ++i) acc = __dadd_rn(acc, __dmul_rn(y[(int64_t)myid[i] * r + col], myw[i]));
+      out[p * r + col] = acc;
+    }
+  }
+}
+
+// rows listed in `sel` of (q, w) arrays gathered to / scattered from a compact (ns, w) array
+__global__ void gather_rows_f64_kernel(const double* __restrict__ src, const int32_t* __restrict__ sel, int ns, int w,
+                                       double* __restrict__ dst) {
+  const int64_t e = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
+  if (e >= (int64_t)ns * w) return;
+  const int i = (int)(e / w), j = (int)(e - (int64_t)i * w);
+  dst[e] = src[(int64_t)sel[i] * w + j];
+}
+template <class T>
+__global__ void scatter_rows_kernel(const T* __restrict__ src, const int32_t* __restrict__ sel, int ns, int w,
+                                    T* __restrict__ dst) {
+  const int64_t e = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
+  if (e >= (int64_t)ns * w) return;
+  const int i = (int)(e / w), j = (int)(e - (int64_t)i * w);
+  dst[(int64_t)sel[i] * w + j] = src[e];
+}
+
 }  // namespace
 
 int data_absmax(b200_model* m, cudaStream_t st, double* out) {
@@ -298,6 +595,10 @@ int shepmod_fit(b200_model* m, cudaStream_t st, int* ier) {
   return 0;
 }
 
+static int shepmod_dense(b200_model* m, const double* z_dev, int64_t q, int cap, int32_t* ids_dev,
+                         double* wts_dev, int32_t* cnt_dev, int32_t* ier_dev, const double* y_dev, int r,
+                         double* out_dev, cudaStream_t st);
+
 int shepmod_predict(b200_model* m, const double* z_dev, int64_t q, int cap, int32_t* ids_dev,
                     double* wts_dev, int32_t* cnt_dev, int32_t* ier_dev, const double* y_dev, int r,
                     double* out_dev, cudaStream_t st) {
@@ -306,6 +607,51 @@ int shepmod_predict(b200_model* m, const double* z_dev, int64_t q, int cap, int3
     return 1;
   }
   if (q == 0) return 0;
+  const int d = m->d;
+  if (d + 1 > SM_FB) {
+    set_error("shepmod_predict: dimension %d > %d unsupported", d, SM_FB - 1);
+    return 1;
+  }
+  if (cap < d + 1) {
+    set_error("shepmod_predict: cap=%d must be at least M+1=%d", cap, d + 1);
+    return 1;
+  }
+  // Large problems: the radius test DIST < RW(K) is first run as a tensor-core filter (the same fused
+  // contraction as the kNN path with a per-node threshold), then SHEPMODVAL's arithmetic runs on the few
+  // candidate nodes of each query; the dense scan below takes what the filter hands back.
+  const bool filter = m->knn_path != B200_PATH_EXACT && tc_supported(m, 40) && (double)m->n * (double)q >= 2.5e8 &&
+                      m->n >= 4096 && d >= 5;
+  if (!filter) return shepmod_dense(m, z_dev, q, cap, ids_dev, wts_dev, cnt_dev, ier_dev, y_dev, r, out_dev, st);
+  B200_TRY(m->part_idx.reserve((size_t)q * 64 * 4));
+  B200_TRY(m->misc.reserve((size_t)q * 8 + 64));
+  int32_t* cand_rows = m->part_idx.as<int32_t>();
+  int32_t* cand_cnt = m->misc.as<int32_t>();
+  int32_t* redo = cand_cnt + q;
+  int32_t* redo_cnt = redo + q;
+  B200_TRY(shepmod_filter(m, z_dev, q, cand_rows, cand_cnt, st));
+  B200_CUDA(cudaMemsetAsync(redo_cnt, 0, 4, st));
+  shepmod_cand_kernel<<<(unsigned)((q + 7) / 8), 256, 0, st>>>(m->x, m->rw.as<double>(), d, z_dev, q, cand_rows, cand_cnt, cap,
+                                                             ids_dev, wts_dev, cnt_dev, ier_dev, y_dev, r,
+                                                             y_dev ? out_dev : nullptr, redo, redo_cnt);
+  B200_CUDA(cudaGetLastError());
+  m->st.launches += 1;
+  int nr = 0;
+  B200_CUDA(cudaMemcpyAsync(&nr, redo_cnt, 4, cudaMemcpyDeviceToHost, st));
+  B200_CUDA(cudaStreamSynchronize(st));
+  m->st.uncertified += nr;
+  if (nr > 0) {
+    // queries the filter hands back (no radius holds them, or more than 64 candidates): the full scan
+    shepmod_block_kernel<<<(unsigned)nr, SM_BT, 0, st>>>(m->x, m->rw.as<double>(), m->n, d, z_dev, redo, cap, ids_dev, wts_dev,
+                                                         cnt_dev, ier_dev, y_dev, r, y_dev ? out_dev : nullptr);
+    B200_CUDA(cudaGetLastError());
+    m->st.launches += 1;
+  }
+  return 0;
+}
+
+static int shepmod_dense(b200_model* m, const double* z_dev, int64_t q, int cap, int32_t* ids_dev,
+                         double* wts_dev, int32_t* cnt_dev, int32_t* ier_dev, const double* y_dev, int r,
+                         double* out_dev, cudaStream_t st) {
   const int d = m->d;
   if (d + 1 > SM_FB) {
     set_error("shepmod_predict: dimension %d > %d unsupported", d, SM_FB - 1);
