@@ -504,16 +504,22 @@ def main():
         flops = 2.0 * ql * nloc * d  # algorithmic: the -2 Z X^T term only
         s1 = stats["ms_stage1"]
         tensor_path = s1 > 0
-        traffic = None
-        tp = os.path.join(ROOT, "profiles", "r01", "knn_tc_traffic.json")
-        if os.path.exists(tp) and G == 1:
-            tj = json.load(open(tp))
-            if tj.get("config") == args.config:
-                traffic = tj["dram_bytes_read"] + tj["dram_bytes_write"]  # per launch, from one ncu --set full capture
+        # DRAM bytes per launch of the current kernel: not measurable outside a profiler, so it is the figure of
+        # the newest committed `ncu --set full` capture of this config (profiles/rNN/knn_tc_traffic.json names it)
+        traffic, traffic_src = None, None
+        for rd in sorted((p for p in os.listdir(os.path.join(ROOT, "profiles")) if p.startswith("r")), reverse=True):
+            tp = os.path.join(ROOT, "profiles", rd, "knn_tc_traffic.json")
+            if os.path.exists(tp) and G == 1:
+                tj = json.load(open(tp))
+                if tj.get("config") == args.config:
+                    traffic = tj["dram_bytes_read"] + tj["dram_bytes_write"]
+                    traffic_src = f"profiles/{rd}/knn_tc_traffic.json"
+                break
         if tensor_path:
             ach = flops / (s1 * 1e-3) / 1e12
             roof = {"bound": "tensor", "kernel": "knn_tc_kernel", "achieved": ach, "peak": pk["tensor"],
                     "unit": "TFLOP/s", "frac": ach / pk["tensor"], "traffic": traffic,
+                    "traffic_source": traffic_src,
                     "peak_source": pk["src"] + " bf16_tflops_sustained", "ms_per_launch": s1,
                     "algorithmic_flops_per_launch": flops}
         else:

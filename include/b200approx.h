@@ -66,7 +66,9 @@ int b200_set_values(b200_model* m, const double* y, int32_t r);
  * the batched form of `self.tree.query(pt[None,:], k=..., return_distance=False)`
  * (nearest_neighbor/__init__.py:75-76).  idx (q,k); d2 (q,k) squared distances
  * (may be NULL).  self_offset >= 0 excludes data row self_offset+p for query p
- * (the "other nodes" scans of SHEPMOD / LSHEP: modified_shepard.f95:45-53). */
+ * (the "other nodes" scans of SHEPMOD / LSHEP: modified_shepard.f95:45-53).
+ * A NaN or infinite query coordinate fails the call ("query points contain NaN or infinity"),
+ * here and in every entry point that searches neighbours, as BallTree.query raises for such input. */
 int b200_knn(b200_model* m, const double* z, int64_t q, int32_t k, int64_t self_offset,
              int64_t* idx, double* d2);
 

@@ -134,6 +134,18 @@ def test_nn_exact_hit_and_edge_cases(ub, oracle):
     mk.fit(x, y)
     with pytest.raises(ValueError):
         mk.predict(z)
+    # NaN / infinite queries are refused on both search paths, as BallTree.query refuses them
+    for bad in (np.nan, np.inf):
+        zb = z.copy()
+        zb[7, 1] = bad
+        with pytest.raises(ValueError):
+            m.predict(zb)
+    xb, zb = synth(20000, 20000, 8)
+    mb = ub.NearestNeighbor(k=4)
+    mb.fit(xb, fun(xb))
+    zb[12345, 3] = np.nan
+    with pytest.raises(ValueError):
+        mb.predict(zb)
     # duplicated fit points make the Voronoi sub-model raise, as voronoi/__init__.py:56-57 does
     xd = np.vstack([x, x[:5]])
     mv = ub.NearestNeighbor(k=8, method=ub.Voronoi)

@@ -76,7 +76,8 @@ def test_tensor_accumulation_error_bound(L):
 @pytest.mark.parametrize("n,q,d,k", [(20000, 1000, 64, 16), (30000, 700, 16, 17), (9000, 513, 8, 1),
                                      (12000, 300, 32, 33), (5000, 260, 10, 15), (40000, 300, 3, 8),
                                      (8000, 300, 100, 5), (6000, 130, 125, 3),  # K = 112 / 128: generic K loop, one half per CTA
-                                     (5000, 260, 10, 40), (7000, 200, 20, 100)])  # 64- and 128-entry candidate lists
+                                     (5000, 260, 10, 40), (7000, 200, 20, 100),  # 128-entry lists: append-and-trim / sorted
+                                     (15000, 400, 24, 24), (50000, 600, 32, 64)])  # 64-entry append lists; C4's shape
 def test_tensor_knn_bit_exact(L, oracle, n, q, d, k):
     x, z = synth(n, q, d)
     m = L.Model(x)
@@ -139,6 +140,14 @@ def test_tensor_knn_hard_inputs(L, oracle):
     idx, d2 = m.knn(z, 10)
     oi, od = oracle.knn(x, z, 10)
     assert np.array_equal(idx, oi) and np.array_equal(d2, od)
+    # the same with the unsorted append-and-trim lists (k = 24: 64 entries, k = 48: 128): tied scores at
+    # the trim threshold are dropped together and the certificate must notice when too few are left
+    for k in (24, 48):
+        m = L.Model(x)
+        m.set_option("knn_path", L.PATH_TENSOR)
+        idx, d2 = m.knn(z, k)
+        oi, od = oracle.knn(x, z, k)
+        assert np.array_equal(idx, oi) and np.array_equal(d2, od)
     # queries far outside the data (fp16 overflow guard) and n not a multiple of 128
     x, z = synth(4999, 130, 5)
     z[:5] *= 1e6

@@ -71,6 +71,10 @@ class B200Error(RuntimeError):
     pass
 
 
+class NonFiniteInput(B200Error, ValueError):
+    """NaN or infinity in the query points; sklearn's BallTree.query raises ValueError for the same input."""
+
+
 def lib():
     """Load the shared library; fail loudly when it has not been built."""
     global _lib
@@ -90,7 +94,8 @@ def lib():
 
 def check(rc):
     if rc != 0:
-        raise B200Error(lib().b200_last_error().decode("utf-8", "replace") or f"libb200approx error {rc}")
+        text = lib().b200_last_error().decode("utf-8", "replace") or f"libb200approx error {rc}"
+        raise (NonFiniteInput if "NaN or infinity" in text else B200Error)(text)
 
 
 def f64(a):

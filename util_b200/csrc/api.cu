@@ -100,10 +100,39 @@ int resolve_y(b200_model* m, const double* y, int32_t* r, bool want_out, bool* h
   return 0;
 }
 
+// Sets *flag when any query coordinate is NaN or infinite (grid-stride over the q*d doubles).
+__global__ void nonfinite_kernel(const double* __restrict__ z, int64_t count, int32_t* __restrict__ flag) {
+  bool bad = false;
+  for (int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; i < count; i += (int64_t)gridDim.x * blockDim.x)
+    bad |= !isfinite(z[i]);
+  if (__syncthreads_or(bad) && threadIdx.x == 0) *flag = 1;
+}
+
 }  // namespace
+
+// sklearn's BallTree.query (the reference's search, nearest_neighbor/__init__.py:75) raises on NaN or
+// infinite input; so does every neighbour search here, instead of returning index -1 rows.
+int reject_nonfinite(b200_model* m, const double* z_dev, int64_t q, cudaStream_t st) {
+  B200_TRY(m->flags.reserve(256));
+  int32_t* flag = m->flags.as<int32_t>() + 6;
+  B200_CUDA(cudaMemsetAsync(flag, 0, 4, st));
+  const int64_t count = q * m->d;
+  const unsigned blocks = (unsigned)std::min<int64_t>((count + 1023) / 1024, (int64_t)m->sm_count * 8);
+  nonfinite_kernel<<<blocks, 256, 0, st>>>(z_dev, count, flag);
+  B200_CUDA(cudaGetLastError());
+  int h = 0;
+  B200_CUDA(cudaMemcpyAsync(&h, flag, 4, cudaMemcpyDeviceToHost, st));
+  B200_CUDA(cudaStreamSynchronize(st));
+  if (h) {
+    set_error("query points contain NaN or infinity");
+    return 1;
+  }
+  return 0;
+}
 
 int knn_dispatch(b200_model* m, const double* z_dev, int64_t q, int k, int64_t self_offset,
                  int32_t* idx_dev, double* d2_dev, cudaStream_t st) {
+  if (q > 0) B200_TRY(reject_nonfinite(m, z_dev, q, st));
   bool tensor = false;
   if (m->knn_path == B200_PATH_TENSOR) {
     if (!tc_supported(m, k)) {

@@ -407,6 +407,85 @@ __device__ __forceinline__ float take_entry(float* ls, int* li, float s, bool ok
   return ls[e];
 }
 
+// ---- append-and-trim lists (U >= 2, keep <= 32U - 16).  A sorted insert into a 64- or 128-entry list costs
+// a warp ~150 clk per survivor; here survivors are appended unsorted and, when the list is full, the row is
+// cut to the entries below its keep-th smallest score T (one bisection on the score bits), T becoming the
+// row's threshold.  Everything dropped or refused has score >= the threshold of that moment >= the final
+// one, which is all the certificate needs; the threshold is just up to 32U - keep appends staler.
+__device__ __forceinline__ uint32_t score_key(float v) {  // order-preserving map float -> uint32
+  const uint32_t b = __float_as_uint(v);
+  return b ^ ((uint32_t)((int32_t)b >> 31) | 0x80000000u);
+}
+__device__ __forceinline__ float key_score(uint32_t k) {
+  return __uint_as_float((k & 0x80000000u) ? (k ^ 0x80000000u) : ~k);
+}
+
+// Cut the row's first `have` entries to those below the keep-th smallest (have >= keep); returns that score.
+template <int U>
+__device__ __forceinline__ float trim_row(float* ls, int* li, int keep, int& have, int lane) {
+  uint32_t key[U];
+  int id[U];
+#pragma unroll
+  for (int u = 0; u < U; ++u) {
+    const int e = u * 32 + lane;
+    key[u] = e < have ? score_key(ls[e]) : 0xffffffffu;
+    id[u] = li[e];
+  }
+  uint32_t T = 0;  // max T with #(key < T) < keep  ==  the keep-th smallest key
+  for (int bit = 31; bit >= 0; --bit) {
+    const uint32_t cand = T | (1u << bit);
+    int c = 0;
+#pragma unroll
+    for (int u = 0; u < U; ++u) c += __popc(__ballot_sync(0xffffffffu, key[u] < cand));
+    if (c < keep) T = cand;
+  }
+  __syncwarp();
+  int pos = 0;
+  const unsigned lt = (1u << lane) - 1u;
+#pragma unroll
+  for (int u = 0; u < U; ++u) {
+    const bool kf = key[u] < T;
+    const unsigned km = __ballot_sync(0xffffffffu, kf);
+    if (kf) {
+      const int r = pos + __popc(km & lt);
+      ls[r] = key_score(key[u]);
+      li[r] = id[u];
+    }
+    pos += __popc(km);
+  }
+  __syncwarp();
+  have = pos;
+  return key_score(T);
+}
+
+// One queue entry -> the row's unsorted list; `have` = entries in it (updated).  Returns the threshold.
+template <int U>
+__device__ __forceinline__ float take_append(float* ls, int* li, float s, unsigned m, int base, float tau, int keep,
+                                             int& have, int lane) {
+  constexpr int W = 32 * U;
+  const unsigned lt = (1u << lane) - 1u;
+  for (;;) {
+    const int room = W - have;
+    const int r = __popc(m & lt);
+    const bool mine = (m >> lane) & 1u;
+    if (mine && r < room) {
+      ls[have + r] = s;
+      li[have + r] = base + lane;
+    }
+    const int add = __popc(m);
+    __syncwarp();
+    if (add <= room) {
+      have += add;
+      break;
+    }
+    have = W;
+    tau = trim_row<U>(ls, li, keep, have, lane);
+    m = __ballot_sync(0xffffffffu, mine && r >= room && s < tau);
+    if (m == 0) break;
+  }
+  return tau;
+}
+
 // Warp roles (E = 4*HALVES):
 //   [0, 2E)     epilogue, two groups of E warps: group g reads columns [64g, 64g+64) of every tile, so an
 //               accumulator is handed back after two TMEM reads per warp instead of four -- the round
@@ -722,6 +801,8 @@ __global__ void __launch_bounds__((HALVES * 12 + 3) * 32, 1) knn_tc_kernel(const
     const uint32_t c_ready = ptx::smem_u32(&ready[c]);
     const int keep = p.keep;
     uint32_t tail[2] = {0u, 0u};
+    const bool append = !THR && U >= 2 && keep <= W - 16;  // append-and-trim lists instead of sorted ones
+    int cntreg = 0;         // append lists: entries in row c*32 + lane
     long long st_busy = 0;  // instrumented build only
     unsigned long long st_ev = 0, st_hit = 0, st_surv = 0, st_bulk = 0;
     for (int b = 0; b < nqb; ++b) {
@@ -737,6 +818,7 @@ __global__ void __launch_bounds__((HALVES * 12 + 3) * 32, 1) knn_tc_kernel(const
       } else {
         tau0[lane] = CUDART_INF_F;
       }
+      cntreg = 0;
       __syncwarp();
       if (lane == 0) ptx::st_release_shared(c_ready, (uint32_t)(b + 1));
       uint32_t spins = 0, nap = 32;
@@ -800,7 +882,14 @@ __global__ void __launch_bounds__((HALVES * 12 + 3) * 32, 1) knn_tc_kernel(const
               __syncwarp();
               continue;
             }
-            const float nt = take_entry<U>(ls0 + (size_t)rl * W, li0 + (size_t)rl * W, s, ok, m, base, tau, keep, lane);
+            float nt;
+            if (U >= 2 && append) {
+              int have = __shfl_sync(0xffffffffu, cntreg, rl);
+              nt = take_append<U>(ls0 + (size_t)rl * W, li0 + (size_t)rl * W, s, m, base, tau, keep, have, lane);
+              if (lane == rl) cntreg = have;
+            } else {
+              nt = take_entry<U>(ls0 + (size_t)rl * W, li0 + (size_t)rl * W, s, ok, m, base, tau, keep, lane);
+            }
             if (lane == 0 && nt != tau) ptx::st_volatile_shared_f32(ptx::smem_u32(&tau0[rl]), nt);
             __syncwarp();
           }
@@ -811,6 +900,21 @@ __global__ void __launch_bounds__((HALVES * 12 + 3) * 32, 1) knn_tc_kernel(const
       // ---- flush this block's candidate lists (coalesced, one row at a time)
       const int64_t q0 = (int64_t)qb * ROWS + c * 32;
       int my_cnt = 0;
+      if (U >= 2 && append) {
+        // rows holding more than keep entries are cut once more: the re-rank then gathers keep - 1 rows
+        for (int r = 0; r < 32; ++r) {
+          int have = __shfl_sync(0xffffffffu, cntreg, r);
+          if (have > keep) {
+            const float nt = trim_row<U>(ls0 + (size_t)r * W, li0 + (size_t)r * W, keep, have, lane);
+            if (lane == r) {
+              cntreg = have;
+              tau0[r] = nt;
+            }
+          }
+          for (int e = have + lane; e < W; e += 32) li0[(size_t)r * W + e] = -1;
+        }
+        __syncwarp();
+      }
       for (int r = 0; r < 32; ++r) {
         int nv = 0;
 #pragma unroll
@@ -823,6 +927,7 @@ __global__ void __launch_bounds__((HALVES * 12 + 3) * 32, 1) knn_tc_kernel(const
         if (lane == r) my_cnt = nv;
       }
       if (THR) my_cnt = min(cnt0[lane], W + 1);
+      if (U >= 2 && append) my_cnt = cntreg;
       p.cand_cnt[q0 + lane] = my_cnt;
       p.cand_tau[q0 + lane] = tau0[lane];
       __syncwarp();
@@ -1046,7 +1151,9 @@ bool tc_config(int d, int k, int margin, bool self, int force_halves, TcConfig* 
   int keep = base + (margin < 0 ? std::max(4, std::min(k / 2, 16)) : margin);
   if (base > 128) return false;
   if (keep > 128) keep = 128;
-  const int u = keep <= 32 ? 1 : (keep <= 64 ? 2 : 4);
+  // keep <= 32: sorted 32-entry lists; above that append-and-trim lists with >= 16 entries of head room
+  // (64 entries up to keep = 48, 128 up to 112), sorted 128-entry lists for the rest
+  const int u = keep <= 32 ? 1 : (keep <= 48 ? 2 : 4);
   const size_t tile = (size_t)tc::TILE * K * 2;
   const size_t limit = 227 * 1024 - 1024;
   for (int halves = 2; halves >= 1; --halves) {
