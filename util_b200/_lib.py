@@ -12,7 +12,8 @@ import os
 import numpy as np
 
 _HERE = os.path.dirname(os.path.abspath(__file__))
-LIB_PATH = os.path.join(_HERE, "csrc", "libb200approx.so")
+# B200_LIB: developer hook for A/B runs of two builds of the same library (profiles/); never a different backend
+LIB_PATH = os.environ.get("B200_LIB") or os.path.join(_HERE, "csrc", "libb200approx.so")
 
 AVERAGE, SHEPARD, VORONOI = 0, 1, 2
 PATH_AUTO, PATH_EXACT, PATH_TENSOR = 0, 1, 2

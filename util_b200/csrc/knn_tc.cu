@@ -780,9 +780,16 @@ __global__ void __launch_bounds__((HALVES * 12 + 3) * 32, 1) knn_tc_kernel(const
       int col = colg;  // first of my columns in the current tile
       // (one instance of the tile step with run-time stage selects: instantiating it per stage made the
       // loop four times as long and cost more in instruction fetch than the selects do)
+      const long long blk0 = (DBG && p.stats) ? clock64() : 0;
       for (int t = 0; t < p.ntiles; ++t, ++it) {
         const uint32_t a = it & 1;
         B200_TILE(a, (it >> 1) & 1);
+        if (DBG && p.stats && warp == 0 && lane == 0) {  // block timeline: clocks to reach tiles 64, 512, 2048, the end
+          if (t == 63) atomicAdd(p.stats + 12, (unsigned long long)(clock64() - blk0));
+          if (t == 511) atomicAdd(p.stats + 13, (unsigned long long)(clock64() - blk0));
+          if (t == 2047) atomicAdd(p.stats + 14, (unsigned long long)(clock64() - blk0));
+          if (t == p.ntiles - 1) atomicAdd(p.stats + 15, (unsigned long long)(clock64() - blk0));
+        }
       }
 #undef B200_TILE
 #undef B200_CHUNK
@@ -804,7 +811,7 @@ __global__ void __launch_bounds__((HALVES * 12 + 3) * 32, 1) knn_tc_kernel(const
     const bool append = !THR && U >= 2 && keep <= W - 16;  // append-and-trim lists instead of sorted ones
     int cntreg = 0;         // append lists: entries in row c*32 + lane
     long long st_busy = 0;  // instrumented build only
-    unsigned long long st_ev = 0, st_hit = 0, st_surv = 0, st_bulk = 0;
+    unsigned long long st_ev = 0, st_hit = 0, st_surv = 0, st_bulk = 0, st_trim = 0;
     for (int b = 0; b < nqb; ++b) {
       const int qb = (int)blockIdx.x + b * (int)gridDim.x;
       for (int e = lane; e < 32 * W; e += 32) {
@@ -885,7 +892,9 @@ __global__ void __launch_bounds__((HALVES * 12 + 3) * 32, 1) knn_tc_kernel(const
             float nt;
             if (U >= 2 && append) {
               int have = __shfl_sync(0xffffffffu, cntreg, rl);
+              const int before = have + __popc(m);
               nt = take_append<U>(ls0 + (size_t)rl * W, li0 + (size_t)rl * W, s, m, base, tau, keep, have, lane);
+              if (DBG) st_trim += have < before;
               if (lane == rl) cntreg = have;
             } else {
               nt = take_entry<U>(ls0 + (size_t)rl * W, li0 + (size_t)rl * W, s, ok, m, base, tau, keep, lane);
@@ -938,6 +947,7 @@ __global__ void __launch_bounds__((HALVES * 12 + 3) * 32, 1) knn_tc_kernel(const
       atomicAdd(p.stats + 2, st_surv);
       atomicAdd(p.stats + 3, st_bulk);
       atomicAdd(p.stats + 4, (unsigned long long)st_busy);
+      atomicAdd(p.stats + 5, st_trim);
     }
   }
   ptx::tc_fence_before();
