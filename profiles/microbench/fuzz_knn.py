@@ -1,5 +1,6 @@
 """Randomised cross-check of the tensor kNN path against the fp64 brute-force kernel (itself pinned to the
-oracle by the test suite): shapes, k, scales, offsets, clustered and duplicated data, both stage-1 kernels.
+oracle by the test suite): shapes, k (sorted, append-and-trim and 128-entry lists), scales, offsets, clustered
+and duplicated data.
     python profiles/microbench/fuzz_knn.py [cases] [seed]
 """
 import sys
@@ -14,7 +15,7 @@ for c in range(cases):
     d = int(rng.choice([2, 3, 5, 8, 13, 16, 29, 32, 61, 64, 77, 100, 125]))
     n = int(rng.integers(4200, 120000))
     q = int(rng.choice([130, 700, 5000, 40000]))
-    k = int(rng.choice([1, 2, 5, 16, 17, 32, 33, 64]))
+    k = int(rng.choice([1, 2, 5, 16, 17, 24, 32, 33, 48, 64, 100]))
     kind = rng.choice(["uniform", "normal", "clusters", "dups", "lattice"])
     if kind == "uniform":
         x = rng.random((n, d)); z = rng.random((q, d))
@@ -32,10 +33,9 @@ for c in range(cases):
         x = rng.integers(0, 6, size=(n, d)).astype(float); z = rng.integers(0, 6, size=(q, d)) + 0.5
     scale = float(rng.choice([1.0, 1e-4, 1e3])); shift = float(rng.choice([0.0, 0.0, 50.0, -1e4]))
     x = x * scale + shift; z = z * scale + shift
-    flags = int(rng.choice([0, 0, 64]))
+    flags = 0
     m = _lib.Model(x)
     m.set_option("knn_path", _lib.PATH_TENSOR)
-    m.set_option("tc_flags", flags)
     try:
         it, dt = m.knn(z, k)
     except Exception as e:  # unsupported shape for the tensor path is fine, anything else is not

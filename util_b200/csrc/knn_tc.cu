@@ -846,7 +846,7 @@ __global__ void __launch_bounds__((HALVES * 12 + 3) * 32, 1) knn_tc_kernel(const
             continue;
           }
           __nanosleep(nap);  // back off: an entry then waits at most ~0.3 us, and the queues hold 16
-          if (nap < 256) nap *= 2;
+          if (nap < 2048) nap *= 2;
           B200_SPIN_GUARD(spins);
           continue;
         }
@@ -1163,9 +1163,12 @@ bool tc_config(int d, int k, int margin, bool self, int force_halves, TcConfig* 
   if (keep > 128) keep = 128;
   // keep <= 32: sorted 32-entry lists; above that append-and-trim lists with >= 16 entries of head room
   // (64 entries up to keep = 48, 128 up to 112), sorted 128-entry lists for the rest
-  const int u = keep <= 32 ? 1 : (keep <= 48 ? 2 : 4);
+  // (in high dimension the 128-entry lists may not fit beside the operand tiles: keep <= 64 then falls
+  // back to sorted 64-entry lists)
+  const int u_first = keep <= 32 ? 1 : (keep <= 48 ? 2 : 4);
   const size_t tile = (size_t)tc::TILE * K * 2;
   const size_t limit = 227 * 1024 - 1024;
+  for (int u = u_first; u >= 2 || u == u_first; u = (u == 4 && keep <= 64) ? 2 : 0)
   for (int halves = 2; halves >= 1; --halves) {
     if (force_halves && halves != force_halves) continue;
     const int rows = halves * tc::TILE, epi = halves * 4;
