@@ -553,7 +553,7 @@ def main():
                 "gpu_launches": int(round(stats["launches"] * args.steps)),
                 **({"tc_stats": {nm: model.stat(f"tc_stat{i}") / args.steps for i, nm in enumerate(
                     ["events", "events_hit", "survivors", "rank_merges", "sel_busy_clk", "trims",
-                     "ready_wait_clk", "acc_wait_clk", "push_clk", "release_clk", "tile_clk", "pushes",
+                     "paired_events", "acc_wait_clk", "push_clk", "release_clk", "tile_clk", "pushes",
                      "push_clk_after_tile64", "pushes_after_tile64", "clk_to_tile512", "clk_to_tile64"])}} if args.tc_stats else {}),
                 "e2e": e2e, "clocks": sampler.summary()}
         if G == 1 and not args.no_cpu:

@@ -8,7 +8,7 @@ from util_b200 import _lib
 
 n, q, d, k = (int(a) for a in sys.argv[1:5])
 x = np.random.default_rng(0).random((n, d)); z = np.random.default_rng(1).random((q, d))
-names = ["events", "events_hit", "survivors", "rank_merges", "sel_busy_clk", "trims", "-", "-", "-", "-", "-", "pushes", "clk_to_tile64", "clk_to_tile512", "clk_to_tile2048", "clk_block"]
+names = ["events", "events_hit", "survivors", "rank_merges", "sel_busy_clk", "trims", "paired_events", "clk_read_ballot", "clk_insert_few", "clk_store_sync", "clk_rank_merge", "pushes", "clk_to_tile64", "clk_to_tile512", "clk_to_tile2048", "clk_block"]
 for stats in (0, 1):
     m = _lib.Model(x)
     m.set_option("knn_path", 2)

@@ -265,6 +265,12 @@ struct KParams {
   do {                                    \
     if (++(spins) > (1u << 26)) __trap(); \
   } while (0)
+#ifndef B200_PAIR
+#define B200_PAIR 1
+#endif
+#ifndef B200_PRESLEEP
+#define B200_PRESLEEP 0
+#endif
 __device__ __forceinline__ void mbar_wait_lean(uint32_t bar, uint32_t parity) {
   uint32_t spins = 0;
   while (!ptx::mbar_try_wait(bar, parity)) B200_SPIN_GUARD(spins);
@@ -273,6 +279,10 @@ __device__ __forceinline__ void mbar_wait_lean(uint32_t bar, uint32_t parity) {
 // hint elapses) instead of re-issuing the probe.  This kernel is bound by instruction issue; sixteen
 // epilogue warps probing in a tight loop took a fifth of all issue slots.
 __device__ __forceinline__ void mbar_wait_suspend(uint32_t bar, uint32_t parity) {
+  if (B200_PRESLEEP > 0) {
+    if (ptx::mbar_test_wait(bar, parity)) return;
+    __nanosleep(B200_PRESLEEP);
+  }
   uint32_t spins = 0;
   while (!ptx::mbar_try_wait_hint(bar, parity, 4000)) B200_SPIN_GUARD(spins);
 }
@@ -811,7 +821,7 @@ __global__ void __launch_bounds__((HALVES * 12 + 3) * 32, 1) knn_tc_kernel(const
     const bool append = !THR && U >= 2 && keep <= W - 16;  // append-and-trim lists instead of sorted ones
     int cntreg = 0;         // append lists: entries in row c*32 + lane
     long long st_busy = 0;  // instrumented build only
-    unsigned long long st_ev = 0, st_hit = 0, st_surv = 0, st_bulk = 0, st_trim = 0;
+    unsigned long long st_ev = 0, st_hit = 0, st_surv = 0, st_bulk = 0, st_trim = 0, st_pair = 0;
     for (int b = 0; b < nqb; ++b) {
       const int qb = (int)blockIdx.x + b * (int)gridDim.x;
       for (int e = lane; e < 32 * W; e += 32) {
@@ -859,6 +869,94 @@ __global__ void __launch_bounds__((HALVES * 12 + 3) * 32, 1) knn_tc_kernel(const
           uint32_t tl = tail[g];
           const long long c0 = (DBG && p.stats && tl != h) ? clock64() : 0;
           while (tl != h) {
+            if (B200_PAIR && U == 1 && !THR && h - tl >= 2) {
+              // Two entries of different rows at once, one per half-warp: a row's 32-entry list is spread over 16
+              // lanes (two entries each), shuffles run 16 wide.  One entry is a chain of dependent shuffles and
+              // shared-memory round trips (~500 clk for ~60 instructions); while every row of a block is still
+              // filling its list the selection warps are what the whole pipeline waits for, and the second
+              // half-warp's chain rides in the same instructions.
+              const float* ea = myq + (size_t)(tl & (uint32_t)(QE - 1)) * QWORDS;
+              const float* eb = myq + (size_t)((tl + 1) & (uint32_t)(QE - 1)) * QWORDS;
+              const int4 ma = *reinterpret_cast<const int4*>(ea + 32);
+              const int4 mb = *reinterpret_cast<const int4*>(eb + 32);
+              if (ma.x != mb.x) {
+                const int hw = lane >> 4, sub = lane & 15;
+                const float* em = hw ? eb : ea;
+                const int4 mt = hw ? mb : ma;
+                const float nlc = __int_as_float(mt.z);
+                const float v0 = em[sub] + nlc, v1 = em[16 + sub] + nlc;
+                float tq = tau0[mt.x];
+                const unsigned b0 = __ballot_sync(0xffffffffu, v0 < tq && mt.y + sub < p.ncols);
+                const unsigned b1 = __ballot_sync(0xffffffffu, v1 < tq && mt.y + 16 + sub < p.ncols);
+                const unsigned mA = (b0 & 0xffffu) | (b1 << 16), mB = (b0 >> 16) | (b1 & 0xffff0000u);
+                if (__popc(mA) < 6 && __popc(mB) < 6) {
+                  tl += 2;
+                  if (lane == 0) ptx::st_volatile_shared_u32(a_tails + 4 * g, tl);
+                  if (DBG) {
+                    st_pair += 2;
+                    st_ev += 2;
+                    st_hit += (mA != 0) + (mB != 0);
+                    st_surv += __popc(mA) + __popc(mB);
+                  }
+                  if (mA | mB) {
+                    unsigned mm = hw ? mB : mA;
+                    const bool mine = mm != 0;
+                    float* lsr = ls0 + (size_t)mt.x * W;
+                    int* lir = li0 + (size_t)mt.x * W;
+                    float sc0 = lsr[sub], sc1 = lsr[16 + sub];
+                    int id0 = lir[sub], id1 = lir[16 + sub];
+                    const float t_in = tq;
+                    const int ke = keep - 1, sh = hw * 16;
+                    unsigned any = 1u;
+                    while (any) {
+                      const bool act = mm != 0;
+                      const int bl = act ? __ffs(mm) - 1 : 0;
+                      mm &= mm - 1;  // (0 stays 0)
+                      float sv = __shfl_sync(0xffffffffu, (bl & 16) ? v1 : v0, bl & 15, 16);
+                      sv = (act && sv < tq) ? sv : CUDART_INF_F;  // +inf lands behind the last entry: nothing moves
+                      const unsigned c0 = __ballot_sync(0xffffffffu, sc0 <= sv), c1 = __ballot_sync(0xffffffffu, sc1 <= sv);
+                      const int pos = __popc((c0 >> sh) & 0xffffu) + __popc((c1 >> sh) & 0xffffu);
+                      float p1s = __shfl_up_sync(0xffffffffu, sc1, 1, 16);
+                      int p1i = __shfl_up_sync(0xffffffffu, id1, 1, 16);
+                      const float cs = __shfl_sync(0xffffffffu, sc0, 15, 16);
+                      const int ci = __shfl_sync(0xffffffffu, id0, 15, 16);
+                      const float p0s = __shfl_up_sync(0xffffffffu, sc0, 1, 16);
+                      const int p0i = __shfl_up_sync(0xffffffffu, id0, 1, 16);
+                      if (sub == 0) {
+                        p1s = cs;
+                        p1i = ci;
+                      }
+                      const int col = mt.y + bl;
+                      if (16 + sub > pos) {
+                        sc1 = p1s;
+                        id1 = p1i;
+                      } else if (16 + sub == pos) {
+                        sc1 = sv;
+                        id1 = col;
+                      }
+                      if (sub > pos) {
+                        sc0 = p0s;
+                        id0 = p0i;
+                      } else if (sub == pos) {
+                        sc0 = sv;
+                        id0 = col;
+                      }
+                      tq = __shfl_sync(0xffffffffu, (ke & 16) ? sc1 : sc0, ke & 15, 16);
+                      any = __ballot_sync(0xffffffffu, mm != 0);
+                    }
+                    if (mine) {
+                      lsr[sub] = sc0;
+                      lsr[16 + sub] = sc1;
+                      lir[sub] = id0;
+                      lir[16 + sub] = id1;
+                      if (sub == 0 && tq != t_in) ptx::st_volatile_shared_f32(ptx::smem_u32(&tau0[mt.x]), tq);
+                    }
+                  }
+                  __syncwarp();
+                  continue;
+                }
+              }
+            }
             const float* e = myq + (size_t)(tl & (uint32_t)(QE - 1)) * QWORDS;
             const int4 meta = *reinterpret_cast<const int4*>(e + 32);
             const float s = e[lane] + __int_as_float(meta.z);  // dot + nlo of the chunk
@@ -948,6 +1046,7 @@ __global__ void __launch_bounds__((HALVES * 12 + 3) * 32, 1) knn_tc_kernel(const
       atomicAdd(p.stats + 3, st_bulk);
       atomicAdd(p.stats + 4, (unsigned long long)st_busy);
       atomicAdd(p.stats + 5, st_trim);
+      atomicAdd(p.stats + 6, st_pair);
     }
   }
   ptx::tc_fence_before();
