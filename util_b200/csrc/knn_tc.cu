@@ -265,11 +265,14 @@ struct KParams {
   do {                                    \
     if (++(spins) > (1u << 26)) __trap(); \
   } while (0)
+// Two tuning switches kept for A/B builds (profiles/microbench/ab.py): pairs of queue entries per selection
+// step, and a short plain sleep before an epilogue warp suspends on its accumulator barrier (every mbarrier
+// arrival in the CTA wakes the suspended warps to probe again; the accumulator is rarely ready within 64 ns).
 #ifndef B200_PAIR
 #define B200_PAIR 1
 #endif
 #ifndef B200_PRESLEEP
-#define B200_PRESLEEP 0
+#define B200_PRESLEEP 64
 #endif
 __device__ __forceinline__ void mbar_wait_lean(uint32_t bar, uint32_t parity) {
   uint32_t spins = 0;
