@@ -274,13 +274,9 @@ struct KParams {
 #ifndef B200_PRESLEEP
 #define B200_PRESLEEP 64
 #endif
-__device__ __forceinline__ void mbar_wait_lean(uint32_t bar, uint32_t parity) {
-  uint32_t spins = 0;
-  while (!ptx::mbar_try_wait(bar, parity)) B200_SPIN_GUARD(spins);
-}
-// The same with a suspend-time hint: the warp sleeps in hardware until the phase completes (or the
-// hint elapses) instead of re-issuing the probe.  This kernel is bound by instruction issue; sixteen
-// epilogue warps probing in a tight loop took a fifth of all issue slots.
+// Wait with a suspend-time hint: the warp sleeps in hardware until the phase completes (or the hint
+// elapses) instead of re-issuing the probe; sixteen epilogue warps probing in a tight loop took a fifth
+// of all issue slots.
 __device__ __forceinline__ void mbar_wait_suspend(uint32_t bar, uint32_t parity) {
   if (B200_PRESLEEP > 0) {
     if (ptx::mbar_test_wait(bar, parity)) return;

@@ -260,8 +260,6 @@ int b200_multi_nn_predict(b200_multi* mm, const double* z, int64_t q, int32_t k,
       const int64_t lo = std::min<int64_t>(q, g * per), hi = std::min<int64_t>(q, lo + per);
       if (hi == lo) return 0;
       int r = 0;
-      double yr = 0;
-      (void)yr;
       return b200_nn_predict(mm->models[g], z + (size_t)lo * d, hi - lo, k, method, nullptr, r,
                              ids ? ids + (size_t)lo * k : nullptr, wts ? wts + (size_t)lo * k : nullptr, nullptr, nullptr,
                              out ? out + (size_t)lo * mm->models[g]->y_r : nullptr);

@@ -523,14 +523,7 @@ shepmod_block_kernel(const double* __restrict__ x, const double* __restrict__ rw
   }
 }
 
-// rows listed in `sel` of (q, w) arrays gathered to / scattered from a compact (ns, w) array
-__global__ void gather_rows_f64_kernel(const double* __restrict__ src, const int32_t* __restrict__ sel, int ns, int w,
-                                       double* __restrict__ dst) {
-  const int64_t e = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
-  if (e >= (int64_t)ns * w) return;
-  const int i = (int)(e / w), j = (int)(e - (int64_t)i * w);
-  dst[e] = src[(int64_t)sel[i] * w + j];
-}
+// rows of a compact (ns, w) array scattered to the rows listed in `sel` of a (q, w) array
 template <class T>
 __global__ void scatter_rows_kernel(const T* __restrict__ src, const int32_t* __restrict__ sel, int ns, int w,
                                     T* __restrict__ dst) {

@@ -189,11 +189,10 @@ voronoi_kernel(const double* __restrict__ x, int d, const double* __restrict__ z
   double* w = pdot + k;
   double* pts = w + k;                  // [d] query
   __shared__ int s_err;
-  __shared__ int s_cnt;
   const int64_t p = blockIdx.x;
   const int t = threadIdx.x, nt = blockDim.x;
   const int32_t* id = idx + p * k;
-  if (t == 0) { s_err = 0; s_cnt = 0; }
+  if (t == 0) s_err = 0;
   for (int j = t; j < d; j += nt) pts[j] = z[p * d + j];
   for (int e = t; e < k * d; e += nt) {
     const int i = e / d, j = e - i * d;
