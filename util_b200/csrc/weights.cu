@@ -176,7 +176,7 @@ avg_shepard_thread_kernel(const double* __restrict__ d2, int64_t q, int k, int m
 //   num = (p.x_o + x_c.x_c) - (p.x_c + x_c.x_o), den = x_o.x_o + x_c.x_c - 2 x_c.x_o
 // with the operand grouping of voronoi.f90:131-134.  ERROR=2 is raised when any
 // pair among the k neighbours has |den| <= sqrt(eps) (:137,145-148).
-__global__ void __launch_bounds__(128)
+__global__ void __launch_bounds__(256)
 voronoi_kernel(const double* __restrict__ x, int d, const double* __restrict__ z, int64_t q, int k,
                const int32_t* __restrict__ idx, const double* __restrict__ y, int r,
                double* __restrict__ wts, int32_t* __restrict__ cnt, int32_t* __restrict__ err,
@@ -226,10 +226,15 @@ voronoi_kernel(const double* __restrict__ x, int d, const double* __restrict__ z
   }
   __syncthreads();
   const double MINV = 1.4901161193847656e-08;
-  for (int c = t; c < k; c += nt) {
+  // the (centre, other) pairs are spread over all threads: `parts` threads share a centre, each takes every
+  // parts-th other point; the maximum ratio is order independent, so the split changes no bit
+  const int parts = nt >= 2 * k ? nt / k : 1;
+  double* part_mr = pts + d;  // [parts][k]
+  for (int e = t; e < k * parts; e += nt) {
+    const int c = e % k, pt = e / k;
     double mr = 0.0;
     const double gcc = G[(size_t)c * (k + 1) + c], pc = pdot[c];
-    for (int o = 0; o < k; ++o) {
+    for (int o = pt; o < k; o += parts) {
       if (o == c) continue;
       const double gco = G[(size_t)c * (k + 1) + o];
       const double num = __dsub_rn(__dadd_rn(pdot[o], gcc), __dadd_rn(pc, gco));                 // :131-132
@@ -241,6 +246,12 @@ voronoi_kernel(const double* __restrict__ x, int d, const double* __restrict__ z
         atomicMax(&s_err, 2);
       }
     }
+    part_mr[(size_t)pt * k + c] = mr;
+  }
+  __syncthreads();
+  for (int c = t; c < k; c += nt) {
+    double mr = part_mr[c];
+    for (int pt = 1; pt < parts; ++pt) mr = fmax(mr, part_mr[(size_t)pt * k + c]);
     w[c] = fmax(__dsub_rn(1.0, mr), 0.0);  // :151
   }
   __syncthreads();
@@ -327,7 +338,8 @@ int nn_weights(b200_model* m, const double* z_dev, int64_t q, int k, int method,
   }
   if (method == B200_VORONOI) {
     const int d = m->d;
-    const size_t smem = ((size_t)k * (d | 1) + (size_t)k * (k + 1) + 2 * (size_t)k + d) * 8;
+    const int vthreads = k > 32 ? 256 : 128;
+    const size_t smem = ((size_t)k * (d | 1) + (size_t)k * (k + 1) + 2 * (size_t)k + d + vthreads) * 8;  // + the partial maxima
     if (smem > 200 * 1024) {
       set_error("nn_weights: Voronoi on k=%d neighbours in %d-D needs %zu B shared memory", k, d, smem);
       return 1;
@@ -338,7 +350,7 @@ int nn_weights(b200_model* m, const double* z_dev, int64_t q, int k, int method,
     double* wbuf = wts_dev ? wts_dev : m->wts.as<double>();
     int32_t* cbuf = cnt_dev ? cnt_dev : m->cnt.as<int32_t>();
     B200_CUDA(cudaFuncSetAttribute(voronoi_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
-    voronoi_kernel<<<(unsigned)q, 128, smem, st>>>(m->x, d, z_dev, q, k, idx_dev, y_dev, r, wbuf, cbuf,
+    voronoi_kernel<<<(unsigned)q, vthreads, smem, st>>>(m->x, d, z_dev, q, k, idx_dev, y_dev, r, wbuf, cbuf,
                                                    err_dev, y_dev ? out_dev : nullptr,
                                                    m->misc.as<int32_t>());
     B200_CUDA(cudaGetLastError());
