@@ -213,10 +213,13 @@ voronoi_kernel(const double* __restrict__ x, int d, const double* __restrict__ z
       }
       if (dd > HUGEV) atomicMax(&s_err, 1);
     } else {
-      // unrank e-k -> (a<=b) over the upper triangle
-      int f = e - k, a = 0;
-      while (f >= k - a) { f -= k - a; ++a; }
-      const int b = a + f;
+      // unrank e-k -> (a<=b) over the upper triangle: rows a' < a hold a(2k-a+1)/2 entries
+      const int f0 = e - k;
+      int a = (int)(((float)(2 * k + 1) - sqrtf((float)((2 * k + 1) * (2 * k + 1) - 8 * f0))) * 0.5f);
+      a = a < 0 ? 0 : (a > k - 1 ? k - 1 : a);
+      while (a > 0 && a * (2 * k - a + 1) / 2 > f0) --a;          // float rounding: at most one step either way
+      while ((a + 1) * (2 * k - a) / 2 <= f0) ++a;
+      const int b = a + (f0 - a * (2 * k - a + 1) / 2);
       double s = 0.0;
       for (int j = 0; j < d; ++j) s = __dadd_rn(s, __dmul_rn(P[(size_t)a * dp + j], P[(size_t)b * dp + j]));
       G[(size_t)a * (k + 1) + b] = s;
@@ -255,31 +258,45 @@ voronoi_kernel(const double* __restrict__ x, int d, const double* __restrict__ z
     w[c] = fmax(__dsub_rn(1.0, mr), 0.0);  // :151
   }
   __syncthreads();
+  // normalisation and output.  The sums keep the reference's order (one thread each); the divisions, the
+  // compaction of the supported neighbours and the stores are spread over the block.
+  __shared__ double s_sum;
+  __shared__ int s_m;
+  int* slot = reinterpret_cast<int*>(pdot);  // [k] output position of neighbour i, -1: no support (pdot is done with)
   if (t == 0) {
-    const int e = s_err;
     double s = 0.0;
     for (int i = 0; i < k; ++i) s = __dadd_rn(s, w[i]);  // :154
+    s_sum = s;
+  }
+  __syncthreads();
+  const int e = s_err;
+  for (int i = t; i < k; i += nt) w[i] = __ddiv_rn(w[i], s_sum);
+  __syncthreads();
+  if (t == 0) {
     int m = 0;
-    double acc[8];
-    const int rr = r < 8 ? r : 8;
-    for (int c = 0; c < rr; ++c) acc[c] = 0.0;
-    for (int i = 0; i < k; ++i) {
-      const double wi = __ddiv_rn(w[i], s);
-      if (e == 0 && wi > 0) {  // voronoi/__init__.py:58 support > 0
-        if (wts) wts[p * k + m] = wi;
-        if (ids_out) ids_out[p * k + m] = id[i];
-        if (out)
-          for (int c = 0; c < rr; ++c)
-            acc[c] = __dadd_rn(acc[c], id[i] >= 0 ? __dmul_rn(y[(int64_t)id[i] * r + c], wi) : CUDART_NAN);
-        ++m;
-      }
+    for (int i = 0; i < k; ++i) slot[i] = (e == 0 && w[i] > 0) ? m++ : -1;  // voronoi/__init__.py:58 support > 0
+    s_m = m;
+  }
+  __syncthreads();
+  const int m = s_m;
+  for (int i = t; i < k; i += nt) {
+    if (slot[i] >= 0) {
+      if (wts) wts[p * k + slot[i]] = w[i];
+      if (ids_out) ids_out[p * k + slot[i]] = id[i];
     }
-    for (int i = m; i < k; ++i) {
+    if (i >= m) {
       if (wts) wts[p * k + i] = 0.0;
       if (ids_out) ids_out[p * k + i] = -1;
     }
-    if (out)
-      for (int c = 0; c < rr; ++c) out[p * r + c] = acc[c];
+  }
+  const int rr = r < 8 ? r : 8;
+  if (out && t < rr) {
+    double acc = 0.0;
+    for (int i = 0; i < k; ++i)
+      if (slot[i] >= 0) acc = __dadd_rn(acc, id[i] >= 0 ? __dmul_rn(y[(int64_t)id[i] * r + t], w[i]) : CUDART_NAN);
+    out[p * r + t] = acc;
+  }
+  if (t == 0) {
     if (cnt) cnt[p] = m;
     if (err) err[p] = e;
   }
