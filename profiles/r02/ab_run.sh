@@ -1,7 +1,4 @@
-timeout 900 python -m pytest tests/test_gpu_parity.py tests/test_gpu_configs.py -q -m gpu -x 2>&1 | tail -2
-for i in 1 2; do
-timeout 300 python bench.py --config c4 --no-ref-class 2>/dev/null | python -c "
-import sys,json
-for l in sys.stdin:
-    j=json.loads(l); print('c4', round(j['value']), round(j['ms_per_step'],2), {k:round(v,2) for k,v in j['stages_ms'].items()}, j['parity_on_sample'])"
-done
+timeout 900 python -m pytest tests/test_gpu_tensor.py tests/test_gpu_parity.py -q -m gpu -x 2>&1 | tail -2
+python profiles/microbench/ab.py build_ab/libcur.so util_b200/csrc/libb200approx.so 1000000 37888 64 16 2
+python profiles/microbench/ab.py build_ab/libcur.so util_b200/csrc/libb200approx.so 100000 100000 16 18 1
+python profiles/microbench/ab.py build_ab/libcur.so util_b200/csrc/libb200approx.so 1000000 500000 64 16 1
