@@ -265,11 +265,26 @@ struct KParams {
   do {                                    \
     if (++(spins) > (1u << 26)) __trap(); \
   } while (0)
-// Two tuning switches kept for A/B builds (profiles/microbench/ab.py): pairs of queue entries per selection
-// step, and a short plain sleep before an epilogue warp suspends on its accumulator barrier (every mbarrier
-// arrival in the CTA wakes the suspended warps to probe again; the accumulator is rarely ready within 64 ns).
+// Tuning switches kept for A/B builds (profiles/microbench/ab.py).  While every row of a block is still filling
+// its list the selection warps are what the pipeline waits for, and they share their SM sub-partitions with
+// waiting warps; every probe a waiting warp issues is an issue slot they lose:
+//   B200_PAIR         two queue entries of different rows per selection step, one per half-warp
+//   B200_PRESLEEP     ns of plain sleep before an epilogue warp suspends on its accumulator barrier (every mbarrier
+//                     arrival in the CTA wakes the suspended warps to probe again)
+//   B200_QWAIT        ns between an epilogue warp's looks at the tail of its full queue (100 -> 1000: -2 %)
+//   B200_ISSUER_HINT  the MMA issuers wait for a free accumulator with a suspend hint instead of probing (-1 %)
+//   B200_ALL_HINT     the same for the producer's and the issuers' tile-ring waits (slower at d = 64, not used)
 #ifndef B200_PAIR
 #define B200_PAIR 1
+#endif
+#ifndef B200_ALL_HINT
+#define B200_ALL_HINT false
+#endif
+#ifndef B200_ISSUER_HINT
+#define B200_ISSUER_HINT true
+#endif
+#ifndef B200_QWAIT
+#define B200_QWAIT 1000
 #endif
 #ifndef B200_PRESLEEP
 #define B200_PRESLEEP 64
@@ -581,13 +596,13 @@ __global__ void __launch_bounds__((HALVES * 12 + 3) * 32, 1) knn_tc_kernel(const
       const uint32_t sB0 = ptx::smem_u32(sB);
       for (int b = 0; b < nqb; ++b) {
         const int qb = (int)blockIdx.x + b * (int)gridDim.x;
-        ptx::mbar_wait(false, ptx::smem_u32(bar_aempty), (b & 1) ^ 1, 64);
+        ptx::mbar_wait(B200_ALL_HINT, ptx::smem_u32(bar_aempty), (b & 1) ^ 1, B200_ALL_HINT ? 0 : 64);
         ptx::mbar_arrive_expect_tx(ptx::smem_u32(bar_afull), HALVES * tile_bytes);
         ptx::bulk_g2s(ptx::smem_u32(sA), reinterpret_cast<const uint8_t*>(p.a_img) + (size_t)qb * HALVES * tile_bytes,
                       HALVES * tile_bytes, ptx::smem_u32(bar_afull));
         const uint8_t* src = reinterpret_cast<const uint8_t*>(p.b_img);
         for (int t = 0; t < p.ntiles; ++t, src += tile_bytes) {
-          ptx::mbar_wait(false, empty0 + s * 8, ph ^ 1, 64);
+          ptx::mbar_wait(B200_ALL_HINT, empty0 + s * 8, ph ^ 1, B200_ALL_HINT ? 0 : 64);
           ptx::mbar_arrive_expect_tx(full0 + s * 8, tile_bytes);
           // one tile as `parts` bulk copies: more requests in flight per slot (tile_bytes is a multiple of 4 KB)
           const uint32_t part = tile_bytes / (uint32_t)p.parts;
@@ -623,15 +638,15 @@ __global__ void __launch_bounds__((HALVES * 12 + 3) * 32, 1) knn_tc_kernel(const
       const uint32_t afull = ptx::smem_u32(bar_afull), aempty = ptx::smem_u32(bar_aempty);
       const uint32_t ntiles = (uint32_t)p.ntiles;
       for (int b = 0; b < nqb; ++b, it0 += ntiles) {
-        ptx::mbar_wait(false, afull, b & 1);
+        ptx::mbar_wait(B200_ALL_HINT, afull, b & 1);
         for (uint32_t t = (j + it0) & 1; t < ntiles; t += 2, ++mine) {
           const uint32_t it = it0 + t, s = it & slot_mask, ph = (it >> slot_shift) & 1;
           const uint64_t bd = b_desc0 + (uint64_t)(s * slot_step);
 #pragma unroll
           for (int h = 0; h < HALVES; ++h) {
             // the accumulator half is free once its four epilogue warps have read the previous tile
-            ptx::mbar_wait(false, acce + h * 8, (mine & 1) ^ 1);
-            if (h == 0) ptx::mbar_wait(false, full0 + s * 8, ph);
+            ptx::mbar_wait(B200_ISSUER_HINT, acce + h * 8, (mine & 1) ^ 1);
+            if (h == 0) ptx::mbar_wait(B200_ALL_HINT, full0 + s * 8, ph);
             ptx::tc_fence_after();
             // (the accumulator base is the literal 0: this CTA owns all 512 columns, checked at start)
             const uint32_t d_tmem = j * ACC_COLS + h * TILE;
@@ -720,7 +735,7 @@ __global__ void __launch_bounds__((HALVES * 12 + 3) * 32, 1) knn_tc_kernel(const
       do {                                                                                           \
         tail_c = ptx::ld_acquire_shared(a_tail);                                                     \
         if (head + nadd_ - tail_c <= (uint32_t)QE) break;                                            \
-        __nanosleep(100);                                                                            \
+        __nanosleep(B200_QWAIT);                                                                     \
         B200_SPIN_GUARD(spins_);                                                                     \
       } while (true);                                                                                \
     }                                                                                                \
