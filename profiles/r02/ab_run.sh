@@ -1,5 +1,4 @@
-python profiles/microbench/ab.py build_ab/libcur.so build_ab/libnew.so 1000000 37888 64 16 1
-python profiles/microbench/ab.py build_ab/libnew.so build_ab/liballhint.so 1000000 37888 64 16 2
-python profiles/microbench/ab.py build_ab/libnew.so build_ab/liballhint.so 100000 100000 16 18 1
-python profiles/microbench/ab.py build_ab/libcur.so build_ab/libnew.so 1000000 1000000 64 16 1
-python profiles/microbench/ab.py build_ab/libnew.so build_ab/liballhint.so 1000000 1000000 64 16 1
+for v in pw300 pw1000; do
+python profiles/microbench/ab.py build_ab/libcur.so build_ab/lib$v.so 1000000 37888 64 16 2
+python profiles/microbench/ab.py build_ab/libcur.so build_ab/lib$v.so 100000 100000 16 18 1
+done

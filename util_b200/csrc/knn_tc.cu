@@ -273,9 +273,13 @@ struct KParams {
 //                     arrival in the CTA wakes the suspended warps to probe again)
 //   B200_QWAIT        ns between an epilogue warp's looks at the tail of its full queue (100 -> 1000: -2 %)
 //   B200_ISSUER_HINT  the MMA issuers wait for a free accumulator with a suspend hint instead of probing (-1 %)
+//   B200_PWAIT        ns between the producer's looks at a full tile ring (64 -> 300: neutral at d = 64, -0.6 % at d = 16)
 //   B200_ALL_HINT     the same for the producer's and the issuers' tile-ring waits (slower at d = 64, not used)
 #ifndef B200_PAIR
 #define B200_PAIR 1
+#endif
+#ifndef B200_PWAIT
+#define B200_PWAIT 300
 #endif
 #ifndef B200_ALL_HINT
 #define B200_ALL_HINT false
@@ -596,13 +600,13 @@ __global__ void __launch_bounds__((HALVES * 12 + 3) * 32, 1) knn_tc_kernel(const
       const uint32_t sB0 = ptx::smem_u32(sB);
       for (int b = 0; b < nqb; ++b) {
         const int qb = (int)blockIdx.x + b * (int)gridDim.x;
-        ptx::mbar_wait(B200_ALL_HINT, ptx::smem_u32(bar_aempty), (b & 1) ^ 1, B200_ALL_HINT ? 0 : 64);
+        ptx::mbar_wait(B200_ALL_HINT, ptx::smem_u32(bar_aempty), (b & 1) ^ 1, B200_ALL_HINT ? 0 : B200_PWAIT);
         ptx::mbar_arrive_expect_tx(ptx::smem_u32(bar_afull), HALVES * tile_bytes);
         ptx::bulk_g2s(ptx::smem_u32(sA), reinterpret_cast<const uint8_t*>(p.a_img) + (size_t)qb * HALVES * tile_bytes,
                       HALVES * tile_bytes, ptx::smem_u32(bar_afull));
         const uint8_t* src = reinterpret_cast<const uint8_t*>(p.b_img);
         for (int t = 0; t < p.ntiles; ++t, src += tile_bytes) {
-          ptx::mbar_wait(B200_ALL_HINT, empty0 + s * 8, ph ^ 1, B200_ALL_HINT ? 0 : 64);
+          ptx::mbar_wait(B200_ALL_HINT, empty0 + s * 8, ph ^ 1, B200_ALL_HINT ? 0 : B200_PWAIT);
           ptx::mbar_arrive_expect_tx(full0 + s * 8, tile_bytes);
           // one tile as `parts` bulk copies: more requests in flight per slot (tile_bytes is a multiple of 4 KB)
           const uint32_t part = tile_bytes / (uint32_t)p.parts;
