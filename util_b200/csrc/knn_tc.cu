@@ -435,7 +435,7 @@ __device__ __forceinline__ float take_entry(float* ls, int* li, float s, bool ok
   return ls[e];
 }
 
-// ---- append-and-trim lists (U >= 2, keep <= 32U - 16).  A sorted insert into a 64- or 128-entry list costs
+// ---- append-and-trim lists (U >= 2, keep <= 32U - 12).  A sorted insert into a 64- or 128-entry list costs
 // a warp ~150 clk per survivor; here survivors are appended unsorted and, when the list is full, the row is
 // cut to the entries below its keep-th smallest score T (one bisection on the score bits), T becoming the
 // row's threshold.  Everything dropped or refused has score >= the threshold of that moment >= the final
@@ -836,7 +836,7 @@ __global__ void __launch_bounds__((HALVES * 12 + 3) * 32, 1) knn_tc_kernel(const
     const uint32_t c_ready = ptx::smem_u32(&ready[c]);
     const int keep = p.keep;
     uint32_t tail[2] = {0u, 0u};
-    const bool append = !THR && U >= 2 && keep <= W - 16;  // append-and-trim lists instead of sorted ones
+    const bool append = !THR && U >= 2 && keep <= W - 12;  // append-and-trim lists instead of sorted ones
     int cntreg = 0;         // append lists: entries in row c*32 + lane
     long long st_busy = 0;  // instrumented build only
     unsigned long long st_ev = 0, st_hit = 0, st_surv = 0, st_bulk = 0, st_trim = 0, st_pair = 0;
@@ -1278,14 +1278,15 @@ bool tc_config(int d, int k, int margin, bool self, int force_halves, TcConfig* 
   int keep = base + (margin < 0 ? std::max(4, std::min(k / 2, 16)) : margin);
   if (base > 128) return false;
   if (keep > 128) keep = 128;
-  // keep <= 32: sorted 32-entry lists; above that append-and-trim lists with >= 16 entries of head room
-  // (64 entries up to keep = 48, 128 up to 112), sorted 128-entry lists for the rest
-  // (in high dimension the 128-entry lists may not fit beside the operand tiles: keep <= 64 then falls
-  // back to sorted 64-entry lists)
-  const int u_first = keep <= 32 ? 1 : (keep <= 48 ? 2 : 4);
+  // keep <= 32: sorted 32-entry lists.  keep <= 64: 64-entry lists, append-and-trim while there are >= 12 entries of
+  // head room, sorted above.  Beyond that 128-entry lists (append-and-trim up to keep = 116), which only fit with one
+  // 128-row half per CTA -- half the selection warps per SM, measured 1.5x slower at equal keep -- so the default
+  // margin gives way down to 12 where that keeps a k <= 52 on the 64-entry lists.
+  if (margin < 0 && keep > 64 && base + 12 <= 64) keep = 64;
+  const int u_first = keep <= 32 ? 1 : (keep <= 64 ? 2 : 4);
   const size_t tile = (size_t)tc::TILE * K * 2;
   const size_t limit = 227 * 1024 - 1024;
-  for (int u = u_first; u >= 2 || u == u_first; u = (u == 4 && keep <= 64) ? 2 : 0)
+  const int u = u_first;
   for (int halves = 2; halves >= 1; --halves) {
     if (force_halves && halves != force_halves) continue;
     const int rows = halves * tc::TILE, epi = halves * 4;
