@@ -253,6 +253,8 @@ struct KParams {
   int32_t* cand_idx;     // [qpad][32*U]
   int32_t* cand_cnt;     // [qpad]
   float* cand_tau;       // [qpad]
+  float* cand_sc;        // glists: [qpad][32*U] scores of the lists kept in global memory (beside cand_idx)
+  int glists;            // append-and-trim lists live in cand_idx / cand_sc instead of shared memory
   const float* row_thr;  // THR kernels: [qpad] fixed threshold of every query row
   float* dbg;            // optional [qpad][ntiles*128] raw tensor dots (tests only)
   unsigned long long* stats;  // optional [16] counters of the instrumented build (tuning only): events, events with a
@@ -540,8 +542,11 @@ __global__ void __launch_bounds__((HALVES * 12 + 3) * 32, 1) knn_tc_kernel(const
   uint8_t* sA = smem;                                  // HALVES query tiles
   uint8_t* sB = sA + (size_t)HALVES * tile_bytes;      // ring of p.slots data tiles
   float* lsc = reinterpret_cast<float*>(sB + (size_t)p.slots * tile_bytes);  // [ROWS][W] list scores
-  int* lid = reinterpret_cast<int*>(lsc + (size_t)ROWS * W);                 // [ROWS][W] list positions
-  float* que = reinterpret_cast<float*>(lid + (size_t)ROWS * W);             // [2E][QE][QWORDS]
+  // (p.glists: the lists live in global memory -- append-and-trim lists are write-mostly, and 128-entry lists of two
+  //  halves do not fit beside the tiles -- and these two planes are empty)
+  const size_t list_elems = p.glists ? 0 : (size_t)ROWS * W;
+  int* lid = reinterpret_cast<int*>(lsc + list_elems);                       // [ROWS][W] list positions
+  float* que = reinterpret_cast<float*>(lid + list_elems);                   // [2E][QE][QWORDS]
   float* tau_sh = que + (size_t)2 * E * QE * QWORDS;                         // [ROWS] thresholds (written by selection warps)
   // queue control words, indexed [row block][column group]: heads, tails, done marks; then ready[row block]
   uint32_t* ctl = reinterpret_cast<uint32_t*>((reinterpret_cast<uintptr_t>(tau_sh + ROWS) + 7) & ~(uintptr_t)7);
@@ -832,6 +837,7 @@ __global__ void __launch_bounds__((HALVES * 12 + 3) * 32, 1) knn_tc_kernel(const
     const int c = warp - 2 * E;  // row block: rows c*32 .. c*32+31, fed by epilogue warps c and E + c
     float* ls0 = lsc + (size_t)c * 32 * W;
     int* li0 = lid + (size_t)c * 32 * W;
+    const bool glists = U >= 2 && !THR && p.glists != 0;
     float* tau0 = tau_sh + c * 32;
     const uint32_t c_ready = ptx::smem_u32(&ready[c]);
     const int keep = p.keep;
@@ -842,9 +848,14 @@ __global__ void __launch_bounds__((HALVES * 12 + 3) * 32, 1) knn_tc_kernel(const
     unsigned long long st_ev = 0, st_hit = 0, st_surv = 0, st_bulk = 0, st_trim = 0, st_pair = 0;
     for (int b = 0; b < nqb; ++b) {
       const int qb = (int)blockIdx.x + b * (int)gridDim.x;
-      for (int e = lane; e < 32 * W; e += 32) {
-        ls0[e] = CUDART_INF_F;
-        li0[e] = -1;
+      if (glists) {  // the rows' lists are their slices of the output arrays (only entries below the count are read)
+        ls0 = p.cand_sc + ((int64_t)qb * ROWS + c * 32) * W;
+        li0 = p.cand_idx + ((int64_t)qb * ROWS + c * 32) * W;
+      } else {
+        for (int e = lane; e < 32 * W; e += 32) {
+          ls0[e] = CUDART_INF_F;
+          li0[e] = -1;
+        }
       }
       int* cnt0 = reinterpret_cast<int*>(ls0);  // THR: entries per row (the score plane is unused there)
       if (THR) {
@@ -1040,16 +1051,18 @@ __global__ void __launch_bounds__((HALVES * 12 + 3) * 32, 1) knn_tc_kernel(const
         }
         __syncwarp();
       }
-      for (int r = 0; r < 32; ++r) {
-        int nv = 0;
+      if (!glists) {
+        for (int r = 0; r < 32; ++r) {
+          int nv = 0;
 #pragma unroll
-        for (int u = 0; u < U; ++u) {
-          const int e = u * 32 + lane;
-          const int id = li0[(size_t)r * W + e];
-          p.cand_idx[(q0 + r) * W + e] = id;
-          nv += __popc(__ballot_sync(0xffffffffu, id >= 0 && e < keep));
+          for (int u = 0; u < U; ++u) {
+            const int e = u * 32 + lane;
+            const int id = li0[(size_t)r * W + e];
+            p.cand_idx[(q0 + r) * W + e] = id;
+            nv += __popc(__ballot_sync(0xffffffffu, id >= 0 && e < keep));
+          }
+          if (lane == r) my_cnt = nv;
         }
-        if (lane == r) my_cnt = nv;
       }
       if (THR) my_cnt = min(cnt0[lane], W + 1);
       if (U >= 2 && append) my_cnt = cntreg;
@@ -1266,6 +1279,7 @@ int tc_prepare(b200_model* m, cudaStream_t st, const double* rw = nullptr) {
 
 struct TcConfig {
   int u, halves, slots, keep, qent;
+  int glists;  // the rows' lists live in global memory (128-entry append-and-trim lists)
   size_t smem;
 };
 
@@ -1287,10 +1301,13 @@ bool tc_config(int d, int k, int margin, bool self, int force_halves, TcConfig* 
   const size_t tile = (size_t)tc::TILE * K * 2;
   const size_t limit = 227 * 1024 - 1024;
   const int u = u_first;
+  // 128-entry append-and-trim lists are write-mostly (read only when a row is trimmed): they live in global memory,
+  // in the output arrays themselves, which leaves shared memory for two halves per CTA
+  const int glists = (u == 4 && keep <= 32 * u - 12) ? 1 : 0;
   for (int halves = 2; halves >= 1; --halves) {
     if (force_halves && halves != force_halves) continue;
     const int rows = halves * tc::TILE, epi = halves * 4;
-    const size_t fixed = halves * tile + (size_t)rows * 32 * u * 8 + (size_t)rows * 4 + (size_t)epi * 36 + 512;
+    const size_t fixed = halves * tile + (glists ? 0 : (size_t)rows * 32 * u * 8) + (size_t)rows * 4 + (size_t)epi * 36 + 512;
     const int choices[6][2] = {{8, 32}, {4, 32}, {8, 16}, {4, 16}, {2, 32}, {2, 16}};  // {ring slots, queue entries}
     for (const auto& ch : choices) {
       if (force_slots && ch[0] != force_slots) continue;
@@ -1301,6 +1318,7 @@ bool tc_config(int d, int k, int margin, bool self, int force_halves, TcConfig* 
       c->slots = ch[0];
       c->qent = ch[1];
       c->keep = keep;
+      c->glists = glists;
       c->smem = tot;
       return true;
     }
@@ -1403,7 +1421,7 @@ int shepmod_filter(b200_model* m, const double* z_dev, int64_t q, int32_t* cand_
                                                                         m->zimg.as<__half>(), qpad, meta);
   tc::row_thr_kernel<<<(unsigned)((qpad + 255) / 256), 256, 0, st>>>(meta, q, qpad, m->d, t.scale, t.cmax, row_thr);
   B200_CUDA(cudaGetLastError());
-  tc::KParams kp;
+  tc::KParams kp{};
   kp.a_img = m->zimg.as<__half>();
   kp.b_img = t.img.as<__half>();
   kp.nlo = t.nlo.as<float>();
@@ -1489,7 +1507,7 @@ int knn_tc(b200_model* m, const double* z_dev, int64_t q, int k, int64_t self_of
   const int64_t qpad = (int64_t)qblocks * rows;
   const int S = m->tc_split > 1 ? m->tc_split : 1;  // concurrent launches over sub-ranges of the data stream
   B200_TRY(m->zimg.reserve((size_t)qpad * t.K * 2));
-  B200_TRY(m->cand.reserve((size_t)S * qpad * W * 4));
+  B200_TRY(m->cand.reserve((size_t)S * qpad * W * 4 * (cfg.glists ? 2 : 1)));  // glists: scores behind the positions
   B200_TRY(m->cand_meta.reserve((size_t)qpad * (8 * S + sizeof(tc::QMeta)) + 64));
   B200_TRY(m->flags.reserve(256));
   B200_TRY(m->misc.reserve((size_t)q * 4 + 64));
@@ -1505,7 +1523,7 @@ int knn_tc(b200_model* m, const double* z_dev, int64_t q, int k, int64_t self_of
                                                                         m->zimg.as<__half>(), qpad, meta);
   B200_CUDA(cudaGetLastError());
   cudaEventRecord(m->ev0, st);
-  tc::KParams kp;
+  tc::KParams kp{};
   kp.a_img = m->zimg.as<__half>();
   kp.b_img = t.img.as<__half>();
   kp.nlo = t.nlo.as<float>();
@@ -1521,6 +1539,8 @@ int knn_tc(b200_model* m, const double* z_dev, int64_t q, int k, int64_t self_of
   kp.cand_idx = m->cand.as<int32_t>();
   kp.cand_cnt = cand_cnt;
   kp.cand_tau = cand_tau;
+  kp.glists = cfg.glists;
+  kp.cand_sc = cfg.glists ? reinterpret_cast<float*>(kp.cand_idx + (size_t)S * qpad * W) : nullptr;
   kp.dbg = dbg;
   kp.stats = nullptr;
   if (m->tc_stats) {  // instrumented build: event and stall counters (tuning only)
@@ -1533,6 +1553,7 @@ int knn_tc(b200_model* m, const double* z_dev, int64_t q, int k, int64_t self_of
     if (cfg.u == 1 && cfg.halves == 1) return launch_tc<1, 1>(m, kq, cfg, dg, s_);
     if (cfg.u == 2 && cfg.halves == 2) return launch_tc<2, 2>(m, kq, cfg, dg, s_);
     if (cfg.u == 2 && cfg.halves == 1) return launch_tc<2, 1>(m, kq, cfg, dg, s_);
+    if (cfg.u == 4 && cfg.halves == 2) return launch_tc<4, 2>(m, kq, cfg, dg, s_);
     if (cfg.u == 4 && cfg.halves == 1) return launch_tc<4, 1>(m, kq, cfg, dg, s_);
     set_error("tensor kNN: no kernel for u=%d halves=%d", cfg.u, cfg.halves);
     return 1;
