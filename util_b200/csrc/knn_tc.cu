@@ -1292,38 +1292,76 @@ bool tc_config(int d, int k, int margin, bool self, int force_halves, TcConfig* 
   int keep = base + (margin < 0 ? std::max(4, std::min(k / 2, 16)) : margin);
   if (base > 128) return false;
   if (keep > 128) keep = 128;
-  // keep <= 32: sorted 32-entry lists.  keep <= 64: 64-entry lists, append-and-trim while there are >= 12 entries of
-  // head room, sorted above.  Beyond that 128-entry lists (append-and-trim up to keep = 116), which only fit with one
-  // 128-row half per CTA -- half the selection warps per SM, measured 1.5x slower at equal keep -- so the default
-  // margin gives way down to 12 where that keeps a k <= 52 on the 64-entry lists.
-  if (margin < 0 && keep > 64 && base + 12 <= 64) keep = 64;
-  const int u_first = keep <= 32 ? 1 : (keep <= 64 ? 2 : 4);
+  // keep <= 32: sorted 32-entry lists in shared memory.  keep <= 52: 64-entry append-and-trim lists, in shared
+  // memory when that leaves room for two halves per CTA and a ring of four tiles, else in global memory.
+  // keep <= 116: 128-entry append-and-trim lists in global memory.  Above: sorted 128-entry lists in shared memory
+  // (one half per CTA: half the selection warps per SM, ~1.5x slower).
   const size_t tile = (size_t)tc::TILE * K * 2;
   const size_t limit = 227 * 1024 - 1024;
-  const int u = u_first;
-  // 128-entry append-and-trim lists are write-mostly (read only when a row is trimmed): they live in global memory,
-  // in the output arrays themselves, which leaves shared memory for two halves per CTA
-  const int glists = (u == 4 && keep <= 32 * u - 12) ? 1 : 0;
-  for (int halves = 2; halves >= 1; --halves) {
-    if (force_halves && halves != force_halves) continue;
-    const int rows = halves * tc::TILE, epi = halves * 4;
-    const size_t fixed = halves * tile + (glists ? 0 : (size_t)rows * 32 * u * 8) + (size_t)rows * 4 + (size_t)epi * 36 + 512;
-    const int choices[6][2] = {{8, 32}, {4, 32}, {8, 16}, {4, 16}, {2, 32}, {2, 16}};  // {ring slots, queue entries}
-    for (const auto& ch : choices) {
-      if (force_slots && ch[0] != force_slots) continue;
-      const size_t tot = fixed + (size_t)ch[0] * tile + (size_t)2 * epi * ch[1] * tc::QWORDS * 4;
-      if (tot > limit) continue;
-      c->u = u;
-      c->halves = halves;
-      c->slots = ch[0];
-      c->qent = ch[1];
-      c->keep = keep;
-      c->glists = glists;
-      c->smem = tot;
+  // Append-and-trim lists (keep <= 32u - 12) are write-mostly -- read only when a row is trimmed -- so they may live
+  // in global memory, in the output arrays themselves, which leaves shared memory for two halves per CTA and a
+  // deeper tile ring.
+  auto fit = [&](int u, int glists, TcConfig* out) -> bool {
+    if (glists && keep > 32 * u - 12) return false;
+    if (keep > 32 * u) return false;
+    for (int halves = 2; halves >= 1; --halves) {
+      if (force_halves && halves != force_halves) continue;
+      const int rows = halves * tc::TILE, epi = halves * 4;
+      const size_t fixed = halves * tile + (glists ? 0 : (size_t)rows * 32 * u * 8) + (size_t)rows * 4 + (size_t)epi * 36 + 512;
+      const int choices[6][2] = {{8, 32}, {4, 32}, {8, 16}, {4, 16}, {2, 32}, {2, 16}};  // {ring slots, queue entries}
+      for (const auto& ch : choices) {
+        if (force_slots && ch[0] != force_slots) continue;
+        const size_t tot = fixed + (size_t)ch[0] * tile + (size_t)2 * epi * ch[1] * tc::QWORDS * 4;
+        if (tot > limit) continue;
+        out->u = u;
+        out->halves = halves;
+        out->slots = ch[0];
+        out->qent = ch[1];
+        out->keep = keep;
+        out->glists = glists;
+        out->smem = tot;
+        return true;
+      }
+    }
+    return false;
+  };
+  // candidates in order of preference; the first that runs two halves per CTA on a ring of >= 4 tiles wins,
+  // else the first that fits at all
+  int cand[3][2];  // {u, lists in global memory}
+  int ncand = 0;
+  auto add = [&](int u, int g) {
+    cand[ncand][0] = u;
+    cand[ncand][1] = g;
+    ++ncand;
+  };
+  if (keep <= 32) {
+    add(1, 0);
+  } else if (keep <= 52) {
+    add(2, 0);
+    add(2, 1);
+  } else if (keep <= 116) {
+    add(4, 1);
+    if (keep <= 64) add(2, 0);
+    add(4, 0);
+  } else {
+    add(4, 0);
+  }
+  TcConfig first{}, t{};
+  bool have_first = false;
+  for (int ci = 0; ci < ncand; ++ci) {
+    const int* cd = cand[ci];
+    if (!fit(cd[0], cd[1], &t)) continue;
+    if (t.halves == 2 && t.slots >= 4) {
+      *c = t;
       return true;
     }
+    if (!have_first) {
+      first = t;
+      have_first = true;
+    }
   }
-  return false;
+  if (have_first) *c = first;
+  return have_first;
 }
 
 template <int HALVES>
