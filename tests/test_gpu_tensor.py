@@ -76,9 +76,10 @@ def test_tensor_accumulation_error_bound(L):
 @pytest.mark.parametrize("n,q,d,k", [(20000, 1000, 64, 16), (30000, 700, 16, 17), (9000, 513, 8, 1),
                                      (12000, 300, 32, 33), (5000, 260, 10, 15), (40000, 300, 3, 8),
                                      (8000, 300, 100, 5), (6000, 130, 125, 3),  # K = 112 / 128: generic K loop, one half per CTA
-                                     (5000, 260, 10, 40), (7000, 200, 20, 100),  # 128-entry lists: append-and-trim / sorted
+                                     (5000, 260, 10, 40), (7000, 200, 20, 100),  # 128-entry append-and-trim lists in global memory
                                      (15000, 400, 24, 24), (50000, 600, 32, 64),  # 64-entry append lists; C4's shape
-                                     (9000, 200, 100, 33)])  # high d: 128-entry lists do not fit, sorted 64-entry ones do
+                                     (9000, 200, 100, 33),   # high d: the 64-entry append lists move to global memory
+                                     (6000, 300, 12, 110)])  # keep > 116: sorted 128-entry lists in shared memory, one half per CTA
 def test_tensor_knn_bit_exact(L, oracle, n, q, d, k):
     x, z = synth(n, q, d)
     m = L.Model(x)
