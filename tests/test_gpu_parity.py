@@ -188,6 +188,33 @@ def test_shepmod_vs_oracle(ub, oracle, n, q, d):
         ub.ShepMod().fit(x[:d + 1])
 
 
+@pytest.mark.parametrize("n,q,d", [(6000, 42000, 64), (5000, 52000, 29)])
+def test_shepmod_tensor_filter_high_dimension(ub, oracle, n, q, d):
+    """The radius filter on the tensor path (n*q >= 2.5e8) where a 128-row tile is large: its hit lists stay in
+    shared memory whatever the kNN kernel of that shape does with its lists.  Sample against the oracle, everything
+    against the library's dense scan."""
+    from util_b200 import _lib
+    x, z = synth(n, q, d)
+    z[:50] = x[:50]
+    y = fun(x)
+    res = []
+    for path in (_lib.PATH_AUTO, _lib.PATH_EXACT):
+        m = _lib.Model(x)
+        m.set_option("knn_path", path)
+        rw, ier = m.shepmod_fit()
+        res.append(m.shepmod_predict(z, cap=128, y=y))
+        m.close()
+    (i1, w1, c1, e1, o1), (i0, w0, c0, e0, o0) = res
+    assert np.array_equal(c0, c1) and np.array_equal(e0, e1) and np.array_equal(o0, o1)
+    sel = np.random.default_rng(3).choice(q, 200, replace=False)
+    oi, ow, oc, oe = oracle.shepmod_predict(x, rw, z[sel], cap=n)
+    ref = oracle.weighted_sum(oi, ow, oc, y)
+    assert relerr(o1[sel, 0], ref) < RTOL
+    for r, p in enumerate(sel):
+        assert np.array_equal(i1[p, :c1[p]], oi[r, :oc[r]])
+        assert np.array_equal(i0[p, :c0[p]], oi[r, :oc[r]])
+
+
 def test_shepmod_capacity_growth(ub, oracle):
     x, z = synth(3000, 100, 2)
     m = ub.ShepMod()

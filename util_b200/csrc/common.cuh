@@ -144,6 +144,7 @@ int merge_topk(const double* d2_parts, const int32_t* idx_parts, int parts, int6
                double* d2_out, int32_t* idx_out, cudaStream_t st);
 // knn_tc.cu
 bool tc_supported(const b200_model* m, int k);
+bool shepmod_filter_supported(const b200_model* m);
 int shepmod_filter(b200_model* m, const double* z_dev, int64_t q, int32_t* cand_rows, int32_t* cand_cnt,
                    cudaStream_t st);
 int knn_tc(b200_model* m, const double* z_dev, int64_t q, int k, int64_t self_offset,

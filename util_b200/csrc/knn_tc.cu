@@ -1286,7 +1286,8 @@ struct TcConfig {
 // Kernel shape for k (+1 when the query's own row is dropped later): the sorted list of a row holds
 // 32*u entries (u = 1, 2, 4), of which the first keep = k + margin count; two 128-row halves per CTA
 // when shared memory allows, else one; the data-tile ring and the selection queues share what is left.
-bool tc_config(int d, int k, int margin, bool self, int force_halves, TcConfig* c, int force_slots = 0) {
+bool tc_config(int d, int k, int margin, bool self, int force_halves, TcConfig* c, int force_slots = 0,
+               bool shared_lists_only = false) {
   const int K = tc::padK(d);
   const int base = k + (self ? 1 : 0);
   int keep = base + (margin < 0 ? std::max(4, std::min(k / 2, 16)) : margin);
@@ -1302,7 +1303,7 @@ bool tc_config(int d, int k, int margin, bool self, int force_halves, TcConfig* 
   // in global memory, in the output arrays themselves, which leaves shared memory for two halves per CTA and a
   // deeper tile ring.
   auto fit = [&](int u, int glists, TcConfig* out) -> bool {
-    if (glists && keep > 32 * u - 12) return false;
+    if (glists && (shared_lists_only || keep > 32 * u - 12)) return false;
     if (keep > 32 * u) return false;
     for (int halves = 2; halves >= 1; --halves) {
       if (force_halves && halves != force_halves) continue;
@@ -1440,7 +1441,7 @@ int shepmod_filter(b200_model* m, const double* z_dev, int64_t q, int32_t* cand_
   const TcData& t = m->tc_sm;
   TcConfig cfg;
   // shape as for a 64-entry list (u = 2); keep is not used by the threshold kernel
-  if (!tc_config(m->d, 40, 0, false, 0, &cfg)) {
+  if (!tc_config(m->d, 40, 0, false, 0, &cfg, 0, /*shared_lists_only=*/true)) {  // the radius filter keeps its hit lists in shared memory
     set_error("radius filter unsupported for d=%d", m->d);
     return 1;
   }
@@ -1497,6 +1498,12 @@ int shepmod_filter(b200_model* m, const double* z_dev, int64_t q, int32_t* cand_
 bool tc_supported(const b200_model* m, int k) {
   TcConfig c;
   return tc_config(m->d, k, 0, true, 0, &c);
+}
+
+// the radius filter's shape: 64-entry hit lists in shared memory (the same call as in shepmod_filter)
+bool shepmod_filter_supported(const b200_model* m) {
+  TcConfig c;
+  return tc_config(m->d, 40, 0, false, 0, &c, 0, /*shared_lists_only=*/true);
 }
 
 static bool t_tiles_ok(const b200_model* m, int split) { return m->tc.tiles >= (int64_t)split * 64; }

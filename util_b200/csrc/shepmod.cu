@@ -612,7 +612,7 @@ int shepmod_predict(b200_model* m, const double* z_dev, int64_t q, int cap, int3
   // Large problems: the radius test DIST < RW(K) is first run as a tensor-core filter (the same fused
   // contraction as the kNN path with a per-node threshold), then SHEPMODVAL's arithmetic runs on the few
   // candidate nodes of each query; the dense scan below takes what the filter hands back.
-  const bool filter = m->knn_path != B200_PATH_EXACT && tc_supported(m, 40) && (double)m->n * (double)q >= 2.5e8 &&
+  const bool filter = m->knn_path != B200_PATH_EXACT && shepmod_filter_supported(m) && (double)m->n * (double)q >= 2.5e8 &&
                       m->n >= 4096 && d >= 5;
   if (!filter) return shepmod_dense(m, z_dev, q, cap, ids_dev, wts_dev, cnt_dev, ier_dev, y_dev, r, out_dev, st);
   B200_TRY(m->part_idx.reserve((size_t)q * 64 * 4));
