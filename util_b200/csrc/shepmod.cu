@@ -374,7 +374,8 @@ shepmod_block_kernel(const double* __restrict__ x, const double* __restrict__ rw
                      const double* __restrict__ z, const int32_t* __restrict__ sel, int cap,
                      int32_t* __restrict__ ids, double* __restrict__ wts, int32_t* __restrict__ cnt,
                      int32_t* __restrict__ ier, const double* __restrict__ y, int r, double* __restrict__ out) {
-  __shared__ double s_z[SM_FB], s_D[SM_FB], s_a[SM_BT], s_rk[SM_BT];
+  __shared__ __align__(16) double s_z[SM_FB];
+  __shared__ double s_D[SM_FB], s_a[SM_BT], s_rk[SM_BT];
   __shared__ int s_DI[SM_FB];
   __shared__ unsigned s_in[SM_BT / 32], s_cd[SM_BT / 32];
   __shared__ int s_c, s_hit, s_J;
@@ -404,7 +405,7 @@ shepmod_block_kernel(const double* __restrict__ x, const double* __restrict__ rw
     if (s_hit >= 0) break;  // uniform: written before the last barrier
     double a = CUDART_INF, rk = 0.0;
     if (k < n) {
-      a = sqdist_seq(s_z, x + k * d, d);
+      a = sqdist_seq_wide<true>(x + k * d, s_z, d);  // the row's loads in flight together; (x - z)^2 == (z - x)^2 bit for bit
       rk = rw[k];
     }
     const double r2 = rk * rk;
