@@ -986,6 +986,54 @@ __global__ void __launch_bounds__((HALVES * 12 + 3) * 32, 1) knn_tc_kernel(const
                 }
               }
             }
+            if (B200_PAIR && U >= 2 && !THR && append && h - tl >= 2) {
+              // append lists: two entries of different rows per step as well, one per half-warp (two values per
+              // lane); a pair that would overfill one of the two lists is left to the single path and its trim
+              const float* ea = myq + (size_t)(tl & (uint32_t)(QE - 1)) * QWORDS;
+              const float* eb = myq + (size_t)((tl + 1) & (uint32_t)(QE - 1)) * QWORDS;
+              const int4 ma = *reinterpret_cast<const int4*>(ea + 32);
+              const int4 mb = *reinterpret_cast<const int4*>(eb + 32);
+              if (ma.x != mb.x) {
+                const int hw = lane >> 4, sub = lane & 15;
+                const float* em = hw ? eb : ea;
+                const int4 mt = hw ? mb : ma;
+                const float nlc = __int_as_float(mt.z);
+                const float v0 = em[sub] + nlc, v1 = em[16 + sub] + nlc;
+                const float tq = tau0[mt.x];
+                const unsigned b0 = __ballot_sync(0xffffffffu, v0 < tq && mt.y + sub < p.ncols);
+                const unsigned b1 = __ballot_sync(0xffffffffu, v1 < tq && mt.y + 16 + sub < p.ncols);
+                const unsigned mA = (b0 & 0xffffu) | (b1 << 16), mB = (b0 >> 16) | (b1 & 0xffff0000u);
+                const int haveA = __shfl_sync(0xffffffffu, cntreg, ma.x), haveB = __shfl_sync(0xffffffffu, cntreg, mb.x);
+                if (haveA + __popc(mA) <= W && haveB + __popc(mB) <= W) {
+                  tl += 2;
+                  if (lane == 0) ptx::st_volatile_shared_u32(a_tails + 4 * g, tl);
+                  if (DBG) {
+                    st_pair += 2;
+                    st_ev += 2;
+                    st_hit += (mA != 0) + (mB != 0);
+                    st_surv += __popc(mA) + __popc(mB);
+                  }
+                  const unsigned mm = hw ? mB : mA;
+                  const int have = hw ? haveB : haveA;
+                  float* lsr = ls0 + (size_t)mt.x * W;
+                  int* lir = li0 + (size_t)mt.x * W;
+                  if ((mm >> sub) & 1u) {
+                    const int r = have + __popc(mm & ((1u << sub) - 1u));
+                    lsr[r] = v0;
+                    lir[r] = mt.y + sub;
+                  }
+                  if ((mm >> (16 + sub)) & 1u) {
+                    const int r = have + __popc(mm & ((1u << (16 + sub)) - 1u));
+                    lsr[r] = v1;
+                    lir[r] = mt.y + 16 + sub;
+                  }
+                  if (lane == ma.x) cntreg = haveA + __popc(mA);
+                  if (lane == mb.x) cntreg = haveB + __popc(mB);
+                  __syncwarp();
+                  continue;
+                }
+              }
+            }
             const float* e = myq + (size_t)(tl & (uint32_t)(QE - 1)) * QWORDS;
             const int4 meta = *reinterpret_cast<const int4*>(e + 32);
             const float s = e[lane] + __int_as_float(meta.z);  // dot + nlo of the chunk
